@@ -1,0 +1,104 @@
+"""Minimal R1CS container + the synthetic circuits of the BASELINE configs
+(oracle; test infrastructure only).
+
+Wire numbering follows constraint/core.go:227-248: [ONE, public..., secret...,
+internal...].  A constraint is (L, R, O), each a list of (coeff, wire) with
+L.w * R.w == O.w (constraint/bn254/solver.go:540-628 accumulates exactly these
+three inner products into a[c], b[c], c[c]).
+"""
+from .bn254 import R
+
+
+class R1CS:
+    def __init__(self, nb_public, nb_secret):
+        # nb_public includes the ONE wire (GetNbPublicVariables)
+        self.nb_public = nb_public
+        self.nb_secret = nb_secret
+        self.nb_internal = 0
+        self.constraints = []
+
+    @property
+    def nb_wires(self):
+        return self.nb_public + self.nb_secret + self.nb_internal
+
+    @property
+    def nb_constraints(self):
+        return len(self.constraints)
+
+    def new_internal(self):
+        idx = self.nb_wires
+        self.nb_internal += 1
+        return idx
+
+    def add(self, L, Rr, O):
+        self.constraints.append((L, Rr, O))
+
+    def abc(self, w):
+        """per-constraint L.w, R.w, O.w; raises if unsatisfied."""
+        def dot(le):
+            return sum(cf * w[i] for cf, i in le) % R
+        a, b, c = [], [], []
+        for k, (L, Rr, O) in enumerate(self.constraints):
+            x, y, z = dot(L), dot(Rr), dot(O)
+            if x * y % R != z:
+                raise ValueError(f"constraint #{k} is not satisfied")
+            a.append(x)
+            b.append(y)
+            c.append(z)
+        return a, b, c
+
+
+def cubic_circuit():
+    """examples/cubic/cubic.go:32-36: x^3 + x + 5 == y.  Wires: 0=ONE 1=Y 2=X 3=x^2 4=x^3."""
+    cs = R1CS(nb_public=2, nb_secret=1)
+    v1 = cs.new_internal()
+    v2 = cs.new_internal()
+    cs.add([(1, 2)], [(1, 2)], [(1, v1)])
+    cs.add([(1, v1)], [(1, 2)], [(1, v2)])
+    cs.add([(1, v2), (1, 2), (5, 0)], [(1, 0)], [(1, 1)])
+    return cs
+
+
+def cubic_witness(x, y):
+    x %= R
+    return [1, y % R, x, x * x % R, x * x * x % R]
+
+
+def mimc_chain(nb_constraints, rng):
+    """MiMC-shaped chain (std/hash/mimc/encrypt.go:124-128,147-153, pow5 rounds):
+    x <- (x + k + c_i)^5, 3 constraints per round, then one assertion that binds
+    the public output; filler squarings bring the count to exactly nb_constraints.
+    Wires: 0=ONE 1=OUT(public) 2=X0(secret) 3=K(secret).  Returns (cs, consts)."""
+    cs = R1CS(nb_public=2, nb_secret=2)
+    consts = []
+    x = [(1, 2)]            # linear expression for the running state
+    rounds = (nb_constraints - 1) // 3
+    for _ in range(rounds):
+        ci = rng.field(R)
+        consts.append(ci)
+        t = x + [(1, 3), (ci, 0)]
+        u = cs.new_internal()
+        cs.add(t, t, [(1, u)])
+        v = cs.new_internal()
+        cs.add([(1, u)], [(1, u)], [(1, v)])
+        nx = cs.new_internal()
+        cs.add([(1, v)], t, [(1, nx)])
+        x = [(1, nx)]
+    while cs.nb_constraints < nb_constraints - 1:
+        nx = cs.new_internal()
+        cs.add(x, x, [(1, nx)])
+        x = [(1, nx)]
+    cs.add(x + [(1, 3)], [(1, 0)], [(1, 1)])
+    return cs, consts
+
+
+def mimc_chain_witness(cs, x0, k):
+    """solve the chain: every constraint defines at most one new wire (its O)."""
+    w = [0] * cs.nb_wires
+    w[0], w[2], w[3] = 1, x0 % R, k % R
+    def dot(le):
+        return sum(cf * w[i] for cf, i in le) % R
+    for L, Rr, O in cs.constraints:
+        (cf, o), = O
+        w[o] = dot(L) * dot(Rr) % R
+    return w
