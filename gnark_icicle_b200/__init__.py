@@ -1,0 +1,14 @@
+"""gnark_icicle_b200 -- B200-native Groth16 (BN254) proving hot path behind gnark's icicle surface.
+
+  csrc/        hand-written sm_100a CUDA (field core, NTT/computeH, Pippenger MSM G1/G2) + the C ABI
+  lib.py       ctypes binding of libg16b200.so (stand-in for the cgo layer)
+  groth16.py   mirror of package icicle_bn254 (Prove, ProvingKey, WithIcicleAcceleration)
+
+The directory ``gnark-icicle_b200`` at the repo root is a link to this package (a hyphen is not importable).
+"""
+from . import lib
+from .groth16 import (HasIcicle, Prove, ProvingKey, Proof, R1CSSolution, WithIcicleAcceleration, WithRandomness,
+                      WithDevice, NewProverConfig, prove_msms, assemble, combine_shards)
+
+__all__ = ["lib", "HasIcicle", "Prove", "ProvingKey", "Proof", "R1CSSolution", "WithIcicleAcceleration",
+           "WithRandomness", "WithDevice", "NewProverConfig", "prove_msms", "assemble", "combine_shards"]

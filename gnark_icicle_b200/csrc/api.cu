@@ -1,0 +1,606 @@
+// C ABI of libg16b200 (declared in include/g16b200.h): context, device-resident proving key, the prove
+// hot path, primitives and measurement helpers.  Host logic only -- kernels live in ntt.cu / msm*.cu.
+//
+// Reference shape being replaced: backend/groth16/bn254/icicle/icicle.go (setupDevicePointers :31-130,
+// Prove :133-422, computeH :453-513) and icicle/provingkey.go:10-28 (deviceInfo).
+#include <chrono>
+#include <cstdlib>
+#include <memory>
+
+#include "../../include/g16b200.h"
+#include "msm_api.cuh"
+#include "ntt.cuh"
+
+using namespace g16;
+
+namespace {
+
+struct PkDev {
+    uint64_t domain_n = 0;
+    int logn = 0;
+    uint64_t n_wires = 0;
+    // this shard's slices
+    DevBuf g1_a, g1_b, g1_k, g1_z, g2_b;
+    DevBuf map_a, map_b, map_k;   // u32 wire index per base
+    uint64_t n_a = 0, n_b = 0, n_k = 0, n_z = 0, n_b2 = 0;
+    uint64_t z_off = 0;           // first h index of this shard's Z slice
+    void release() {
+        g1_a.release(); g1_b.release(); g1_k.release(); g1_z.release(); g2_b.release();
+        map_a.release(); map_b.release(); map_k.release();
+    }
+};
+
+}  // namespace
+
+struct g16_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[16] = {};
+    std::string err;
+    std::map<int, NttDomain> domains;
+    std::map<uint64_t, PkDev> pks;
+    uint64_t next_pk = 1;
+    MsmWorkspace ws[5];
+    DevBuf stage[4];             // host-pointer variants: staged inputs
+    DevBuf fb_table_g1, fb_table_g2;
+    int msm_c = 0, msm_waves = 2;
+
+    NttDomain& domain(int logn) {
+        auto it = domains.find(logn);
+        if (it != domains.end()) return it->second;
+        NttDomain& d = domains[logn];
+        d.init(logn);
+        return d;
+    }
+};
+
+namespace {
+
+template <class F>
+int guarded(g16_ctx* ctx, F&& f) {
+    if (!ctx) return 1;
+    try {
+        G16_CUDA(cudaSetDevice(ctx->device));
+        f();
+        return 0;
+    } catch (const std::exception& e) {
+        ctx->err = e.what();
+        cudaGetLastError();   // clear a sticky launch error so that later calls report their own
+        return 2;
+    }
+}
+
+bool is_pow2(uint64_t n) { return n && !(n & (n - 1)); }
+
+void slice(uint64_t len, uint32_t idx, uint32_t cnt, uint64_t& lo, uint64_t& hi) {
+    if (cnt <= 1) { lo = 0; hi = len; return; }
+    lo = len * idx / cnt;
+    hi = len * (idx + 1) / cnt;
+}
+
+void upload(DevBuf& dst, const void* src, size_t bytes, cudaStream_t st) {
+    dst.reserve(bytes ? bytes : 16);
+    if (bytes) G16_CUDA(cudaMemcpyAsync(dst.p, src, bytes, cudaMemcpyHostToDevice, st));
+}
+
+}  // namespace
+
+extern "C" {
+
+int g16_ctx_create(g16_ctx** out, int curve_id, const int* device_ids, int n_devices) {
+    if (!out) return 1;
+    *out = nullptr;
+    if (curve_id != G16_CURVE_BN254) return 3;
+    if (n_devices > 1) return 4;
+    std::unique_ptr<g16_ctx> c(new g16_ctx());
+    try {
+        int count = 0;
+        G16_CUDA(cudaGetDeviceCount(&count));
+        if (count < 1) throw std::runtime_error("no CUDA device: libg16b200 has no CPU fallback");
+        c->device = (device_ids && n_devices == 1) ? device_ids[0] : 0;
+        G16_CUDA(cudaSetDevice(c->device));
+        G16_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+        for (auto& e : c->ev) G16_CUDA(cudaEventCreate(&e));
+        if (const char* e = getenv("G16_MSM_C")) c->msm_c = atoi(e);
+        if (const char* e = getenv("G16_MSM_WAVES")) c->msm_waves = atoi(e);
+    } catch (const std::exception& e) {
+        fprintf(stderr, "g16_ctx_create: %s\n", e.what());
+        return 2;
+    }
+    *out = c.release();
+    return 0;
+}
+
+void g16_ctx_destroy(g16_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    for (auto& kv : ctx->pks) kv.second.release();
+    for (auto& kv : ctx->domains) kv.second.release();
+    for (auto& w : ctx->ws) w.release();
+    for (auto& s : ctx->stage) s.release();
+    ctx->fb_table_g1.release(); ctx->fb_table_g2.release();
+    for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char* g16_last_error(const g16_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int g16_ctx_set(g16_ctx* ctx, const char* key, int64_t value) {
+    if (!ctx || !key) return 1;
+    std::string k(key);
+    if (k == "msm_c") ctx->msm_c = (int)value;
+    else if (k == "msm_waves") ctx->msm_waves = (int)value;
+    else { ctx->err = "unknown tunable " + k; return 1; }
+    return 0;
+}
+
+uint64_t g16_kernel_launch_count(void) { return launch_counter().load(); }
+void* g16_ctx_stream(g16_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+}  // extern "C"
+
+// =================================================================== proving key
+extern "C" int g16_pk_upload(g16_ctx* ctx, const g16_pk_desc* d, uint64_t* pk_handle) {
+    return guarded(ctx, [&] {
+        if (!d || !pk_handle) throw std::runtime_error("null argument");
+        if (!is_pow2(d->domain_n)) throw std::runtime_error("domain_n must be a power of two");
+        if (d->n_b2 != d->n_b) throw std::runtime_error("G2.B and G1.B must have the same length");
+        if (d->n_z + 1 != d->domain_n && d->n_z != d->domain_n) throw std::runtime_error("G1.Z must have domain_n - 1 entries");
+        if (d->n_k > d->n_wires) throw std::runtime_error("G1.K longer than the wire vector");
+        const uint32_t sc = d->shard_count ? d->shard_count : 1, si = d->shard_index;
+        if (si >= sc) throw std::runtime_error("shard_index out of range");
+        cudaStream_t st = ctx->stream;
+        PkDev pk;
+        pk.domain_n = d->domain_n;
+        pk.logn = ilog2_ceil(d->domain_n);
+        pk.n_wires = d->n_wires;
+
+        // wire index of every A / B base: position among the non-infinity wires (prove.go:152-178)
+        std::vector<uint32_t> ma, mb, mk;
+        ma.reserve(d->n_a); mb.reserve(d->n_b);
+        for (uint64_t i = 0; i < d->n_wires; i++) {
+            if (!d->infinity_a || !d->infinity_a[i]) ma.push_back((uint32_t)i);
+            if (!d->infinity_b || !d->infinity_b[i]) mb.push_back((uint32_t)i);
+        }
+        if (ma.size() != d->n_a) throw std::runtime_error("InfinityA does not match len(G1.A): " + std::to_string(ma.size()) + " vs " + std::to_string(d->n_a));
+        if (mb.size() != d->n_b) throw std::runtime_error("InfinityB does not match len(G1.B): " + std::to_string(mb.size()) + " vs " + std::to_string(d->n_b));
+        mk.resize(d->n_k);
+        for (uint64_t i = 0; i < d->n_k; i++) {
+            mk[i] = d->k_index ? d->k_index[i] : (uint32_t)(d->n_wires - d->n_k + i);
+            if (mk[i] >= d->n_wires) throw std::runtime_error("k_index out of range");
+        }
+
+        uint64_t lo, hi;
+        slice(d->n_a, si, sc, lo, hi);
+        pk.n_a = hi - lo;
+        upload(pk.g1_a, (const char*)d->g1_a + lo * 64, pk.n_a * 64, st);
+        upload(pk.map_a, ma.data() + lo, pk.n_a * 4, st);
+        slice(d->n_b, si, sc, lo, hi);
+        pk.n_b = pk.n_b2 = hi - lo;
+        upload(pk.g1_b, (const char*)d->g1_b + lo * 64, pk.n_b * 64, st);
+        upload(pk.g2_b, (const char*)d->g2_b + lo * 128, pk.n_b * 128, st);
+        upload(pk.map_b, mb.data() + lo, pk.n_b * 4, st);
+        slice(d->n_k, si, sc, lo, hi);
+        pk.n_k = hi - lo;
+        upload(pk.g1_k, (const char*)d->g1_k + lo * 64, pk.n_k * 64, st);
+        upload(pk.map_k, mk.data() + lo, pk.n_k * 4, st);
+        uint64_t nz = d->n_z < d->domain_n ? d->n_z : d->domain_n - 1;   // h[:n-1] (prove.go:235-237)
+        slice(nz, si, sc, lo, hi);
+        pk.n_z = hi - lo;
+        pk.z_off = lo;
+        upload(pk.g1_z, (const char*)d->g1_z + lo * 64, pk.n_z * 64, st);
+
+        // twiddles of the domain (replaces icicle.go:44-75)
+        NttDomain& dom = ctx->domain(pk.logn);
+        dom.table(TW_INV, st);
+        dom.table(TW_COSET_FWD, st);
+        dom.table(TW_COSET_INV, st);
+        G16_CUDA(cudaStreamSynchronize(st));   // host vectors above go out of scope
+        uint64_t h = ctx->next_pk++;
+        ctx->pks[h] = pk;
+        *pk_handle = h;
+    });
+}
+
+extern "C" int g16_pk_free(g16_ctx* ctx, uint64_t pk_handle) {
+    return guarded(ctx, [&] {
+        auto it = ctx->pks.find(pk_handle);
+        if (it == ctx->pks.end()) throw std::runtime_error("unknown proving-key handle");
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+        it->second.release();
+        ctx->pks.erase(it);
+    });
+}
+
+// =================================================================== prove
+namespace {
+
+template <class Aff>
+void copy_out(void* dst, const Aff& p) { memcpy(dst, &p, sizeof(Aff)); }
+
+void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* b_d, Fr::T* c_d, void* out_points,
+                  g16_stats* stats, uint64_t launches0) {
+    cudaStream_t st = ctx->stream;
+    NttDomain& dom = ctx->domain(pk.logn);
+    cudaEvent_t* ev = ctx->ev;
+    MsmPlan plan[5];
+    MsmStats ms[5];
+    G16_CUDA(cudaEventRecord(ev[0], st));
+    compute_h_device(dom, a_d, b_d, c_d, st);                 // h (bit-reversed) in a_d
+    G16_CUDA(cudaEventRecord(ev[1], st));
+    msm_g1_enqueue(ctx->ws[G16_OUT_AR], W_d, pk.map_a.as<uint32_t>(), pk.g1_a.as<G1::Aff>(), pk.n_a, ctx->msm_c, ctx->msm_waves, st, plan[0], &ms[0]);
+    G16_CUDA(cudaEventRecord(ev[2], st));
+    msm_g1_enqueue(ctx->ws[G16_OUT_BS1], W_d, pk.map_b.as<uint32_t>(), pk.g1_b.as<G1::Aff>(), pk.n_b, ctx->msm_c, ctx->msm_waves, st, plan[1], &ms[1]);
+    G16_CUDA(cudaEventRecord(ev[3], st));
+    msm_g1_enqueue(ctx->ws[G16_OUT_KRS_K], W_d, pk.map_k.as<uint32_t>(), pk.g1_k.as<G1::Aff>(), pk.n_k, ctx->msm_c, ctx->msm_waves, st, plan[2], &ms[2]);
+    G16_CUDA(cudaEventRecord(ev[4], st));
+    msm_g1_enqueue(ctx->ws[G16_OUT_KRS_HZ], a_d + pk.z_off, nullptr, pk.g1_z.as<G1::Aff>(), pk.n_z, ctx->msm_c, ctx->msm_waves, st, plan[3], &ms[3]);
+    G16_CUDA(cudaEventRecord(ev[5], st));
+    msm_g2_enqueue(ctx->ws[G16_OUT_BS2], W_d, pk.map_b.as<uint32_t>(), pk.g2_b.as<G2::Aff>(), pk.n_b2, ctx->msm_c, ctx->msm_waves, st, plan[4], &ms[4]);
+    G16_CUDA(cudaEventRecord(ev[6], st));
+    G16_CUDA(cudaStreamSynchronize(st));
+    auto t0 = std::chrono::steady_clock::now();
+    char* out = (char*)out_points;
+    const uint64_t ns[5] = {pk.n_a, pk.n_b, pk.n_k, pk.n_z, pk.n_b2};
+    for (int i = 0; i < 4; i++) copy_out(out + 64 * i, ns[i] ? msm_g1_finish(ctx->ws[i], plan[i]) : G1::aff_inf());
+    copy_out(out + 256, ns[4] ? msm_g2_finish(ctx->ws[4], plan[4]) : G2::aff_inf());
+    auto t1 = std::chrono::steady_clock::now();
+    if (stats) {
+        G16_CUDA(cudaEventElapsedTime(&stats->ms_compute_h, ev[0], ev[1]));
+        for (int i = 0; i < 5; i++) {
+            G16_CUDA(cudaEventElapsedTime(&stats->ms_msm[i], ev[1 + i], ev[2 + i]));
+            stats->msm_c[i] = plan[i].c; stats->msm_windows[i] = plan[i].W; stats->msm_n[i] = ns[i];
+        }
+        G16_CUDA(cudaEventElapsedTime(&stats->ms_total, ev[0], ev[6]));
+        stats->ms_host = std::chrono::duration<float, std::milli>(t1 - t0).count();
+        stats->d2h_bytes = 0;
+        for (int i = 0; i < 5; i++) stats->d2h_bytes += (uint64_t)plan[i].W * (i == 4 ? sizeof(G2::Xyzz) : sizeof(G1::Xyzz));
+        stats->kernel_launches = (uint32_t)(launch_counter().load() - launches0);
+    }
+}
+
+}  // namespace
+
+extern "C" int g16_prove_bn254_dev(g16_ctx* ctx, uint64_t pk_handle, const void* W_d, void* a_d, void* b_d, void* c_d,
+                                   void* out_points, g16_stats* stats) {
+    return guarded(ctx, [&] {
+        auto it = ctx->pks.find(pk_handle);
+        if (it == ctx->pks.end()) throw std::runtime_error("unknown proving-key handle");
+        if (!W_d || !a_d || !b_d || !c_d || !out_points) throw std::runtime_error("null argument");
+        uint64_t l0 = launch_counter().load();
+        if (stats) memset(stats, 0, sizeof(*stats));
+        prove_device(ctx, it->second, (const Fr::T*)W_d, (Fr::T*)a_d, (Fr::T*)b_d, (Fr::T*)c_d, out_points, stats, l0);
+    });
+}
+
+extern "C" int g16_prove_bn254(g16_ctx* ctx, uint64_t pk_handle, const void* W, uint64_t n_wires, const void* a,
+                               const void* b, const void* c, uint64_t n_constraints, void* out_points, g16_stats* stats) {
+    return guarded(ctx, [&] {
+        auto it = ctx->pks.find(pk_handle);
+        if (it == ctx->pks.end()) throw std::runtime_error("unknown proving-key handle");
+        PkDev& pk = it->second;
+        if (!W || !a || !b || !c || !out_points) throw std::runtime_error("null argument");
+        if (n_wires != pk.n_wires) throw std::runtime_error("witness length does not match the proving key");
+        if (n_constraints > pk.domain_n) throw std::runtime_error("more constraints than the domain holds");
+        uint64_t l0 = launch_counter().load();
+        if (stats) memset(stats, 0, sizeof(*stats));
+        cudaStream_t st = ctx->stream;
+        const size_t nb = (size_t)pk.domain_n * 32, cb = (size_t)n_constraints * 32;
+        G16_CUDA(cudaEventRecord(ctx->ev[8], st));
+        const void* src[3] = {a, b, c};
+        for (int i = 0; i < 3; i++) {      // pad to the domain size (icicle.go:463-467)
+            ctx->stage[i].reserve(nb);
+            G16_CUDA(cudaMemcpyAsync(ctx->stage[i].p, src[i], cb, cudaMemcpyHostToDevice, st));
+            if (nb > cb) G16_CUDA(cudaMemsetAsync((char*)ctx->stage[i].p + cb, 0, nb - cb, st));
+        }
+        ctx->stage[3].reserve((size_t)n_wires * 32);
+        G16_CUDA(cudaMemcpyAsync(ctx->stage[3].p, W, (size_t)n_wires * 32, cudaMemcpyHostToDevice, st));
+        G16_CUDA(cudaEventRecord(ctx->ev[9], st));
+        prove_device(ctx, pk, ctx->stage[3].as<Fr::T>(), ctx->stage[0].as<Fr::T>(), ctx->stage[1].as<Fr::T>(),
+                     ctx->stage[2].as<Fr::T>(), out_points, stats, l0);
+        if (stats) {
+            G16_CUDA(cudaEventElapsedTime(&stats->ms_h2d, ctx->ev[8], ctx->ev[9]));
+            stats->ms_total += stats->ms_h2d;
+            stats->h2d_bytes = 3 * cb + (uint64_t)n_wires * 32;
+        }
+    });
+}
+
+// =================================================================== primitives
+namespace {
+
+void msm_g1_dev_impl(g16_ctx* ctx, const void* s_d, const void* b_d, uint64_t n, void* out) {
+    MsmPlan pl;
+    if (n) {
+        msm_g1_enqueue(ctx->ws[0], (const Fr::T*)s_d, nullptr, (const G1::Aff*)b_d, n, ctx->msm_c, ctx->msm_waves, ctx->stream, pl, nullptr);
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    copy_out(out, n ? msm_g1_finish(ctx->ws[0], pl) : G1::aff_inf());
+}
+void msm_g2_dev_impl(g16_ctx* ctx, const void* s_d, const void* b_d, uint64_t n, void* out) {
+    MsmPlan pl;
+    if (n) {
+        msm_g2_enqueue(ctx->ws[4], (const Fr::T*)s_d, nullptr, (const G2::Aff*)b_d, n, ctx->msm_c, ctx->msm_waves, ctx->stream, pl, nullptr);
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    copy_out(out, n ? msm_g2_finish(ctx->ws[4], pl) : G2::aff_inf());
+}
+
+// gnark fft.Domain semantics on a device array (see include/g16b200.h)
+void ntt_dev_impl(g16_ctx* ctx, Fr::T* x, uint64_t n, int inverse, int coset, int decimation) {
+    if (!is_pow2(n)) throw std::runtime_error("NTT size must be a power of two");
+    int logn = ilog2_ceil(n);
+    NttDomain& d = ctx->domain(logn);
+    cudaStream_t st = ctx->stream;
+    NttBatch b{{x, x, x}, 1};
+    if (n == 1) return;   // every variant is the identity on one element (g^0 = 1, 1/n = 1)
+    if (!inverse) {
+        if (decimation == G16_DIT) {
+            ntt_dit(d, b, coset ? TW_COSET_FWD : TW_FWD, st);
+        } else {
+            if (coset) fr_scale_powers(x, n, logn, Fr::one(), d.coset_gen, 0, 1, st);   // a[i] *= g^i (natural index)
+            ntt_dif(d, b, TW_FWD, st);
+        }
+    } else {
+        if (decimation == G16_DIF) {
+            ntt_dif(d, b, coset ? TW_COSET_INV : TW_INV, st);
+            fr_scale_powers(x, n, logn, d.n_inv, Fr::one(), 0, 0, st);
+        } else {
+            ntt_dit(d, b, TW_INV, st);
+            if (coset) fr_scale_powers(x, n, logn, d.n_inv, d.coset_inv, 0, 1, st);   // natural order out
+            else fr_scale_powers(x, n, logn, d.n_inv, Fr::one(), 0, 0, st);
+        }
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+int g16_msm_g1_dev(g16_ctx* ctx, const void* s_d, const void* b_d, uint64_t n, void* out) {
+    return guarded(ctx, [&] { msm_g1_dev_impl(ctx, s_d, b_d, n, out); });
+}
+int g16_msm_g2_dev(g16_ctx* ctx, const void* s_d, const void* b_d, uint64_t n, void* out) {
+    return guarded(ctx, [&] { msm_g2_dev_impl(ctx, s_d, b_d, n, out); });
+}
+int g16_msm_g1(g16_ctx* ctx, const void* scalars, const void* bases, uint64_t n, void* out) {
+    return guarded(ctx, [&] {
+        upload(ctx->stage[0], scalars, n * 32, ctx->stream);
+        upload(ctx->stage[1], bases, n * 64, ctx->stream);
+        msm_g1_dev_impl(ctx, ctx->stage[0].p, ctx->stage[1].p, n, out);
+    });
+}
+int g16_msm_g2(g16_ctx* ctx, const void* scalars, const void* bases, uint64_t n, void* out) {
+    return guarded(ctx, [&] {
+        upload(ctx->stage[0], scalars, n * 32, ctx->stream);
+        upload(ctx->stage[1], bases, n * 128, ctx->stream);
+        msm_g2_dev_impl(ctx, ctx->stage[0].p, ctx->stage[1].p, n, out);
+    });
+}
+
+int g16_ntt_dev(g16_ctx* ctx, void* data_d, uint64_t n, int inverse, int coset, int decimation) {
+    return guarded(ctx, [&] {
+        ntt_dev_impl(ctx, (Fr::T*)data_d, n, inverse, coset, decimation);
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+int g16_ntt(g16_ctx* ctx, void* data, uint64_t n, int inverse, int coset, int decimation) {
+    return guarded(ctx, [&] {
+        upload(ctx->stage[0], data, n * 32, ctx->stream);
+        ntt_dev_impl(ctx, ctx->stage[0].as<Fr::T>(), n, inverse, coset, decimation);
+        G16_CUDA(cudaMemcpyAsync(data, ctx->stage[0].p, n * 32, cudaMemcpyDeviceToHost, ctx->stream));
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+
+int g16_compute_h_dev(g16_ctx* ctx, void* a_d, void* b_d, void* c_d, uint64_t domain_n) {
+    return guarded(ctx, [&] {
+        if (!is_pow2(domain_n)) throw std::runtime_error("domain_n must be a power of two");
+        compute_h_device(ctx->domain(ilog2_ceil(domain_n)), (Fr::T*)a_d, (Fr::T*)b_d, (Fr::T*)c_d, ctx->stream);
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+int g16_compute_h(g16_ctx* ctx, const void* a, const void* b, const void* c, uint64_t n_constraints, uint64_t domain_n, void* h_out) {
+    return guarded(ctx, [&] {
+        if (!is_pow2(domain_n) || n_constraints > domain_n) throw std::runtime_error("bad domain size");
+        const size_t nb = (size_t)domain_n * 32, cb = (size_t)n_constraints * 32;
+        const void* src[3] = {a, b, c};
+        for (int i = 0; i < 3; i++) {
+            ctx->stage[i].reserve(nb);
+            if (cb) G16_CUDA(cudaMemcpyAsync(ctx->stage[i].p, src[i], cb, cudaMemcpyHostToDevice, ctx->stream));
+            if (nb > cb) G16_CUDA(cudaMemsetAsync((char*)ctx->stage[i].p + cb, 0, nb - cb, ctx->stream));
+        }
+        compute_h_device(ctx->domain(ilog2_ceil(domain_n)), ctx->stage[0].as<Fr::T>(), ctx->stage[1].as<Fr::T>(), ctx->stage[2].as<Fr::T>(), ctx->stream);
+        G16_CUDA(cudaMemcpyAsync(h_out, ctx->stage[0].p, nb, cudaMemcpyDeviceToHost, ctx->stream));
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+
+int g16_fr_mul_vec(g16_ctx* ctx, const void* a, const void* b, uint64_t n, void* out) {
+    return guarded(ctx, [&] {
+        upload(ctx->stage[0], a, n * 32, ctx->stream);
+        upload(ctx->stage[1], b, n * 32, ctx->stream);
+        fr_mul_vec(ctx->stage[0].as<Fr::T>(), ctx->stage[0].as<Fr::T>(), ctx->stage[1].as<Fr::T>(), n, ctx->stream);
+        if (n) G16_CUDA(cudaMemcpyAsync(out, ctx->stage[0].p, n * 32, cudaMemcpyDeviceToHost, ctx->stream));
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+
+int g16_g1_fixed_base_mul_dev(g16_ctx* ctx, const void* s_d, uint64_t n, void* out_d) {
+    return guarded(ctx, [&] {
+        fixed_base_g1(ctx->fb_table_g1, (const Fr::T*)s_d, n, (G1::Aff*)out_d, ctx->stream);
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+int g16_g2_fixed_base_mul_dev(g16_ctx* ctx, const void* s_d, uint64_t n, void* out_d) {
+    return guarded(ctx, [&] {
+        fixed_base_g2(ctx->fb_table_g2, (const Fr::T*)s_d, n, (G2::Aff*)out_d, ctx->stream);
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+int g16_g1_fixed_base_mul(g16_ctx* ctx, const void* scalars, uint64_t n, void* out) {
+    return guarded(ctx, [&] {
+        upload(ctx->stage[0], scalars, n * 32, ctx->stream);
+        ctx->stage[1].reserve(n * 64 + 16);
+        fixed_base_g1(ctx->fb_table_g1, ctx->stage[0].as<Fr::T>(), n, ctx->stage[1].as<G1::Aff>(), ctx->stream);
+        if (n) G16_CUDA(cudaMemcpyAsync(out, ctx->stage[1].p, n * 64, cudaMemcpyDeviceToHost, ctx->stream));
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+int g16_g2_fixed_base_mul(g16_ctx* ctx, const void* scalars, uint64_t n, void* out) {
+    return guarded(ctx, [&] {
+        upload(ctx->stage[0], scalars, n * 32, ctx->stream);
+        ctx->stage[1].reserve(n * 128 + 16);
+        fixed_base_g2(ctx->fb_table_g2, ctx->stage[0].as<Fr::T>(), n, ctx->stage[1].as<G2::Aff>(), ctx->stream);
+        if (n) G16_CUDA(cudaMemcpyAsync(out, ctx->stage[1].p, n * 128, cudaMemcpyDeviceToHost, ctx->stream));
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+
+}  // extern "C"
+
+// =================================================================== host-side group helpers + epilogue
+namespace {
+
+template <class C>
+typename C::Aff aff_add(const typename C::Aff& a, const typename C::Aff& b) {
+    typename C::Xyzz t = C::from_aff(a);
+    C::madd(t, b);
+    return C::to_aff(t);
+}
+template <class C>
+typename C::Aff aff_mul(const typename C::Aff& a, const Fr::T& k_mont) {
+    Fr::T k = Fr::from_mont(k_mont);
+    return C::to_aff(C::mul(C::from_aff(a), k.l, 8));
+}
+template <class T>
+T rd(const void* p) { T v; memcpy(&v, p, sizeof(T)); return v; }
+
+}  // namespace
+
+extern "C" {
+
+int g16_g1_add(const void* a, const void* b, void* out) {
+    if (!a || !b || !out) return 1;
+    copy_out(out, aff_add<G1>(rd<G1::Aff>(a), rd<G1::Aff>(b)));
+    return 0;
+}
+int g16_g2_add(const void* a, const void* b, void* out) {
+    if (!a || !b || !out) return 1;
+    copy_out(out, aff_add<G2>(rd<G2::Aff>(a), rd<G2::Aff>(b)));
+    return 0;
+}
+int g16_g1_scalar_mul(const void* a, const void* k, void* out) {
+    if (!a || !k || !out) return 1;
+    copy_out(out, aff_mul<G1>(rd<G1::Aff>(a), rd<Fr::T>(k)));
+    return 0;
+}
+int g16_g2_scalar_mul(const void* a, const void* k, void* out) {
+    if (!a || !k || !out) return 1;
+    copy_out(out, aff_mul<G2>(rd<G2::Aff>(a), rd<Fr::T>(k)));
+    return 0;
+}
+
+// prove.go:180-195 (kr = -r*s, deltas), :209-224 (ar), :202-212 (bs1), :251-279 (krs), :297-302 (Bs)
+int g16_assemble_proof_bn254(const void* pk_points, const void* r_, const void* s_, const void* msm_points, void* proof_out) {
+    if (!pk_points || !r_ || !s_ || !msm_points || !proof_out) return 1;
+    const char* pp = (const char*)pk_points;
+    const char* mp = (const char*)msm_points;
+    G1::Aff alpha = rd<G1::Aff>(pp), beta = rd<G1::Aff>(pp + 64), delta = rd<G1::Aff>(pp + 128);
+    G2::Aff beta2 = rd<G2::Aff>(pp + 192), delta2 = rd<G2::Aff>(pp + 320);
+    Fr::T r = rd<Fr::T>(r_), s = rd<Fr::T>(s_);
+    Fr::T kr = Fr::neg(Fr::mul(r, s));
+    G1::Aff d_r = aff_mul<G1>(delta, r), d_s = aff_mul<G1>(delta, s), d_kr = aff_mul<G1>(delta, kr);
+    G1::Aff ar = aff_add<G1>(aff_add<G1>(rd<G1::Aff>(mp + 64 * G16_OUT_AR), alpha), d_r);
+    G1::Aff bs1 = aff_add<G1>(aff_add<G1>(rd<G1::Aff>(mp + 64 * G16_OUT_BS1), beta), d_s);
+    G1::Aff krs = aff_add<G1>(rd<G1::Aff>(mp + 64 * G16_OUT_KRS_K), d_kr);
+    krs = aff_add<G1>(krs, rd<G1::Aff>(mp + 64 * G16_OUT_KRS_HZ));
+    krs = aff_add<G1>(krs, aff_mul<G1>(ar, s));
+    krs = aff_add<G1>(krs, aff_mul<G1>(bs1, r));
+    G2::Aff bs = aff_add<G2>(aff_add<G2>(rd<G2::Aff>(mp + 256), aff_mul<G2>(delta2, s)), beta2);
+    char* o = (char*)proof_out;
+    copy_out(o, ar);
+    copy_out(o + 64, bs);
+    copy_out(o + 192, krs);
+    return 0;
+}
+
+}  // extern "C"
+
+// =================================================================== integer-pipe peak microbenchmark
+namespace {
+
+template <bool WIDE>
+__global__ void __launch_bounds__(256) k_imad_peak(uint32_t* sink, uint32_t a0, uint32_t b0, int iters) {
+    uint32_t a = a0 + threadIdx.x, b = b0 | 1u;
+    if (WIDE) {
+        uint64_t x0 = threadIdx.x, x1 = a, x2 = b, x3 = 7, x4 = 11, x5 = 13, x6 = 17, x7 = 19;
+        for (int i = 0; i < iters; i++) {
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(x0) : "r"(a), "r"(b));
+                asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(x1) : "r"(a), "r"(b));
+                asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(x2) : "r"(a), "r"(b));
+                asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(x3) : "r"(a), "r"(b));
+                asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(x4) : "r"(a), "r"(b));
+                asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(x5) : "r"(a), "r"(b));
+                asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(x6) : "r"(a), "r"(b));
+                asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(x7) : "r"(a), "r"(b));
+            }
+        }
+        uint64_t x = x0 ^ x1 ^ x2 ^ x3 ^ x4 ^ x5 ^ x6 ^ x7;
+        if (x == 0x123456789abcdefull) sink[0] = (uint32_t)x;
+    } else {
+        uint32_t x0 = threadIdx.x, x1 = a, x2 = b, x3 = 7, x4 = 11, x5 = 13, x6 = 17, x7 = 19;
+        for (int i = 0; i < iters; i++) {
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(x0) : "r"(a), "r"(b));
+                asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(x1) : "r"(a), "r"(b));
+                asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(x2) : "r"(a), "r"(b));
+                asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(x3) : "r"(a), "r"(b));
+                asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(x4) : "r"(a), "r"(b));
+                asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(x5) : "r"(a), "r"(b));
+                asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(x6) : "r"(a), "r"(b));
+                asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(x7) : "r"(a), "r"(b));
+            }
+        }
+        uint32_t x = x0 ^ x1 ^ x2 ^ x3 ^ x4 ^ x5 ^ x6 ^ x7;
+        if (x == 0x12345678u) sink[0] = x;
+    }
+}
+
+template <bool WIDE>
+double imad_rate(g16_ctx* ctx, uint32_t* sink) {
+    int sms = 0;
+    G16_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
+    const int iters = 4096, blocks = sms * 8;
+    cudaStream_t st = ctx->stream;
+    k_imad_peak<WIDE><<<blocks, 256, 0, st>>>(sink, 3, 5, 64);   // warm-up
+    G16_LAUNCH_CHECK();
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; rep++) {
+        G16_CUDA(cudaEventRecord(ctx->ev[10], st));
+        k_imad_peak<WIDE><<<blocks, 256, 0, st>>>(sink, 3, 5, iters);
+        G16_LAUNCH_CHECK();
+        G16_CUDA(cudaEventRecord(ctx->ev[11], st));
+        G16_CUDA(cudaStreamSynchronize(st));
+        float ms = 0;
+        G16_CUDA(cudaEventElapsedTime(&ms, ctx->ev[10], ctx->ev[11]));
+        if (ms < best) best = ms;
+    }
+    double ops = (double)blocks * 256 * iters * 64;
+    return ops / (best * 1e-3);
+}
+
+}  // namespace
+
+extern "C" int g16_imad_peak(g16_ctx* ctx, double* imad_per_s, double* imad_wide_per_s) {
+    return guarded(ctx, [&] {
+        ctx->stage[0].reserve(64);
+        if (imad_per_s) *imad_per_s = imad_rate<false>(ctx, ctx->stage[0].as<uint32_t>());
+        if (imad_wide_per_s) *imad_wide_per_s = imad_rate<true>(ctx, ctx->stage[0].as<uint32_t>());
+    });
+}

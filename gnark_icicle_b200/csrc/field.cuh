@@ -1,0 +1,318 @@
+// Montgomery prime fields on 32-bit limbs for sm_100a (device: mad.lo.cc / madc.hi.cc carry chains that
+// ptxas fuses into IMAD.WIDE.U32.X; host: portable 64-bit code used only by the O(1) epilogue).
+//
+// Replaces the arithmetic the reference obtains from gnark-crypto fr/fp (go.mod:11; call sites
+// backend/groth16/bn254/prove.go:356-399 for fr, :202-304 for fp) and, on its GPU path, from icicle's
+// device field (backend/groth16/bn254/icicle/icicle.go:489-510 NTT/vec ops, :302-382 MSM).
+// Memory image = gnark-crypto's: N/2 little-endian uint64 limbs == N little-endian uint32 limbs,
+// Montgomery form with R = 2^(32N).
+#pragma once
+#include <cstdint>
+#include <cstring>
+
+#ifdef __CUDACC__
+#define G16_HD __host__ __device__ __forceinline__
+#define G16_D __device__ __forceinline__
+// cold paths (inversion, full group additions, doublings): real calls keep compile time and
+// register pressure of the hot kernels down
+#define G16_HD_COLD __host__ __device__ __noinline__
+#else
+#define G16_HD inline
+#define G16_D inline
+#define G16_HD_COLD inline
+#endif
+
+namespace g16 {
+
+template <int N>
+struct alignas(16) Big {
+    uint32_t l[N];
+};
+
+// ---------------------------------------------------------------- field parameter packs
+// mod(i) etc. are switch-based so that, after unrolling, every limb is an immediate operand.
+struct FpBN254 {
+    static constexpr int N = 8;
+    static constexpr uint32_t INV = 0xe4866389u;  // -p^-1 mod 2^32
+    G16_HD static constexpr uint32_t mod(int i) {
+        constexpr uint32_t m[8] = {0xd87cfd47u, 0x3c208c16u, 0x6871ca8du, 0x97816a91u, 0x8181585du, 0xb85045b6u, 0xe131a029u, 0x30644e72u};
+        return m[i];
+    }
+    G16_HD static constexpr uint32_t one(int i) {  // R mod p
+        constexpr uint32_t m[8] = {0xc58f0d9du, 0xd35d438du, 0xf5c70b3du, 0x0a78eb28u, 0x7879462cu, 0x666ea36fu, 0x9a07df2fu, 0x0e0a77c1u};
+        return m[i];
+    }
+    G16_HD static constexpr uint32_t r2(int i) {  // R^2 mod p
+        constexpr uint32_t m[8] = {0x538afa89u, 0xf32cfc5bu, 0xd44501fbu, 0xb5e71911u, 0x0a417ff6u, 0x47ab1effu, 0xcab8351fu, 0x06d89f71u};
+        return m[i];
+    }
+};
+struct FrBN254 {
+    static constexpr int N = 8;
+    static constexpr uint32_t INV = 0xefffffffu;
+    G16_HD static constexpr uint32_t mod(int i) {
+        constexpr uint32_t m[8] = {0xf0000001u, 0x43e1f593u, 0x79b97091u, 0x2833e848u, 0x8181585du, 0xb85045b6u, 0xe131a029u, 0x30644e72u};
+        return m[i];
+    }
+    G16_HD static constexpr uint32_t one(int i) {
+        constexpr uint32_t m[8] = {0x4ffffffbu, 0xac96341cu, 0x9f60cd29u, 0x36fc7695u, 0x7879462eu, 0x666ea36fu, 0x9a07df2fu, 0x0e0a77c1u};
+        return m[i];
+    }
+    G16_HD static constexpr uint32_t r2(int i) {
+        constexpr uint32_t m[8] = {0xae216da7u, 0x1bb8e645u, 0xe35c59e3u, 0x53fe3ab1u, 0x53bb8085u, 0x8c49833du, 0x7f4e44a5u, 0x0216d0b1u};
+        return m[i];
+    }
+};
+
+#ifdef __CUDA_ARCH__
+// ---------------------------------------------------------------- PTX carry-chain primitives
+namespace ptx {
+G16_D uint32_t add_cc(uint32_t a, uint32_t b) { uint32_t r; asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+G16_D uint32_t addc_cc(uint32_t a, uint32_t b) { uint32_t r; asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+G16_D uint32_t addc(uint32_t a, uint32_t b) { uint32_t r; asm volatile("addc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+G16_D uint32_t sub_cc(uint32_t a, uint32_t b) { uint32_t r; asm volatile("sub.cc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+G16_D uint32_t subc_cc(uint32_t a, uint32_t b) { uint32_t r; asm volatile("subc.cc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+G16_D uint32_t subc(uint32_t a, uint32_t b) { uint32_t r; asm volatile("subc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+G16_D uint32_t mul_lo(uint32_t a, uint32_t b) { uint32_t r; asm volatile("mul.lo.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+G16_D uint32_t mul_hi(uint32_t a, uint32_t b) { uint32_t r; asm volatile("mul.hi.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+G16_D uint32_t mad_lo_cc(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("mad.lo.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
+G16_D uint32_t madc_lo_cc(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("madc.lo.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
+G16_D uint32_t madc_hi_cc(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("madc.hi.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
+G16_D uint32_t madc_hi(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("madc.hi.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
+}  // namespace ptx
+#endif
+
+// ---------------------------------------------------------------- the field
+template <class P>
+struct Field {
+    static constexpr int N = P::N;
+    typedef Big<N> T;
+
+    G16_HD static T zero() { T r;
+#pragma unroll
+        for (int i = 0; i < N; i++) r.l[i] = 0; return r; }
+    G16_HD static T one() { T r;
+#pragma unroll
+        for (int i = 0; i < N; i++) r.l[i] = P::one(i); return r; }
+    G16_HD static T r2() { T r;
+#pragma unroll
+        for (int i = 0; i < N; i++) r.l[i] = P::r2(i); return r; }
+    G16_HD static T modulus() { T r;
+#pragma unroll
+        for (int i = 0; i < N; i++) r.l[i] = P::mod(i); return r; }
+    G16_HD static bool is_zero(const T& a) { uint32_t o = 0;
+#pragma unroll
+        for (int i = 0; i < N; i++) o |= a.l[i]; return o == 0; }
+    G16_HD static bool eq(const T& a, const T& b) { uint32_t o = 0;
+#pragma unroll
+        for (int i = 0; i < N; i++) o |= a.l[i] ^ b.l[i]; return o == 0; }
+
+    // r = a - p if a >= p (a < 2p)
+    G16_HD static T reduce_once(const T& a) {
+        T s;
+#ifdef __CUDA_ARCH__
+        s.l[0] = ptx::sub_cc(a.l[0], P::mod(0));
+#pragma unroll
+        for (int i = 1; i < N; i++) s.l[i] = ptx::subc_cc(a.l[i], P::mod(i));
+        uint32_t borrow = ptx::subc(0, 0);  // 0xffffffff if a < p
+        T r;
+#pragma unroll
+        for (int i = 0; i < N; i++) r.l[i] = borrow ? a.l[i] : s.l[i];
+        return r;
+#else
+        uint64_t br = 0;
+        for (int i = 0; i < N; i++) { uint64_t d = (uint64_t)a.l[i] - P::mod(i) - br; s.l[i] = (uint32_t)d; br = (d >> 32) & 1; }
+        return br ? a : s;
+#endif
+    }
+
+    G16_HD static T add(const T& a, const T& b) {
+        T r;
+#ifdef __CUDA_ARCH__
+        r.l[0] = ptx::add_cc(a.l[0], b.l[0]);
+#pragma unroll
+        for (int i = 1; i < N - 1; i++) r.l[i] = ptx::addc_cc(a.l[i], b.l[i]);
+        r.l[N - 1] = ptx::addc(a.l[N - 1], b.l[N - 1]);  // p < 2^(32N-1): no carry out
+#else
+        uint64_t c = 0;
+        for (int i = 0; i < N; i++) { c += (uint64_t)a.l[i] + b.l[i]; r.l[i] = (uint32_t)c; c >>= 32; }
+#endif
+        return reduce_once(r);
+    }
+    G16_HD static T dbl(const T& a) { return add(a, a); }
+
+    G16_HD static T sub(const T& a, const T& b) {
+        T r;
+#ifdef __CUDA_ARCH__
+        r.l[0] = ptx::sub_cc(a.l[0], b.l[0]);
+#pragma unroll
+        for (int i = 1; i < N; i++) r.l[i] = ptx::subc_cc(a.l[i], b.l[i]);
+        uint32_t borrow = ptx::subc(0, 0);
+        r.l[0] = ptx::add_cc(r.l[0], borrow & P::mod(0));
+#pragma unroll
+        for (int i = 1; i < N - 1; i++) r.l[i] = ptx::addc_cc(r.l[i], borrow & P::mod(i));
+        r.l[N - 1] = ptx::addc(r.l[N - 1], borrow & P::mod(N - 1));
+#else
+        uint64_t br = 0;
+        for (int i = 0; i < N; i++) { uint64_t d = (uint64_t)a.l[i] - b.l[i] - br; r.l[i] = (uint32_t)d; br = (d >> 32) & 1; }
+        if (br) { uint64_t c = 0; for (int i = 0; i < N; i++) { c += (uint64_t)r.l[i] + P::mod(i); r.l[i] = (uint32_t)c; c >>= 32; } }
+#endif
+        return r;
+    }
+    G16_HD static T neg(const T& a) { return is_zero(a) ? a : sub(zero(), a); }
+
+#ifdef __CUDA_ARCH__
+    // acc[j], acc[j+1] = a[j] * bi for even j  (a may point at the odd limbs)
+    G16_D static void mul_n(uint32_t* acc, const uint32_t* a, uint32_t bi) {
+#pragma unroll
+        for (int j = 0; j < N; j += 2) { acc[j] = ptx::mul_lo(a[j], bi); acc[j + 1] = ptx::mul_hi(a[j], bi); }
+    }
+    // acc += (a[0], a[2], ...) * bi as one carry chain; carry-out is left in CC
+    G16_D static void cmad_n(uint32_t* acc, const uint32_t* a, uint32_t bi) {
+        acc[0] = ptx::mad_lo_cc(a[0], bi, acc[0]);
+        acc[1] = ptx::madc_hi_cc(a[0], bi, acc[1]);
+#pragma unroll
+        for (int j = 2; j < N; j += 2) { acc[j] = ptx::madc_lo_cc(a[j], bi, acc[j]); acc[j + 1] = ptx::madc_hi_cc(a[j], bi, acc[j + 1]); }
+    }
+    // same with the modulus limbs (immediates): acc += (p[o], p[o+2], ...) * m
+    template <int O>
+    G16_D static void cmad_mod(uint32_t* acc, uint32_t m) {
+        acc[0] = ptx::mad_lo_cc(P::mod(O), m, acc[0]);
+        acc[1] = ptx::madc_hi_cc(P::mod(O), m, acc[1]);
+#pragma unroll
+        for (int j = 2; j < N; j += 2) { acc[j] = ptx::madc_lo_cc(P::mod(O + j), m, acc[j]); acc[j + 1] = ptx::madc_hi_cc(P::mod(O + j), m, acc[j + 1]); }
+    }
+    // y <- (y >> 64) + (a[0], a[2], ...) * bi, consuming the carry in CC (a points at the odd limbs)
+    G16_D static void madc_n_rshift(uint32_t* y, const uint32_t* a, uint32_t bi) {
+#pragma unroll
+        for (int j = 0; j < N - 2; j += 2) { y[j] = ptx::madc_lo_cc(a[j], bi, y[j + 2]); y[j + 1] = ptx::madc_hi_cc(a[j], bi, y[j + 3]); }
+        y[N - 2] = ptx::madc_lo_cc(a[N - 2], bi, 0);
+        y[N - 1] = ptx::madc_hi(a[N - 1 - 1], bi, 0);
+    }
+    // one interleaved multiply-reduce step; x plays "even" (position 0), y plays "odd" (position 1)
+    G16_D static void mad_redc(uint32_t* x, uint32_t* y, const uint32_t* a, uint32_t bi, bool first) {
+        if (first) {
+            mul_n(y, a + 1, bi);
+            mul_n(x, a, bi);
+        } else {
+            x[0] = ptx::add_cc(x[0], y[1]);
+            madc_n_rshift(y, a + 1, bi);
+            cmad_n(x, a, bi);
+            y[N - 1] = ptx::addc(y[N - 1], 0);
+        }
+        uint32_t m = x[0] * P::INV;
+        cmad_mod<1>(y, m);
+        cmad_mod<0>(x, m);
+        y[N - 1] = ptx::addc(y[N - 1], 0);
+    }
+#endif
+
+    // Montgomery product a*b*R^-1 mod p, inputs and output in [0, p)
+    G16_HD static T mul(const T& a, const T& b) {
+#ifdef __CUDA_ARCH__
+        uint32_t even[N], odd[N];
+#pragma unroll
+        for (int i = 0; i < N; i += 2) {
+            mad_redc(even, odd, a.l, b.l[i], i == 0);
+            mad_redc(odd, even, a.l, b.l[i + 1], false);
+        }
+        // result = even + (odd >> 32)
+        T r;
+        r.l[0] = ptx::add_cc(even[0], odd[1]);
+#pragma unroll
+        for (int i = 1; i < N - 1; i++) r.l[i] = ptx::addc_cc(even[i], odd[i + 1]);
+        r.l[N - 1] = ptx::addc(even[N - 1], 0);
+        return reduce_once(r);
+#else
+        // host: CIOS on 64-bit limbs (epilogue only; never on the accelerated path)
+        constexpr int M = N / 2;
+        typedef unsigned __int128 u128;
+        uint64_t A[M], B[M], Q[M], t[M + 2];
+        for (int i = 0; i < M; i++) {
+            A[i] = (uint64_t)a.l[2 * i] | ((uint64_t)a.l[2 * i + 1] << 32);
+            B[i] = (uint64_t)b.l[2 * i] | ((uint64_t)b.l[2 * i + 1] << 32);
+            Q[i] = (uint64_t)P::mod(2 * i) | ((uint64_t)P::mod(2 * i + 1) << 32);
+        }
+        uint64_t x = (uint64_t)(0u - P::INV);          // p^-1 mod 2^32
+        x = x * (2 - Q[0] * x);                        // Newton step -> mod 2^64
+        const uint64_t inv64 = 0 - x;
+        for (int i = 0; i < M + 2; i++) t[i] = 0;
+        for (int i = 0; i < M; i++) {
+            u128 c = 0;
+            for (int j = 0; j < M; j++) { c += (u128)A[j] * B[i] + t[j]; t[j] = (uint64_t)c; c >>= 64; }
+            c += t[M]; t[M] = (uint64_t)c; t[M + 1] = (uint64_t)(c >> 64);
+            uint64_t m = t[0] * inv64;
+            c = (u128)m * Q[0] + t[0]; c >>= 64;
+            for (int j = 1; j < M; j++) { c += (u128)m * Q[j] + t[j]; t[j - 1] = (uint64_t)c; c >>= 64; }
+            c += t[M]; t[M - 1] = (uint64_t)c; t[M] = t[M + 1] + (uint64_t)(c >> 64);
+        }
+        T r;
+        for (int i = 0; i < M; i++) { r.l[2 * i] = (uint32_t)t[i]; r.l[2 * i + 1] = (uint32_t)(t[i] >> 32); }
+        return reduce_once(r);
+#endif
+    }
+    G16_HD static T sqr(const T& a) { return mul(a, a); }
+    G16_HD static T to_mont(const T& a) { return mul(a, r2()); }
+    G16_HD static T from_mont(const T& a) { T o = zero(); o.l[0] = 1; return mul(a, o); }
+
+    // a^e, e a plain little-endian integer of `words` 32-bit words (not constant time; host/tooling use)
+    G16_HD_COLD static T pow(const T& a, const uint32_t* e, int words) {
+        T acc = one();
+        for (int i = words * 32 - 1; i >= 0; i--) {
+            acc = sqr(acc);
+            if ((e[i >> 5] >> (i & 31)) & 1) acc = mul(acc, a);
+        }
+        return acc;
+    }
+    G16_HD static T pow_u64(const T& a, uint64_t e) {
+        uint32_t w[2] = {(uint32_t)e, (uint32_t)(e >> 32)};
+        return pow(a, w, 2);
+    }
+    // Fermat inversion a^(p-2); inv(0) = 0
+    G16_HD_COLD static T inv(const T& a) {
+        uint32_t e[N];
+        uint64_t br = 2;
+        for (int i = 0; i < N; i++) { uint64_t d = (uint64_t)P::mod(i) - br; e[i] = (uint32_t)d; br = (d >> 32) & 1; }
+        return pow(a, e, N);
+    }
+    G16_HD static T from_u64(uint64_t v) { T t = zero(); t.l[0] = (uint32_t)v; t.l[1] = (uint32_t)(v >> 32); return to_mont(t); }
+};
+
+typedef Field<FpBN254> Fp;
+typedef Field<FrBN254> Fr;
+
+// ---------------------------------------------------------------- Fp2 = Fp[u]/(u^2+1)  (gnark E2{A0,A1})
+template <class F>
+struct Ext2 {
+    struct T { typename F::T a0, a1; };
+    G16_HD static T zero() { T r; r.a0 = F::zero(); r.a1 = F::zero(); return r; }
+    G16_HD static T one() { T r; r.a0 = F::one(); r.a1 = F::zero(); return r; }
+    G16_HD static bool is_zero(const T& a) { return F::is_zero(a.a0) && F::is_zero(a.a1); }
+    G16_HD static bool eq(const T& a, const T& b) { return F::eq(a.a0, b.a0) && F::eq(a.a1, b.a1); }
+    G16_HD static T add(const T& a, const T& b) { T r; r.a0 = F::add(a.a0, b.a0); r.a1 = F::add(a.a1, b.a1); return r; }
+    G16_HD static T sub(const T& a, const T& b) { T r; r.a0 = F::sub(a.a0, b.a0); r.a1 = F::sub(a.a1, b.a1); return r; }
+    G16_HD static T dbl(const T& a) { return add(a, a); }
+    G16_HD static T neg(const T& a) { T r; r.a0 = F::neg(a.a0); r.a1 = F::neg(a.a1); return r; }
+    // Karatsuba: 3 base multiplications
+    G16_HD static T mul(const T& a, const T& b) {
+        typename F::T v0 = F::mul(a.a0, b.a0), v1 = F::mul(a.a1, b.a1);
+        typename F::T s = F::mul(F::add(a.a0, a.a1), F::add(b.a0, b.a1));
+        T r;
+        r.a0 = F::sub(v0, v1);
+        r.a1 = F::sub(F::sub(s, v0), v1);
+        return r;
+    }
+    // (a0+a1)(a0-a1) + 2 a0 a1 u : 2 base multiplications
+    G16_HD static T sqr(const T& a) {
+        typename F::T p = F::mul(F::add(a.a0, a.a1), F::sub(a.a0, a.a1));
+        typename F::T q = F::mul(a.a0, a.a1);
+        T r; r.a0 = p; r.a1 = F::dbl(q); return r;
+    }
+    G16_HD static T inv(const T& a) {
+        typename F::T d = F::inv(F::add(F::sqr(a.a0), F::sqr(a.a1)));
+        T r; r.a0 = F::mul(a.a0, d); r.a1 = F::neg(F::mul(a.a1, d)); return r;
+    }
+};
+typedef Ext2<Fp> Fp2;
+
+}  // namespace g16

@@ -1,0 +1,435 @@
+// Pippenger bucket MSM for sm_100a, templated on the curve (G1 over Fp, G2 over Fp2).
+//
+// Replaces iciclegnark.MsmOnDevice / MsmG2OnDevice (backend/groth16/bn254/icicle/icicle.go:302,315,332,
+// 355,382) and mirrors the results of gnark-crypto's G1Jac/G2Jac.MultiExp as the CPU prover calls them
+// (backend/groth16/bn254/prove.go:204,217,237,247,293).  Inputs are gnark memory images: scalars =
+// Montgomery Fr, bases = Montgomery affine with (0,0) = infinity (legal, skipped -- the reference must strip
+// them on the host, icicle.go:98-105,343-347).  The result is handed back in affine form, the only
+// representation that is comparable across implementations.
+//
+// Pipeline (all on one stream, no host synchronisation until the W window sums are read back):
+//   k_digits       from-Montgomery + signed c-bit digit recoding, one biased u16 per (window, scalar)
+//   k_hist         per-(window, point-chunk) shared-memory histogram -> global bucket counts
+//   k_scan         exclusive scan of the W*2^(c-1) counts
+//   k_scatter      in-house counting sort: CTA-aggregated range reservation + shared-memory cursors;
+//                  emits (point index | sign<<31) grouped by (window, bucket)
+//   k_accumulate   balanced segmented reduction: every thread owns S consecutive sorted entries, adds
+//                  them with XYZZ mixed additions, and emits whole buckets directly and at most one
+//                  head and one tail piece -- long buckets are split across threads/warps automatically
+//   k_fixup        stitches head/tail pieces of buckets that span threads; empty buckets -> infinity
+//   k_bucket_reduce / k_window_sum   running-sum reduction sum_b (b+1)*B_b per window, tree-combined
+//   host           Horner over the W window sums (W*c doublings) + one inversion to affine
+#pragma once
+#include "common.cuh"
+
+namespace g16 {
+
+struct MsmWorkspace {
+    DevBuf digits, sorted, counts, offsets, cursor, buckets, head, tail, partial, wsum;
+    PinnedBuf host_wsum;
+    void release() {
+        digits.release(); sorted.release(); counts.release(); offsets.release(); cursor.release();
+        buckets.release(); head.release(); tail.release(); partial.release(); wsum.release(); host_wsum.release();
+    }
+};
+
+struct MsmPlan {
+    int c, W;
+    uint32_t B;        // buckets per window = 2^(c-1)
+    uint32_t NB;       // W * B
+    int red_m, red_rb; // bucket-reduce: buckets per thread, CTAs per window
+};
+
+constexpr int MSM_RED_THREADS = 64;
+
+inline MsmPlan msm_plan(uint64_t n, int force_c, bool g2) {
+    MsmPlan p;
+    int best = 8; double best_cost = 1e300;
+    for (int c = 8; c <= 16; c++) {
+        int W = 255 / c + 1;
+        double madd = g2 ? 30.0 : 10.0, fadd = g2 ? 42.0 : 14.0;
+        double cost = (double)n * W * madd + (double)W * (1u << (c - 1)) * (2.0 * fadd + 3.0 * fadd);
+        if (cost < best_cost) { best_cost = cost; best = c; }
+    }
+    p.c = force_c >= 8 && force_c <= 16 ? force_c : best;
+    p.W = 255 / p.c + 1;
+    p.B = 1u << (p.c - 1);
+    p.NB = p.W * p.B;
+    uint32_t m = p.B / (MSM_RED_THREADS * 32);
+    if (m < 1) m = 1;
+    p.red_m = (int)m;
+    p.red_rb = (int)(p.B / (MSM_RED_THREADS * m));
+    return p;
+}
+
+// ------------------------------------------------------------------ digits
+static __global__ void k_digits(const Fr::T* __restrict__ scalars, const uint32_t* __restrict__ map, uint64_t n,
+                         uint16_t* __restrict__ digits, int c, int W) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint64_t src = map ? map[i] : i;
+    const uint4* q = reinterpret_cast<const uint4*>(scalars + src);
+    uint4 a = __ldg(q), b = __ldg(q + 1);
+    Fr::T s;
+    s.l[0] = a.x; s.l[1] = a.y; s.l[2] = a.z; s.l[3] = a.w; s.l[4] = b.x; s.l[5] = b.y; s.l[6] = b.z; s.l[7] = b.w;
+    s = Fr::from_mont(s);
+    uint32_t l[9];
+#pragma unroll
+    for (int k = 0; k < 8; k++) l[k] = s.l[k];
+    l[8] = 0;
+    const uint32_t mask = (1u << c) - 1, half = 1u << (c - 1);
+    uint32_t carry = 0;
+    for (int w = 0; w < W; w++) {
+        int bit = w * c;
+        uint32_t raw = 0;
+        if (bit < 256) {
+            int limb = bit >> 5, sh = bit & 31;
+            uint64_t two = (uint64_t)l[limb] | ((uint64_t)l[limb + 1] << 32);
+            raw = (uint32_t)(two >> sh) & mask;
+        }
+        raw += carry;
+        // digit d = raw (carry 0) or raw - 2^c (carry 1); stored biased: d + 2^(c-1) in [0, 2^c)
+        if (raw >= half) { carry = 1; raw -= half; } else { carry = 0; raw += half; }
+        digits[(uint64_t)w * n + i] = (uint16_t)raw;
+    }
+}
+
+// decode biased digit -> (bucket index |d|-1, sign); returns false for d == 0
+__device__ __forceinline__ bool decode_digit(uint32_t enc, uint32_t half, uint32_t& bucket, uint32_t& neg) {
+    int d = (int)enc - (int)half;
+    if (d == 0) return false;
+    neg = d < 0 ? 1u : 0u;
+    bucket = (uint32_t)(d < 0 ? -d : d) - 1;
+    return true;
+}
+
+// ------------------------------------------------------------------ counting sort
+static __global__ void k_hist(const uint16_t* __restrict__ digits, uint64_t n, uint32_t* __restrict__ counts, int c, uint64_t per_block) {
+    extern __shared__ uint32_t h[];
+    const uint32_t B = 1u << (c - 1), half = B;
+    const int w = blockIdx.y;
+    for (uint32_t b = threadIdx.x; b < B; b += blockDim.x) h[b] = 0;
+    __syncthreads();
+    uint64_t lo = (uint64_t)blockIdx.x * per_block, hi = lo + per_block;
+    if (hi > n) hi = n;
+    const uint16_t* dg = digits + (uint64_t)w * n;
+    for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+        uint32_t bucket, neg;
+        if (decode_digit(dg[i], half, bucket, neg)) atomicAdd(&h[bucket], 1u);
+    }
+    __syncthreads();
+    uint32_t* cw = counts + (uint64_t)w * B;
+    for (uint32_t b = threadIdx.x; b < B; b += blockDim.x) {
+        uint32_t v = h[b];
+        if (v) atomicAdd(&cw[b], v);
+    }
+}
+
+// single-CTA exclusive scan; offsets has nb+1 entries, cursor (nb) receives a copy of the starts
+static __global__ void k_scan(const uint32_t* __restrict__ counts, uint32_t* __restrict__ offsets, uint32_t* __restrict__ cursor, uint32_t nb) {
+    __shared__ uint32_t part[1024];
+    uint32_t per = (nb + 1023) / 1024;
+    uint32_t lo = threadIdx.x * per, hi = lo + per;
+    if (lo > nb) lo = nb;
+    if (hi > nb) hi = nb;
+    uint32_t s = 0;
+    for (uint32_t i = lo; i < hi; i++) s += counts[i];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    // Hillis-Steele inclusive scan over 1024 partials
+    for (int off = 1; off < 1024; off <<= 1) {
+        uint32_t v = threadIdx.x >= (unsigned)off ? part[threadIdx.x - off] : 0;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    uint32_t run = threadIdx.x ? part[threadIdx.x - 1] : 0;
+    for (uint32_t i = lo; i < hi; i++) { offsets[i] = run; cursor[i] = run; run += counts[i]; }
+    if (threadIdx.x == 1023) offsets[nb] = part[1023];
+}
+
+static __global__ void k_scatter(const uint16_t* __restrict__ digits, uint64_t n, uint32_t* __restrict__ cursor,
+                          uint32_t* __restrict__ sorted, int c, uint64_t per_block) {
+    extern __shared__ uint32_t h[];
+    const uint32_t B = 1u << (c - 1), half = B;
+    const int w = blockIdx.y;
+    for (uint32_t b = threadIdx.x; b < B; b += blockDim.x) h[b] = 0;
+    __syncthreads();
+    uint64_t lo = (uint64_t)blockIdx.x * per_block, hi = lo + per_block;
+    if (hi > n) hi = n;
+    const uint16_t* dg = digits + (uint64_t)w * n;
+    for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+        uint32_t bucket, neg;
+        if (decode_digit(dg[i], half, bucket, neg)) atomicAdd(&h[bucket], 1u);
+    }
+    __syncthreads();
+    uint32_t* cw = cursor + (uint64_t)w * B;
+    for (uint32_t b = threadIdx.x; b < B; b += blockDim.x) {
+        uint32_t v = h[b];
+        if (v) h[b] = atomicAdd(&cw[b], v);   // reserve [base, base+v) of this bucket for this CTA
+    }
+    __syncthreads();
+    for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+        uint32_t bucket, neg;
+        if (decode_digit(dg[i], half, bucket, neg)) {
+            uint32_t pos = atomicAdd(&h[bucket], 1u);
+            sorted[pos] = (uint32_t)i | (neg << 31);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ bucket accumulation
+template <class C>
+__device__ __forceinline__ typename C::Aff load_aff(const typename C::Aff* p) {
+    typename C::Aff r;
+    constexpr int Q = sizeof(typename C::Aff) / 16;
+    const uint4* src = reinterpret_cast<const uint4*>(p);
+    uint4* dst = reinterpret_cast<uint4*>(&r);
+#pragma unroll
+    for (int i = 0; i < Q; i++) dst[i] = __ldg(src + i);
+    return r;
+}
+template <class C>
+__device__ __forceinline__ void store_xyzz(typename C::Xyzz* p, const typename C::Xyzz& v) {
+    constexpr int Q = sizeof(typename C::Xyzz) / 16;
+    const uint4* src = reinterpret_cast<const uint4*>(&v);
+    uint4* dst = reinterpret_cast<uint4*>(p);
+#pragma unroll
+    for (int i = 0; i < Q; i++) dst[i] = src[i];
+}
+template <class C>
+__device__ __forceinline__ typename C::Xyzz load_xyzz(const typename C::Xyzz* p) {
+    typename C::Xyzz r;
+    constexpr int Q = sizeof(typename C::Xyzz) / 16;
+    const uint4* src = reinterpret_cast<const uint4*>(p);
+    uint4* dst = reinterpret_cast<uint4*>(&r);
+#pragma unroll
+    for (int i = 0; i < Q; i++) dst[i] = src[i];
+    return r;
+}
+
+// entries per thread for `total` sorted entries spread over `nthreads` threads (multiple of 4, >= 4)
+__host__ __device__ __forceinline__ uint32_t msm_slice(uint32_t total, uint32_t nthreads) {
+    uint32_t s = (total + nthreads - 1) / nthreads;
+    s = (s + 3u) & ~3u;
+    return s < 4 ? 4 : s;
+}
+
+template <class C, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
+k_accumulate(const typename C::Aff* __restrict__ bases, const uint32_t* __restrict__ sorted,
+             const uint32_t* __restrict__ offsets, uint32_t nb, uint32_t nthreads,
+             typename C::Xyzz* __restrict__ buckets, typename C::Xyzz* __restrict__ head, typename C::Xyzz* __restrict__ tail) {
+    typedef typename C::Xyzz Xyzz;
+    typedef typename C::Aff Aff;
+    const uint32_t t = blockIdx.x * THREADS + threadIdx.x;
+    if (t >= nthreads) return;
+    const uint32_t total = offsets[nb];
+    const uint32_t S = msm_slice(total, nthreads);
+    const uint64_t start64 = (uint64_t)t * S;
+    if (start64 >= total) return;
+    const uint32_t my_start = (uint32_t)start64;
+    const uint32_t my_end = (uint64_t)my_start + S > total ? total : my_start + S;
+
+    // bucket containing my_start: largest gb with offsets[gb] <= my_start and offsets[gb+1] > my_start
+    uint32_t lo = 0, hi = nb;  // invariant: offsets[lo] <= my_start < offsets[hi]
+    while (hi - lo > 1) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (offsets[mid] <= my_start) lo = mid; else hi = mid;
+    }
+    uint32_t gb = lo;
+    uint32_t b_start = offsets[gb], b_end = offsets[gb + 1];
+    uint32_t seg_start = my_start;
+    Xyzz acc = C::inf();
+
+    for (uint32_t p = my_start; p < my_end; p += 4) {
+        uint4 idx4 = *reinterpret_cast<const uint4*>(sorted + p);   // padded allocation: reading past `total` is safe
+        uint32_t idx[4] = {idx4.x, idx4.y, idx4.z, idx4.w};
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            uint32_t pos = p + k;
+            if (pos >= my_end) break;
+            while (pos == b_end) {   // bucket boundary (also steps over empty buckets)
+                if (pos > seg_start) {
+                    if (b_start >= my_start) store_xyzz<C>(buckets + gb, acc);   // bucket lies wholly inside my slice
+                    else store_xyzz<C>(head + t, acc);                           // started in an earlier slice
+                    acc = C::inf();
+                    seg_start = pos;
+                }
+                gb++;
+                b_start = b_end;
+                b_end = offsets[gb + 1];
+            }
+            Aff pt = load_aff<C>(bases + (idx[k] & 0x7fffffffu));
+            if (idx[k] >> 31) pt = C::neg(pt);
+            C::madd(acc, pt);
+        }
+    }
+    // final piece [seg_start, my_end) of bucket gb
+    if (my_end > seg_start) {
+        bool starts_inside = b_start >= my_start, ends_inside = b_end <= my_end;
+        if (starts_inside && ends_inside) store_xyzz<C>(buckets + gb, acc);
+        else if (seg_start == my_start) store_xyzz<C>(head + t, acc);
+        else store_xyzz<C>(tail + t, acc);
+    }
+}
+
+template <class C>
+__global__ void k_fixup(const uint32_t* __restrict__ offsets, uint32_t nb, uint32_t nthreads,
+                        typename C::Xyzz* __restrict__ buckets, const typename C::Xyzz* __restrict__ head,
+                        const typename C::Xyzz* __restrict__ tail) {
+    typedef typename C::Xyzz Xyzz;
+    uint32_t gb = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gb >= nb) return;
+    const uint32_t total = offsets[nb];
+    const uint32_t S = msm_slice(total, nthreads);
+    uint32_t start = offsets[gb], end = offsets[gb + 1];
+    if (start == end) { store_xyzz<C>(buckets + gb, C::inf()); return; }
+    uint32_t t0 = start / S, t1 = (end - 1) / S;
+    if (t0 == t1) return;   // written directly by k_accumulate
+    Xyzz acc = (start == t0 * S) ? load_xyzz<C>(head + t0) : load_xyzz<C>(tail + t0);
+    for (uint32_t t = t0 + 1; t <= t1; t++) C::add(acc, load_xyzz<C>(head + t));
+    store_xyzz<C>(buckets + gb, acc);
+}
+
+// ------------------------------------------------------------------ bucket reduction
+// grid (red_rb, W); thread handles m consecutive buckets; CTA result -> partial[w * red_rb + blockIdx.x]
+template <class C>
+__global__ void __launch_bounds__(MSM_RED_THREADS)
+k_bucket_reduce(const typename C::Xyzz* __restrict__ buckets, uint32_t B, int m, typename C::Xyzz* __restrict__ partial) {
+    typedef typename C::Xyzz Xyzz;
+    __shared__ Xyzz sm[MSM_RED_THREADS];
+    const int w = blockIdx.y;
+    const uint32_t chunk = blockIdx.x * MSM_RED_THREADS + threadIdx.x;
+    const uint32_t b0 = chunk * (uint32_t)m;
+    const Xyzz* bw = buckets + (uint64_t)w * B;
+    Xyzz run = C::inf(), ws = C::inf();
+    for (int k = m - 1; k >= 0; k--) {
+        C::add(run, load_xyzz<C>(bw + b0 + k));
+        C::add(ws, run);
+    }
+    // + b0 * run  (weights are b+1; the running sums above cover (b - b0 + 1))
+    if (b0) {
+        uint32_t kk[1] = {b0};
+        Xyzz t = C::mul(run, kk, 1);
+        C::add(ws, t);
+    }
+    sm[threadIdx.x] = ws;
+    __syncthreads();
+    for (int stride = MSM_RED_THREADS / 2; stride >= 1; stride >>= 1) {
+        if ((int)threadIdx.x < stride) { Xyzz a = sm[threadIdx.x]; C::add(a, sm[threadIdx.x + stride]); sm[threadIdx.x] = a; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) store_xyzz<C>(partial + (uint64_t)w * gridDim.x + blockIdx.x, sm[0]);
+}
+
+// grid W, 32 threads: sum the rb partials of a window
+template <class C>
+__global__ void __launch_bounds__(32) k_window_sum(const typename C::Xyzz* __restrict__ partial, int rb, typename C::Xyzz* __restrict__ wsum) {
+    typedef typename C::Xyzz Xyzz;
+    __shared__ Xyzz sm[32];
+    const int w = blockIdx.x;
+    sm[threadIdx.x] = (int)threadIdx.x < rb ? load_xyzz<C>(partial + (uint64_t)w * rb + threadIdx.x) : C::inf();
+    __syncwarp();
+    for (int stride = 16; stride >= 1; stride >>= 1) {
+        if ((int)threadIdx.x < stride) { Xyzz a = sm[threadIdx.x]; C::add(a, sm[threadIdx.x + stride]); sm[threadIdx.x] = a; }
+        __syncwarp();
+    }
+    if (threadIdx.x == 0) store_xyzz<C>(wsum + w, sm[0]);
+}
+
+// ------------------------------------------------------------------ host driver
+struct MsmStats { int c = 0, W = 0; uint32_t acc_threads = 0; };
+
+// Enqueues the whole MSM on `st`; window sums land in ws.host_wsum (pinned) after the stream drains.
+template <class C, int ACC_THREADS, int ACC_MINB>
+void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const typename C::Aff* bases_d,
+                 uint64_t n, int force_c, int waves, cudaStream_t st, MsmPlan& plan_out, MsmStats* stats) {
+    typedef typename C::Xyzz Xyzz;
+    constexpr bool IS_G2 = sizeof(typename C::Aff) > 64;
+    MsmPlan pl = msm_plan(n, force_c, IS_G2);
+    plan_out = pl;
+    if (stats) { stats->c = pl.c; stats->W = pl.W; stats->acc_threads = 0; }
+    if (n == 0) return;   // callers treat an empty MSM as infinity (icicle.go:330-333)
+    if ((uint64_t)n * pl.W >= 0xfffffff0ull || n >= 0x7fffffffull) throw std::runtime_error("MSM too large for 32-bit entry indices");
+    const uint32_t total_max = (uint32_t)(n * pl.W);
+
+    int dev = 0, sms = 0;
+    G16_CUDA(cudaGetDevice(&dev));
+    G16_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    int occ = 0;
+    G16_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_accumulate<C, ACC_THREADS, ACC_MINB>, ACC_THREADS, 0));
+    if (occ < 1) occ = 1;
+    uint32_t nthreads = (uint32_t)sms * occ * ACC_THREADS * (waves > 0 ? waves : 2);
+    uint32_t cap = (total_max + 3) / 4;
+    if (nthreads > cap) nthreads = cap < 1 ? 1 : cap;
+
+    ws.digits.reserve((size_t)n * pl.W * sizeof(uint16_t) + 64);
+    ws.sorted.reserve((size_t)total_max * sizeof(uint32_t) + 64);
+    ws.counts.reserve((size_t)pl.NB * 4);
+    ws.offsets.reserve((size_t)(pl.NB + 1) * 4);
+    ws.cursor.reserve((size_t)pl.NB * 4);
+    ws.buckets.reserve((size_t)pl.NB * sizeof(Xyzz));
+    ws.head.reserve((size_t)nthreads * sizeof(Xyzz));
+    ws.tail.reserve((size_t)nthreads * sizeof(Xyzz));
+    ws.partial.reserve((size_t)pl.W * pl.red_rb * sizeof(Xyzz));
+    ws.wsum.reserve((size_t)pl.W * sizeof(Xyzz));
+    ws.host_wsum.reserve((size_t)pl.W * sizeof(Xyzz));
+
+    uint16_t* digits = ws.digits.as<uint16_t>();
+    uint32_t* sorted = ws.sorted.as<uint32_t>();
+    uint32_t* counts = ws.counts.as<uint32_t>();
+    uint32_t* offsets = ws.offsets.as<uint32_t>();
+    uint32_t* cursor = ws.cursor.as<uint32_t>();
+    Xyzz* buckets = ws.buckets.as<Xyzz>();
+
+    k_digits<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(scalars_d, map_d, n, digits, pl.c, pl.W);
+    G16_LAUNCH_CHECK();
+    G16_CUDA(cudaMemsetAsync(counts, 0, (size_t)pl.NB * 4, st));
+
+    // (window, point-chunk) CTAs; enough chunks to fill the machine a few times over
+    size_t hsmem = (size_t)pl.B * 4;
+    uint32_t chunks = (uint32_t)((sms * 4 + pl.W - 1) / pl.W);
+    uint64_t per_block = (n + chunks - 1) / chunks;
+    if (per_block < 1024) per_block = 1024;
+    chunks = (uint32_t)((n + per_block - 1) / per_block);
+    if (hsmem > 48 * 1024) {
+        G16_CUDA(cudaFuncSetAttribute(k_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsmem));
+        G16_CUDA(cudaFuncSetAttribute(k_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsmem));
+    }
+    dim3 hgrid(chunks, pl.W);
+    k_hist<<<hgrid, 1024, hsmem, st>>>(digits, n, counts, pl.c, per_block);
+    G16_LAUNCH_CHECK();
+    k_scan<<<1, 1024, 0, st>>>(counts, offsets, cursor, pl.NB);
+    G16_LAUNCH_CHECK();
+    k_scatter<<<hgrid, 1024, hsmem, st>>>(digits, n, cursor, sorted, pl.c, per_block);
+    G16_LAUNCH_CHECK();
+
+    k_accumulate<C, ACC_THREADS, ACC_MINB><<<(nthreads + ACC_THREADS - 1) / ACC_THREADS, ACC_THREADS, 0, st>>>(
+        bases_d, sorted, offsets, pl.NB, nthreads, buckets, ws.head.as<Xyzz>(), ws.tail.as<Xyzz>());
+    G16_LAUNCH_CHECK();
+    k_fixup<C><<<(pl.NB + 127) / 128, 128, 0, st>>>(offsets, pl.NB, nthreads, buckets, ws.head.as<Xyzz>(), ws.tail.as<Xyzz>());
+    G16_LAUNCH_CHECK();
+    dim3 rgrid(pl.red_rb, pl.W);
+    k_bucket_reduce<C><<<rgrid, MSM_RED_THREADS, 0, st>>>(buckets, pl.B, pl.red_m, ws.partial.as<Xyzz>());
+    G16_LAUNCH_CHECK();
+    k_window_sum<C><<<pl.W, 32, 0, st>>>(ws.partial.as<Xyzz>(), pl.red_rb, ws.wsum.as<Xyzz>());
+    G16_LAUNCH_CHECK();
+    G16_CUDA(cudaMemcpyAsync(ws.host_wsum.p, ws.wsum.p, (size_t)pl.W * sizeof(Xyzz), cudaMemcpyDeviceToHost, st));
+    if (stats) { stats->c = pl.c; stats->W = pl.W; stats->acc_threads = nthreads; }
+}
+
+// Horner over the window sums (host, O(W*c) group operations) -> affine
+template <class C>
+typename C::Aff msm_finish(const MsmWorkspace& ws, const MsmPlan& pl) {
+    typedef typename C::Xyzz Xyzz;
+    const Xyzz* wsum = ws.host_wsum.as<Xyzz>();
+    Xyzz acc = C::inf();
+    for (int w = pl.W - 1; w >= 0; w--) {
+        for (int i = 0; i < pl.c; i++) acc = C::dbl(acc);
+        C::add(acc, wsum[w]);
+    }
+    return C::to_aff(acc);
+}
+
+}  // namespace g16

@@ -1,0 +1,23 @@
+// Non-template entry points of the MSM translation units (msm_g1.cu, msm_g2.cu).
+#pragma once
+#include "msm.cuh"
+
+namespace g16 {
+
+void msm_g1_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const G1::Aff* bases_d, uint64_t n,
+                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats);
+G1::Aff msm_g1_finish(const MsmWorkspace& ws, const MsmPlan& plan);
+void msm_g2_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const G2::Aff* bases_d, uint64_t n,
+                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats);
+G2::Aff msm_g2_finish(const MsmWorkspace& ws, const MsmPlan& plan);
+
+// out[i] = [scalars[i]] * G (generator), affine Montgomery.  Setup-side tooling: the device analogue of
+// curve.BatchScalarMultiplicationG1/G2 (backend/groth16/bn254/setup.go:251,320) used to materialise
+// synthetic proving keys at BASELINE sizes.  `table_d` caches the window table between calls.
+void fixed_base_g1(DevBuf& table_d, const Fr::T* scalars_d, uint64_t n, G1::Aff* out_d, cudaStream_t st);
+void fixed_base_g2(DevBuf& table_d, const Fr::T* scalars_d, uint64_t n, G2::Aff* out_d, cudaStream_t st);
+
+G1::Aff g1_generator();
+G2::Aff g2_generator();
+
+}  // namespace g16

@@ -1,0 +1,23 @@
+// G1 instantiation of the Pippenger pipeline (see msm.cuh).
+#include "msm_api.cuh"
+#include "fixed_base.cuh"
+
+namespace g16 {
+
+void msm_g1_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const G1::Aff* bases_d, uint64_t n,
+                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats) {
+    msm_enqueue<G1, 128, 4>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats);
+}
+G1::Aff msm_g1_finish(const MsmWorkspace& ws, const MsmPlan& plan) { return msm_finish<G1>(ws, plan); }
+
+G1::Aff g1_generator() {
+    G1::Aff g;
+    g.x = Fp::one();
+    g.y = Fp::add(Fp::one(), Fp::one());
+    return g;
+}
+void fixed_base_g1(DevBuf& table_d, const Fr::T* scalars_d, uint64_t n, G1::Aff* out_d, cudaStream_t st) {
+    fixed_base_run<G1, Fp>(table_d, g1_generator(), scalars_d, n, out_d, st);
+}
+
+}  // namespace g16

@@ -1,0 +1,303 @@
+// Fr NTT kernels and the computeH pipeline for sm_100a.
+//
+// Replaces, on the reference's accelerated path (backend/groth16/bn254/icicle/icicle.go):
+//   :68,73   GenerateTwiddleFactors        -> NttDomain::table (per-stage twiddles, coset shift folded in)
+//   :489     INttOnDevice(.., false) x3    -> ntt_dif(TW_INV)           (1/n folded into the pointwise step)
+//   :490     NttOnDevice(.., coset) x3     -> ntt_dit(TW_COSET_FWD)     (no CosetTable sweep)
+//   :500     PolyOps                       -> fr_pointwise_h            (one fused kernel, scalar den)
+//   :502     INttOnDevice(.., coset)       -> ntt_dif(TW_COSET_INV)     (no CosetTableInv sweep)
+//   :510     ReverseScalars                -> eliminated: DIF output *is* the bit-reversed order pk.G1.Z uses
+// and mirrors the CPU semantics of backend/groth16/bn254/prove.go:356-399 (fft.Domain DIF/DIT).
+//
+// Kernel shape: one CTA stages a tile of 2^k rows x 2^cb columns (row stride 2^s elements) in shared
+// memory as two 128-bit planes, runs k radix-2 stages on it and writes it back; a size-n transform is
+// ceil(log n / k) such sweeps.  32-byte elements are read and written as 2 x 128-bit accesses.
+#include "ntt.cuh"
+#include <cstdlib>
+
+namespace g16 {
+
+static const uint32_t ROOT_2_28[8] = {0x725b19f0u, 0x9bd61b6eu, 0x41112ed4u, 0x402d111eu, 0x8ef62abcu, 0x00e0a7ebu, 0xa58a7e85u, 0x2a3c09f0u};
+
+int ntt_log_tile() {
+    static int v = [] { const char* e = getenv("G16_NTT_LOG_TILE"); int x = e ? atoi(e) : 10; return x < 4 ? 4 : (x > 12 ? 12 : x); }();
+    return v;
+}
+int ntt_log_cols() {
+    static int v = [] { const char* e = getenv("G16_NTT_LOG_COLS"); int x = e ? atoi(e) : 1; return x < 0 ? 0 : (x > 3 ? 3 : x); }();
+    return v;
+}
+
+// ------------------------------------------------------------------ twiddle tables
+struct StageParams {
+    Fr::T root[28];   // per stage s: multiplicative step
+    Fr::T shift[28];  // per stage s: constant factor
+};
+
+__global__ void k_build_table(Fr::T* out, uint64_t n, StageParams sp) {
+    // thread t fills E = e+1 in [8t, 8t+8); stage s = floor(log2 E), j = E - 2^s
+    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t E0 = t * 8;
+    if (E0 >= n) return;
+    Fr::T val = Fr::zero();
+    bool have = false;
+    for (int i = 0; i < 8; i++) {
+        uint64_t E = E0 + i;
+        if (E == 0 || E >= n) continue;
+        int s = 63 - __clzll((long long)E);
+        uint64_t j = E - (1ull << s);
+        if (!have || j == 0) {
+            val = Fr::mul(sp.shift[s], Fr::pow_u64(sp.root[s], j));
+            have = true;
+        } else {
+            val = Fr::mul(val, sp.root[s]);
+        }
+        out[E - 1] = val;
+    }
+}
+
+void NttDomain::init(int logn_) {
+    logn = logn_;
+    n = 1ull << logn;
+    if (logn > 28) throw std::runtime_error("NTT domain larger than 2^28 (Fr two-adicity)");
+    Fr::T root; memcpy(root.l, ROOT_2_28, 32);
+    root = Fr::to_mont(root);
+    for (int i = logn; i < 28; i++) root = Fr::sqr(root);
+    omega = root;
+    omega_inv = Fr::inv(root);
+    coset_gen = Fr::from_u64(5);
+    coset_inv = Fr::inv(coset_gen);
+    n_inv = Fr::inv(Fr::from_u64(n));
+    Fr::T gn = Fr::pow_u64(coset_gen, n);
+    Fr::T den = Fr::inv(Fr::sub(gn, Fr::one()));
+    h_c1 = n_inv;
+    h_c2 = Fr::mul(den, Fr::sqr(n_inv));
+}
+
+const Fr::T* NttDomain::table(NttTable t, cudaStream_t st) {
+    if (tw[t]) return tw[t];
+    if (logn == 0) { G16_CUDA(cudaMalloc(&tw[t], 32)); return tw[t]; }
+    StageParams sp;
+    Fr::T w = (t == TW_FWD || t == TW_COSET_FWD) ? omega : omega_inv;
+    Fr::T g = (t == TW_COSET_FWD) ? coset_gen : (t == TW_COSET_INV ? coset_inv : Fr::one());
+    // stage s = logn-1 uses w and g; each lower stage squares both
+    for (int s = logn - 1; s >= 0; s--) {
+        sp.root[s] = w; sp.shift[s] = g;
+        w = Fr::sqr(w); g = Fr::sqr(g);
+    }
+    for (int s = logn; s < 28; s++) { sp.root[s] = Fr::one(); sp.shift[s] = Fr::one(); }
+    Fr::T* p = nullptr;
+    G16_CUDA(cudaMalloc(&p, (size_t)n * sizeof(Fr::T)));
+    uint64_t threads = (n + 7) / 8;
+    k_build_table<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(p, n, sp);
+    G16_LAUNCH_CHECK();
+    tw[t] = p;
+    return p;
+}
+
+void NttDomain::release() {
+    for (int i = 0; i < 4; i++) { if (tw[i]) cudaFree(tw[i]); tw[i] = nullptr; }
+}
+
+// ------------------------------------------------------------------ butterfly sweeps
+struct PassArgs {
+    Fr::T* p[3];
+    const Fr::T* tw;
+    int s;   // log2 of the row stride (= log2 of the smallest half-size handled by this sweep)
+    int k;   // stages in this sweep (tile rows = 2^k)
+    int cb;  // log2 of tile columns
+};
+
+__device__ __forceinline__ Fr::T ld_planes(const uint4* lo, const uint4* hi, int e) {
+    Fr::T r; uint4 a = lo[e], b = hi[e];
+    r.l[0] = a.x; r.l[1] = a.y; r.l[2] = a.z; r.l[3] = a.w; r.l[4] = b.x; r.l[5] = b.y; r.l[6] = b.z; r.l[7] = b.w;
+    return r;
+}
+__device__ __forceinline__ void st_planes(uint4* lo, uint4* hi, int e, const Fr::T& v) {
+    lo[e] = make_uint4(v.l[0], v.l[1], v.l[2], v.l[3]);
+    hi[e] = make_uint4(v.l[4], v.l[5], v.l[6], v.l[7]);
+}
+__device__ __forceinline__ Fr::T ldg_fr(const Fr::T* p) {
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    uint4 a = __ldg(q), b = __ldg(q + 1);
+    Fr::T r;
+    r.l[0] = a.x; r.l[1] = a.y; r.l[2] = a.z; r.l[3] = a.w; r.l[4] = b.x; r.l[5] = b.y; r.l[6] = b.z; r.l[7] = b.w;
+    return r;
+}
+
+constexpr int NTT_THREADS = 256;
+
+template <bool DIF>
+__global__ void __launch_bounds__(NTT_THREADS) k_ntt_pass(PassArgs a) {
+    extern __shared__ uint4 sm[];
+    const int T = 1 << (a.k + a.cb);
+    uint4* lo = sm;
+    uint4* hi = sm + T;
+    Fr::T* data = a.p[blockIdx.y];
+    const int s = a.s, k = a.k, cb = a.cb;
+    const int cmask = (1 << cb) - 1;
+    const uint64_t qbase = (uint64_t)blockIdx.x << cb;
+    const uint64_t smask = (1ull << s) - 1;
+
+    for (int e = threadIdx.x; e < T; e += NTT_THREADS) {
+        int c = e & cmask, r = e >> cb;
+        uint64_t q = qbase + c;
+        uint64_t gi = ((q >> s) << (s + k)) | ((uint64_t)r << s) | (q & smask);
+        const uint4* src = reinterpret_cast<const uint4*>(data + gi);
+        lo[e] = src[0];
+        hi[e] = src[1];
+    }
+    __syncthreads();
+
+    const int nb = T >> 1;
+    for (int st = 0; st < k; st++) {
+        const int m = DIF ? (k - 1 - st) : st;
+        const int mmask = (1 << m) - 1;
+        const Fr::T* tws = a.tw + ((1ull << (m + s)) - 1);
+        for (int bi = threadIdx.x; bi < nb; bi += NTT_THREADS) {
+            int c = bi & cmask, rb = bi >> cb;
+            int r0 = ((rb >> m) << (m + 1)) | (rb & mmask);
+            int e0 = (r0 << cb) | c;
+            int e1 = e0 + (1 << (m + cb));
+            uint64_t q = qbase + c;
+            uint64_t j = ((uint64_t)(r0 & mmask) << s) | (q & smask);
+            Fr::T t = ldg_fr(tws + j);
+            Fr::T u = ld_planes(lo, hi, e0), v = ld_planes(lo, hi, e1);
+            if (DIF) {
+                st_planes(lo, hi, e0, Fr::add(u, v));
+                st_planes(lo, hi, e1, Fr::mul(Fr::sub(u, v), t));
+            } else {
+                v = Fr::mul(v, t);
+                st_planes(lo, hi, e0, Fr::add(u, v));
+                st_planes(lo, hi, e1, Fr::sub(u, v));
+            }
+        }
+        __syncthreads();
+    }
+
+    for (int e = threadIdx.x; e < T; e += NTT_THREADS) {
+        int c = e & cmask, r = e >> cb;
+        uint64_t q = qbase + c;
+        uint64_t gi = ((q >> s) << (s + k)) | ((uint64_t)r << s) | (q & smask);
+        uint4* dst = reinterpret_cast<uint4*>(data + gi);
+        dst[0] = lo[e];
+        dst[1] = hi[e];
+    }
+}
+
+struct Sweep { int s, k, cb; };
+
+static std::vector<Sweep> plan_sweeps(int logn) {
+    std::vector<Sweep> v;
+    if (logn == 0) return v;
+    const int LT = ntt_log_tile();
+    int k0 = logn < LT ? logn : LT;
+    int rem = logn - k0;
+    if (rem == 0) { v.push_back({0, k0, 0}); return v; }
+    int cb = ntt_log_cols();
+    int kmax = LT - cb;
+    int np = (rem + kmax - 1) / kmax;
+    // balance: spread all logn stages over np+1 sweeps, contiguous sweep may take up to LT
+    int total = np + 1;
+    int base = logn / total, extra = logn % total;
+    std::vector<int> ks(total, base);
+    for (int i = 0; i < extra; i++) ks[i]++;
+    // the contiguous sweep (index 0) may be as large as LT; strided ones at most kmax
+    for (int i = 1; i < total; i++) while (ks[i] > kmax) { ks[i]--; ks[0]++; }
+    int s = 0;
+    for (int i = 0; i < total; i++) {
+        int c = (i == 0) ? 0 : cb;
+        if (c > s) c = s;                       // keep a tile row contiguous in memory
+        while (ks[i] + c > LT) c--;
+        v.push_back({s, ks[i], c});
+        s += ks[i];
+    }
+    return v;
+}
+
+template <bool DIF>
+static void launch_sweep(NttDomain& d, const NttBatch& b, const Fr::T* tw, const Sweep& sw, cudaStream_t st) {
+    PassArgs a;
+    for (int i = 0; i < 3; i++) a.p[i] = b.p[i < b.count ? i : 0];
+    a.tw = tw; a.s = sw.s; a.k = sw.k; a.cb = sw.cb;
+    size_t smem = (size_t)2 * sizeof(uint4) << (sw.k + sw.cb);
+    if (smem > 48 * 1024)
+        G16_CUDA(cudaFuncSetAttribute(k_ntt_pass<DIF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    uint64_t gx = (d.n >> sw.k) >> sw.cb;
+    dim3 grid((unsigned)gx, (unsigned)b.count);
+    k_ntt_pass<DIF><<<grid, NTT_THREADS, smem, st>>>(a);
+    G16_LAUNCH_CHECK();
+}
+
+void ntt_dif(NttDomain& d, const NttBatch& b, NttTable t, cudaStream_t st) {
+    if (d.logn == 0) return;
+    const Fr::T* tw = d.table(t, st);
+    std::vector<Sweep> v = plan_sweeps(d.logn);
+    for (int i = (int)v.size() - 1; i >= 0; i--) launch_sweep<true>(d, b, tw, v[i], st);
+}
+void ntt_dit(NttDomain& d, const NttBatch& b, NttTable t, cudaStream_t st) {
+    if (d.logn == 0) return;
+    const Fr::T* tw = d.table(t, st);
+    std::vector<Sweep> v = plan_sweeps(d.logn);
+    for (size_t i = 0; i < v.size(); i++) launch_sweep<false>(d, b, tw, v[i], st);
+}
+
+// ------------------------------------------------------------------ element-wise kernels
+__global__ void k_scale_powers(Fr::T* a, uint64_t n, int logn, Fr::T c, Fr::T base, int bitrev_index, int use_base) {
+    // thread handles 16 consecutive exponents
+    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t i0 = t * 16;
+    if (i0 >= n) return;
+    Fr::T p = c;
+    if (use_base) p = Fr::mul(c, Fr::pow_u64(base, i0));
+    for (int k = 0; k < 16 && i0 + k < n; k++) {
+        uint64_t i = i0 + k;
+        uint64_t pos = bitrev_index ? (__brevll(i) >> (64 - logn)) : i;
+        if (logn == 0) pos = 0;
+        a[pos] = Fr::mul(a[pos], p);
+        if (use_base) p = Fr::mul(p, base);
+    }
+}
+void fr_scale_powers(Fr::T* a, uint64_t n, int logn, const Fr::T& c, const Fr::T& base, int bitrev_index, int use_base, cudaStream_t st) {
+    uint64_t threads = (n + 15) / 16;
+    k_scale_powers<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(a, n, logn, c, base, bitrev_index, use_base);
+    G16_LAUNCH_CHECK();
+}
+
+__global__ void k_pointwise_h(Fr::T* a, const Fr::T* b, const Fr::T* c, uint64_t n, Fr::T c1, Fr::T c2) {
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        Fr::T x = ldg_fr(a + i), y = ldg_fr(b + i), z = ldg_fr(c + i);
+        Fr::T t = Fr::mul(Fr::mul(x, y), c1);
+        a[i] = Fr::mul(Fr::sub(t, z), c2);
+    }
+}
+void fr_pointwise_h(Fr::T* a, const Fr::T* b, const Fr::T* c, uint64_t n, const Fr::T& c1, const Fr::T& c2, cudaStream_t st) {
+    unsigned blocks = (unsigned)((n + 255) / 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    k_pointwise_h<<<blocks, 256, 0, st>>>(a, b, c, n, c1, c2);
+    G16_LAUNCH_CHECK();
+}
+
+__global__ void k_mul_vec(Fr::T* out, const Fr::T* a, const Fr::T* b, uint64_t n) {
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+        out[i] = Fr::mul(ldg_fr(a + i), ldg_fr(b + i));
+}
+void fr_mul_vec(Fr::T* out, const Fr::T* a, const Fr::T* b, uint64_t n, cudaStream_t st) {
+    if (!n) return;
+    unsigned blocks = (unsigned)((n + 255) / 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    k_mul_vec<<<blocks, 256, 0, st>>>(out, a, b, n);
+    G16_LAUNCH_CHECK();
+}
+
+// ------------------------------------------------------------------ computeH (prove.go:356-399 / icicle.go:453-513)
+void compute_h_device(NttDomain& d, Fr::T* a, Fr::T* b, Fr::T* c, cudaStream_t st) {
+    NttBatch abc{{a, b, c}, 3};
+    ntt_dif(d, abc, TW_INV, st);          // n * coefficients, bit-reversed
+    ntt_dit(d, abc, TW_COSET_FWD, st);    // n * evaluations on g<w>, natural order
+    fr_pointwise_h(a, b, c, d.n, d.h_c1, d.h_c2, st);
+    NttBatch one{{a, a, a}, 1};
+    ntt_dif(d, one, TW_COSET_INV, st);    // h coefficients, bit-reversed order
+}
+
+}  // namespace g16

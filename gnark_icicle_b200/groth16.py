@@ -1,0 +1,179 @@
+"""Host-side mirror of package ``icicle_bn254`` (reference: backend/groth16/bn254/icicle/{icicle.go,
+provingkey.go,noicicle.go}) above the libg16b200 C ABI.
+
+The reference's host language is Go; no Go toolchain exists on the build or GPU machines, so this mirror is
+Python (the Go shim a maintainer would use is go/icicle_bn254/ + INTEGRATION.md).  Names and argument
+meaning follow the reference:
+
+  HasIcicle                                  icicle.go:29
+  ProvingKey{ProvingKey; *deviceInfo}        icicle/provingkey.go:25-28   -> ProvingKey (+ .device)
+  (pk *ProvingKey) setupDevicePointers()     icicle.go:31-130             -> ProvingKey.setup_device_pointers
+  Prove(r1cs, pk, fullWitness, opts...)      icicle.go:133-422            -> Prove
+  backend.WithIcicleAcceleration()           backend/backend.go:142-147   -> WithIcicleAcceleration
+
+Differences that are deliberate: r, s can be injected (the reference hard-codes SetRandom at
+icicle.go:283-288, which makes byte-exact comparison impossible); BSB22 commitments are not supported
+ and raise.
+"""
+import secrets
+from dataclasses import dataclass, field as _field
+
+import numpy as np
+
+from . import lib as _lib
+
+HasIcicle = True
+_FR_MOD = 21888242871839275222246405745257275088548364400416034343698204186575808495617
+
+
+# ---- backend.ProverOption (backend/backend.go:66-147)
+@dataclass
+class ProverConfig:
+    accelerator: str = ""
+    r: object = None          # injected randomness (Fr limbs, Montgomery); None = sample
+    s: object = None
+    device: int = 0
+    shard_index: int = 0
+    shard_count: int = 1
+
+
+def WithIcicleAcceleration():
+    def opt(cfg):
+        cfg.accelerator = "icicle"
+    return opt
+
+
+def WithRandomness(r, s):
+    def opt(cfg):
+        cfg.r, cfg.s = r, s
+    return opt
+
+
+def WithDevice(device, shard_index=0, shard_count=1):
+    def opt(cfg):
+        cfg.device, cfg.shard_index, cfg.shard_count = device, shard_index, shard_count
+    return opt
+
+
+def NewProverConfig(*opts):
+    cfg = ProverConfig()
+    for o in opts:
+        o(cfg)
+    return cfg
+
+
+# ---- data crossing the boundary
+@dataclass
+class R1CSSolution:
+    """constraint/bn254/system.go:221-224: W (all wires) and A, B, C (L.w, R.w, O.w per constraint)."""
+    W: np.ndarray
+    A: np.ndarray
+    B: np.ndarray
+    C: np.ndarray
+
+
+@dataclass
+class Proof:
+    """prove.go:44-49 (no commitments): raw gnark memory images."""
+    Ar: np.ndarray    # (8,)  G1Affine
+    Bs: np.ndarray    # (16,) G2Affine
+    Krs: np.ndarray   # (8,)  G1Affine
+
+    def raw(self):
+        return np.concatenate([self.Ar, self.Bs, self.Krs]).tobytes()
+
+
+@dataclass
+class ProvingKey:
+    """setup.go:35-58 fields that feed the prover, as numpy limb arrays, plus the device info."""
+    domain_n: int
+    g1_alpha: np.ndarray
+    g1_beta: np.ndarray
+    g1_delta: np.ndarray
+    g1_a: np.ndarray
+    g1_b: np.ndarray
+    g1_z: np.ndarray
+    g1_k: np.ndarray
+    g2_beta: np.ndarray
+    g2_delta: np.ndarray
+    g2_b: np.ndarray
+    infinity_a: np.ndarray
+    infinity_b: np.ndarray
+    nb_wires: int
+    nb_public: int
+    commitment_keys: list = _field(default_factory=list)
+    device: object = None     # deviceInfo (provingkey.go:10-23): (Context, handle)
+
+    def setup_device_pointers(self, cfg=None):
+        """icicle.go:31-130: one-time upload; lazily on first Prove (icicle.go:145-150)."""
+        if self.device is not None:
+            return
+        cfg = cfg or ProverConfig()
+        ctx = _lib.Context(cfg.device)
+        handle = ctx.pk_upload(self.domain_n, self.g1_a, self.g1_b, self.g1_k, self.g1_z, self.g2_b,
+                               self.infinity_a, self.infinity_b, self.nb_wires,
+                               shard_index=cfg.shard_index, shard_count=cfg.shard_count)
+        self.device = (ctx, handle)
+
+    def pk_points(self):
+        return np.concatenate([self.g1_alpha.reshape(-1), self.g1_beta.reshape(-1), self.g1_delta.reshape(-1),
+                               self.g2_beta.reshape(-1), self.g2_delta.reshape(-1)]).astype(np.uint64)
+
+    def free_device(self):
+        if self.device is not None:
+            ctx, handle = self.device
+            ctx.pk_free(handle)
+            ctx.close()
+            self.device = None
+
+
+def _random_fr():
+    v = secrets.randbelow(_FR_MOD)
+    return np.array([(v >> (64 * i)) & 0xFFFFFFFFFFFFFFFF for i in range(4)], dtype=np.uint64)
+
+
+def prove_msms(pk, sol, cfg=None):
+    """Device section of Prove (icicle.go:204-410): returns (48 limbs = 5 raw MSM points, stats)."""
+    pk.setup_device_pointers(cfg)
+    ctx, handle = pk.device
+    return ctx.prove(handle, sol.W, sol.A, sol.B, sol.C)
+
+
+def Prove(r1cs, pk, full_witness, *opts):
+    """icicle_bn254.Prove (icicle.go:133-422).
+
+    ``r1cs`` must offer ``solve(full_witness) -> R1CSSolution`` (constraint/bn254/system.go:65; the solver
+    is host code outside the accelerated path) -- or pass ``r1cs=None`` and an R1CSSolution as the witness.
+    Without WithIcicleAcceleration() the reference falls back to the CPU prover (icicle.go:141-143); this
+    package has no CPU prover, so that is an error here.
+    """
+    cfg = NewProverConfig(*opts)
+    if cfg.accelerator != "icicle":
+        raise _lib.G16Error("accelerator option missing: pass WithIcicleAcceleration() "
+                            "(the CPU prover lives in gnark, not in this package)")
+    if pk.commitment_keys:
+        raise NotImplementedError("BSB22 commitments are outside this round's scope (SURVEY.md 8(f) N3)")
+    sol = full_witness if r1cs is None else r1cs.solve(full_witness)
+    points, stats = prove_msms(pk, sol, cfg)
+    r = cfg.r if cfg.r is not None else _random_fr()
+    s = cfg.s if cfg.s is not None else _random_fr()
+    proof = assemble(pk, points, r, s)
+    proof.stats = stats
+    return proof
+
+
+def assemble(pk, msm_points, r, s):
+    """host epilogue (icicle.go:281-295,306-307,319-321,362-372,386-391) on already-combined MSM points."""
+    out = _lib.assemble_proof(pk.pk_points(), r, s, msm_points)
+    return Proof(Ar=out[0:8].copy(), Bs=out[8:24].copy(), Krs=out[24:32].copy())
+
+
+def combine_shards(point_blocks):
+    """Sum the per-shard raw MSM blocks (each 48 limbs) of a point-range-sharded prove."""
+    acc = np.array(point_blocks[0], dtype=np.uint64).copy()
+    for blk in point_blocks[1:]:
+        blk = np.asarray(blk, dtype=np.uint64)
+        for i in range(4):
+            acc[8 * i:8 * i + 8] = _lib.g1_add(acc[8 * i:8 * i + 8], blk[8 * i:8 * i + 8])
+        acc[32:48] = _lib.g2_add(acc[32:48], blk[32:48])
+    return acc

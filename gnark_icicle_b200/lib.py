@@ -1,0 +1,290 @@
+"""ctypes binding of libg16b200.so (the C ABI in include/g16b200.h).
+
+This is the Python stand-in for the cgo layer a Go host would use (INTEGRATION.md shows the cgo stub);
+it exists because neither build machine has a Go toolchain.  Arrays are numpy ``uint64`` with a trailing
+limb axis -- Fr ``(n, 4)``, G1 affine ``(n, 8)``, G2 affine ``(n, 16)`` -- i.e. gnark-crypto's memory image.
+Device-resident operands are passed as integer device pointers (``torch.Tensor.data_ptr()``); torch is
+plumbing only.  There is no CPU fallback: a missing library or GPU raises.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libg16b200.so")
+
+DIF, DIT = 0, 1
+OUT_AR, OUT_BS1, OUT_KRS_K, OUT_KRS_HZ, OUT_BS2 = range(5)
+PROVE_OUT_BYTES = 384
+
+
+class G16Error(RuntimeError):
+    pass
+
+
+class Stats(ctypes.Structure):
+    _fields_ = [
+        ("ms_total", ctypes.c_float), ("ms_h2d", ctypes.c_float), ("ms_compute_h", ctypes.c_float),
+        ("ms_msm", ctypes.c_float * 5), ("ms_host", ctypes.c_float),
+        ("msm_c", ctypes.c_int32 * 5), ("msm_windows", ctypes.c_int32 * 5), ("msm_n", ctypes.c_uint64 * 5),
+        ("h2d_bytes", ctypes.c_uint64), ("d2h_bytes", ctypes.c_uint64),
+        ("kernel_launches", ctypes.c_uint32), ("reserved", ctypes.c_uint32),
+    ]
+
+    def as_dict(self):
+        return dict(ms_total=self.ms_total, ms_h2d=self.ms_h2d, ms_compute_h=self.ms_compute_h,
+                    ms_msm=list(self.ms_msm), ms_host=self.ms_host, msm_c=list(self.msm_c),
+                    msm_windows=list(self.msm_windows), msm_n=list(self.msm_n), h2d_bytes=self.h2d_bytes,
+                    d2h_bytes=self.d2h_bytes, kernel_launches=self.kernel_launches)
+
+
+class PkDesc(ctypes.Structure):
+    _fields_ = [
+        ("domain_n", ctypes.c_uint64),
+        ("g1_a", ctypes.c_void_p), ("n_a", ctypes.c_uint64),
+        ("g1_b", ctypes.c_void_p), ("n_b", ctypes.c_uint64),
+        ("g1_k", ctypes.c_void_p), ("n_k", ctypes.c_uint64),
+        ("g1_z", ctypes.c_void_p), ("n_z", ctypes.c_uint64),
+        ("g2_b", ctypes.c_void_p), ("n_b2", ctypes.c_uint64),
+        ("infinity_a", ctypes.c_void_p), ("infinity_b", ctypes.c_void_p),
+        ("n_wires", ctypes.c_uint64),
+        ("k_index", ctypes.c_void_p),
+        ("shard_index", ctypes.c_uint32), ("shard_count", ctypes.c_uint32),
+    ]
+
+
+# every symbol include/g16b200.h declares (tests check the library exports all of them)
+SYMBOLS = [
+    "g16_ctx_create", "g16_ctx_destroy", "g16_last_error", "g16_ctx_set", "g16_kernel_launch_count",
+    "g16_pk_upload", "g16_pk_free", "g16_prove_bn254", "g16_prove_bn254_dev", "g16_assemble_proof_bn254",
+    "g16_msm_g1", "g16_msm_g1_dev", "g16_msm_g2", "g16_msm_g2_dev", "g16_ntt", "g16_ntt_dev",
+    "g16_compute_h", "g16_compute_h_dev", "g16_fr_mul_vec",
+    "g16_g1_fixed_base_mul", "g16_g2_fixed_base_mul", "g16_g1_fixed_base_mul_dev", "g16_g2_fixed_base_mul_dev",
+    "g16_g1_add", "g16_g2_add", "g16_g1_scalar_mul", "g16_g2_scalar_mul", "g16_imad_peak", "g16_ctx_stream",
+]
+
+_lib = None
+
+
+def load():
+    """dlopen the in-tree library; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise G16Error(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(make -C gnark_icicle_b200/csrc); there is no CPU fallback")
+        lib = ctypes.CDLL(LIB_PATH)
+        lib.g16_last_error.restype = ctypes.c_char_p
+        lib.g16_last_error.argtypes = [ctypes.c_void_p]
+        lib.g16_kernel_launch_count.restype = ctypes.c_uint64
+        lib.g16_ctx_stream.restype = ctypes.c_void_p
+        lib.g16_ctx_stream.argtypes = [ctypes.c_void_p]
+        lib.g16_ctx_destroy.argtypes = [ctypes.c_void_p]
+        lib.g16_ctx_destroy.restype = None
+        _lib = lib
+    return _lib
+
+
+def _ptr(a):
+    if a is None:
+        return ctypes.c_void_p(0)
+    if isinstance(a, int):
+        return ctypes.c_void_p(a)
+    return ctypes.c_void_p(a.ctypes.data)
+
+
+def _arr(a, width):
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    if a.ndim == 1 and a.size == width:
+        a = a.reshape(1, width)
+    assert a.ndim == 2 and a.shape[1] == width, (a.shape, width)
+    return a
+
+
+u64 = ctypes.c_uint64
+
+
+class Context:
+    """One GPU, one call in flight (g16_ctx)."""
+
+    def __init__(self, device=0):
+        self._lib = load()
+        self._h = ctypes.c_void_p()
+        ids = (ctypes.c_int * 1)(device)
+        rc = self._lib.g16_ctx_create(ctypes.byref(self._h), 0, ids, 1)
+        if rc != 0:
+            self._h = ctypes.c_void_p()
+            raise G16Error(f"g16_ctx_create failed with status {rc} (no usable CUDA device? there is no CPU fallback)")
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._lib.g16_ctx_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise G16Error(f"{what}: {self._lib.g16_last_error(self._h).decode()}")
+
+    def set(self, key, value):
+        self._check(self._lib.g16_ctx_set(self._h, key.encode(), ctypes.c_int64(value)), "g16_ctx_set")
+
+    @property
+    def stream(self):
+        return self._lib.g16_ctx_stream(self._h)
+
+    # ---- primitives, host arrays
+    def fr_mul_vec(self, a, b):
+        a, b = _arr(a, 4), _arr(b, 4)
+        out = np.empty_like(a)
+        self._check(self._lib.g16_fr_mul_vec(self._h, _ptr(a), _ptr(b), u64(len(a)), _ptr(out)), "g16_fr_mul_vec")
+        return out
+
+    def msm_g1(self, scalars, bases):
+        s, p = _arr(scalars, 4), _arr(bases, 8)
+        assert len(s) == len(p)
+        out = np.zeros(8, dtype=np.uint64)
+        self._check(self._lib.g16_msm_g1(self._h, _ptr(s), _ptr(p), u64(len(s)), _ptr(out)), "g16_msm_g1")
+        return out
+
+    def msm_g2(self, scalars, bases):
+        s, p = _arr(scalars, 4), _arr(bases, 16)
+        assert len(s) == len(p)
+        out = np.zeros(16, dtype=np.uint64)
+        self._check(self._lib.g16_msm_g2(self._h, _ptr(s), _ptr(p), u64(len(s)), _ptr(out)), "g16_msm_g2")
+        return out
+
+    def ntt(self, data, inverse=False, coset=False, decimation=DIF):
+        x = _arr(data, 4).copy()
+        self._check(self._lib.g16_ntt(self._h, _ptr(x), u64(len(x)), int(inverse), int(coset), int(decimation)), "g16_ntt")
+        return x
+
+    def compute_h(self, a, b, c, domain_n):
+        a, b, c = _arr(a, 4), _arr(b, 4), _arr(c, 4)
+        assert len(a) == len(b) == len(c)
+        h = np.empty((domain_n, 4), dtype=np.uint64)
+        self._check(self._lib.g16_compute_h(self._h, _ptr(a), _ptr(b), _ptr(c), u64(len(a)), u64(domain_n), _ptr(h)), "g16_compute_h")
+        return h
+
+    def g1_fixed_base_mul(self, scalars):
+        s = _arr(scalars, 4)
+        out = np.empty((len(s), 8), dtype=np.uint64)
+        self._check(self._lib.g16_g1_fixed_base_mul(self._h, _ptr(s), u64(len(s)), _ptr(out)), "g16_g1_fixed_base_mul")
+        return out
+
+    def g2_fixed_base_mul(self, scalars):
+        s = _arr(scalars, 4)
+        out = np.empty((len(s), 16), dtype=np.uint64)
+        self._check(self._lib.g16_g2_fixed_base_mul(self._h, _ptr(s), u64(len(s)), _ptr(out)), "g16_g2_fixed_base_mul")
+        return out
+
+    # ---- primitives, device pointers (ints); results on host
+    def msm_g1_dev(self, scalars_ptr, bases_ptr, n):
+        out = np.zeros(8, dtype=np.uint64)
+        self._check(self._lib.g16_msm_g1_dev(self._h, _ptr(scalars_ptr), _ptr(bases_ptr), u64(n), _ptr(out)), "g16_msm_g1_dev")
+        return out
+
+    def msm_g2_dev(self, scalars_ptr, bases_ptr, n):
+        out = np.zeros(16, dtype=np.uint64)
+        self._check(self._lib.g16_msm_g2_dev(self._h, _ptr(scalars_ptr), _ptr(bases_ptr), u64(n), _ptr(out)), "g16_msm_g2_dev")
+        return out
+
+    def ntt_dev(self, data_ptr, n, inverse=False, coset=False, decimation=DIF):
+        self._check(self._lib.g16_ntt_dev(self._h, _ptr(data_ptr), u64(n), int(inverse), int(coset), int(decimation)), "g16_ntt_dev")
+
+    def compute_h_dev(self, a_ptr, b_ptr, c_ptr, domain_n):
+        self._check(self._lib.g16_compute_h_dev(self._h, _ptr(a_ptr), _ptr(b_ptr), _ptr(c_ptr), u64(domain_n)), "g16_compute_h_dev")
+
+    def g1_fixed_base_mul_dev(self, scalars_ptr, n, out_ptr):
+        self._check(self._lib.g16_g1_fixed_base_mul_dev(self._h, _ptr(scalars_ptr), u64(n), _ptr(out_ptr)), "g16_g1_fixed_base_mul_dev")
+
+    def g2_fixed_base_mul_dev(self, scalars_ptr, n, out_ptr):
+        self._check(self._lib.g16_g2_fixed_base_mul_dev(self._h, _ptr(scalars_ptr), u64(n), _ptr(out_ptr)), "g16_g2_fixed_base_mul_dev")
+
+    # ---- proving key + prove
+    def pk_upload(self, domain_n, g1_a, g1_b, g1_k, g1_z, g2_b, infinity_a, infinity_b, n_wires, k_index=None,
+                  shard_index=0, shard_count=1):
+        g1_a, g1_b, g1_k, g1_z, g2_b = _arr(g1_a, 8), _arr(g1_b, 8), _arr(g1_k, 8), _arr(g1_z, 8), _arr(g2_b, 16)
+        ia = np.ascontiguousarray(infinity_a, dtype=np.uint8)
+        ib = np.ascontiguousarray(infinity_b, dtype=np.uint8)
+        ki = None if k_index is None else np.ascontiguousarray(k_index, dtype=np.uint32)
+        d = PkDesc(domain_n, _ptr(g1_a), len(g1_a), _ptr(g1_b), len(g1_b), _ptr(g1_k), len(g1_k), _ptr(g1_z), len(g1_z),
+                   _ptr(g2_b), len(g2_b), _ptr(ia), _ptr(ib), n_wires, _ptr(ki), shard_index, shard_count)
+        h = u64(0)
+        self._check(self._lib.g16_pk_upload(self._h, ctypes.byref(d), ctypes.byref(h)), "g16_pk_upload")
+        return h.value
+
+    def pk_free(self, handle):
+        self._check(self._lib.g16_pk_free(self._h, u64(handle)), "g16_pk_free")
+
+    def prove(self, pk_handle, W, a, b, c):
+        """host arrays in, (5 raw MSM points as a 48-limb array, stats dict) out."""
+        W, a, b, c = _arr(W, 4), _arr(a, 4), _arr(b, 4), _arr(c, 4)
+        out = np.zeros(PROVE_OUT_BYTES // 8, dtype=np.uint64)
+        st = Stats()
+        self._check(self._lib.g16_prove_bn254(self._h, u64(pk_handle), _ptr(W), u64(len(W)), _ptr(a), _ptr(b), _ptr(c),
+                                              u64(len(a)), _ptr(out), ctypes.byref(st)), "g16_prove_bn254")
+        return out, st.as_dict()
+
+    def prove_dev(self, pk_handle, W_ptr, a_ptr, b_ptr, c_ptr):
+        out = np.zeros(PROVE_OUT_BYTES // 8, dtype=np.uint64)
+        st = Stats()
+        self._check(self._lib.g16_prove_bn254_dev(self._h, u64(pk_handle), _ptr(W_ptr), _ptr(a_ptr), _ptr(b_ptr), _ptr(c_ptr),
+                                                  _ptr(out), ctypes.byref(st)), "g16_prove_bn254_dev")
+        return out, st.as_dict()
+
+    def imad_peak(self):
+        a, b = ctypes.c_double(0), ctypes.c_double(0)
+        self._check(self._lib.g16_imad_peak(self._h, ctypes.byref(a), ctypes.byref(b)), "g16_imad_peak")
+        return a.value, b.value
+
+
+def kernel_launch_count():
+    return int(load().g16_kernel_launch_count())
+
+
+# ---- host-only helpers (no GPU needed)
+def g1_add(a, b):
+    a, b = _arr(a, 8), _arr(b, 8)
+    out = np.zeros(8, dtype=np.uint64)
+    assert load().g16_g1_add(_ptr(a), _ptr(b), _ptr(out)) == 0
+    return out
+
+
+def g2_add(a, b):
+    a, b = _arr(a, 16), _arr(b, 16)
+    out = np.zeros(16, dtype=np.uint64)
+    assert load().g16_g2_add(_ptr(a), _ptr(b), _ptr(out)) == 0
+    return out
+
+
+def g1_scalar_mul(a, k):
+    a, k = _arr(a, 8), _arr(k, 4)
+    out = np.zeros(8, dtype=np.uint64)
+    assert load().g16_g1_scalar_mul(_ptr(a), _ptr(k), _ptr(out)) == 0
+    return out
+
+
+def g2_scalar_mul(a, k):
+    a, k = _arr(a, 16), _arr(k, 4)
+    out = np.zeros(16, dtype=np.uint64)
+    assert load().g16_g2_scalar_mul(_ptr(a), _ptr(k), _ptr(out)) == 0
+    return out
+
+
+def assemble_proof(pk_points, r, s, msm_points):
+    """pk_points: 80 limbs (alpha, beta, delta G1; beta, delta G2); returns 32 limbs Ar||Bs||Krs."""
+    pk_points = np.ascontiguousarray(pk_points, dtype=np.uint64).reshape(-1)
+    msm_points = np.ascontiguousarray(msm_points, dtype=np.uint64).reshape(-1)
+    assert pk_points.size == 56 and msm_points.size == 48, (pk_points.size, msm_points.size)
+    r, s = _arr(r, 4), _arr(s, 4)
+    out = np.zeros(32, dtype=np.uint64)
+    assert load().g16_assemble_proof_bn254(_ptr(pk_points), _ptr(r), _ptr(s), _ptr(msm_points), _ptr(out)) == 0
+    return out

@@ -1,0 +1,155 @@
+/* libg16b200 -- C ABI of the B200-native Groth16 (BN254) proving hot path.
+ *
+ * Drop-in boundary for the device library that gnark's accelerated prover binds through cgo
+ * (reference: backend/groth16/bn254/icicle/icicle.go, which calls github.com/ingonyama-zk/iciclegnark).
+ * Each entry point names the reference interface it replaces (file:line under /root/reference).
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on failure; g16_last_error(ctx) describes the failure.
+ *     There is NO CPU fallback: without a working CUDA device every compute entry point fails.
+ *   - memory images are gnark-crypto's: fr/fp.Element = 4 little-endian uint64 limbs in Montgomery form
+ *     (R = 2^256); G1Affine = X||Y (64 B); G2Affine = X.A0||X.A1||Y.A0||Y.A1 (128 B); infinity = all zero.
+ *   - pointers are HOST pointers unless the function name ends in _dev, whose data pointers are DEVICE
+ *     pointers on the context's GPU (results are still written to host memory).
+ *   - a context is bound to one GPU and is thread-compatible: one call in flight per context.
+ *   - scalars equal to zero and bases equal to infinity are legal inputs everywhere; zero-length MSMs
+ *     return infinity (the reference special-cases both on the host: icicle.go:98-105,330-333,343-347).
+ */
+#ifndef G16B200_H
+#define G16B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct g16_ctx g16_ctx;
+
+#define G16_CURVE_BN254 0
+#define G16_CURVE_BLS12_377 1 /* reserved: not built in this round */
+
+/* index of each MSM result in g16_prove_bn254's output block */
+#define G16_OUT_AR 0      /* sum wA_j * G1.A_j            64 B at offset 0   (icicle.go:312-324 before the epilogue) */
+#define G16_OUT_BS1 1     /* sum wB_j * G1.B_j            64 B at offset 64  (icicle.go:299-310) */
+#define G16_OUT_KRS_K 2   /* sum w_priv * G1.K            64 B at offset 128 (icicle.go:337-362) */
+#define G16_OUT_KRS_HZ 3  /* sum h_i * G1.Z_i             64 B at offset 192 (icicle.go:326-335) */
+#define G16_OUT_BS2 4     /* sum wB_j * G2.B_j           128 B at offset 256 (icicle.go:377-393) */
+#define G16_PROVE_OUT_BYTES 384
+
+typedef struct {
+    float ms_total;        /* device time of the whole call (CUDA events) */
+    float ms_h2d;          /* host->device copies (host-pointer variants only) */
+    float ms_compute_h;    /* the 7-transform quotient pipeline */
+    float ms_msm[5];       /* indexed by G16_OUT_* */
+    float ms_host;         /* host epilogue of the MSMs (Horner over windows + affine conversion), wall clock */
+    int32_t msm_c[5];      /* window bits used */
+    int32_t msm_windows[5];
+    uint64_t msm_n[5];     /* points in each MSM (this shard) */
+    uint64_t h2d_bytes;
+    uint64_t d2h_bytes;
+    uint32_t kernel_launches; /* kernels of this library launched by the call */
+    uint32_t reserved;
+} g16_stats;
+
+/* ---- context ------------------------------------------------------------------------------------- */
+/* device_ids/n_devices: this round binds one GPU per context (n_devices must be 1; one process per GPU,
+ * shards are combined by the caller -- see INTEGRATION.md).  Replaces the implicit default-device state
+ * of iciclegnark (icicle.go never passes a device id). */
+int g16_ctx_create(g16_ctx** out, int curve_id, const int* device_ids, int n_devices);
+void g16_ctx_destroy(g16_ctx* ctx);
+const char* g16_last_error(const g16_ctx* ctx);
+/* tunables: "msm_c" (0 = auto, 8..16), "msm_waves" (accumulate waves, default 2) */
+int g16_ctx_set(g16_ctx* ctx, const char* key, int64_t value);
+/* total kernels launched by this library in this process (bench.py's gpu_launches evidence) */
+uint64_t g16_kernel_launch_count(void);
+
+/* ---- device-resident proving key ------------------------------------------------------------------ */
+/* Replaces pk.setupDevicePointers (icicle.go:31-130) and deviceInfo (icicle/provingkey.go:10-23):
+ * bases are uploaded once, kept in Montgomery affine form (no host-side conversion), infinity entries
+ * of K are kept (not stripped), the coset/twiddle tables are generated on the device. */
+typedef struct {
+    uint64_t domain_n;             /* pk.Domain.Cardinality (power of two) */
+    const void* g1_a; uint64_t n_a;   /* pk.G1.A  (len nbWires - NbInfinityA) */
+    const void* g1_b; uint64_t n_b;   /* pk.G1.B  (len nbWires - NbInfinityB) */
+    const void* g1_k; uint64_t n_k;   /* pk.G1.K  (private wires) */
+    const void* g1_z; uint64_t n_z;   /* pk.G1.Z  (domain_n - 1, bit-reversed at setup, setup.go:265-267) */
+    const void* g2_b; uint64_t n_b2;  /* pk.G2.B  (same length as g1_b) */
+    const uint8_t* infinity_a;     /* pk.InfinityA, one byte per wire (setup.go:212-237) */
+    const uint8_t* infinity_b;     /* pk.InfinityB */
+    uint64_t n_wires;
+    const uint32_t* k_index;       /* wire index feeding each K base (after filterHeap, prove.go:241-246);
+                                      NULL = wires [n_wires - n_k, n_wires) in order */
+    uint32_t shard_index;          /* this context keeps slice shard_index of shard_count of every base */
+    uint32_t shard_count;          /*   array (point-range sharding across GPUs); 0/1 = whole key */
+} g16_pk_desc;
+int g16_pk_upload(g16_ctx* ctx, const g16_pk_desc* desc, uint64_t* pk_handle);
+int g16_pk_free(g16_ctx* ctx, uint64_t pk_handle);
+
+/* ---- the proof hot path ---------------------------------------------------------------------------- */
+/* Replaces the device section of icicle_bn254.Prove (icicle.go:204-410): computeH + the five MSMs.
+ * W: full wire vector (n_wires Fr); a,b,c: solver outputs L.w, R.w, O.w (n_constraints Fr each).
+ * out_points: G16_PROVE_OUT_BYTES bytes, the five raw MSM results in affine form (this shard's partial
+ * sums when the key is sharded).  The O(1) epilogue (icicle.go:281-295,306-307,319-321,362-372,386-391)
+ * stays with the caller, or use g16_assemble_proof_bn254. */
+int g16_prove_bn254(g16_ctx* ctx, uint64_t pk_handle, const void* W, uint64_t n_wires, const void* a,
+                    const void* b, const void* c, uint64_t n_constraints, void* out_points, g16_stats* stats);
+/* device-pointer variant: W_d (n_wires), a_d/b_d/c_d (domain_n elements each, zero padded, CLOBBERED) */
+int g16_prove_bn254_dev(g16_ctx* ctx, uint64_t pk_handle, const void* W_d, void* a_d, void* b_d, void* c_d,
+                        void* out_points, g16_stats* stats);
+
+/* Host epilogue of prove.go:180-195,209-224,251-279,297-302 with injected randomness r, s (Fr, Montgomery):
+ * pk_points = G1.Alpha || G1.Beta || G1.Delta (3 x 64 B) || G2.Beta || G2.Delta (2 x 128 B);
+ * proof_out = Ar (64) || Bs (128) || Krs (64). */
+int g16_assemble_proof_bn254(const void* pk_points, const void* r, const void* s, const void* msm_points,
+                             void* proof_out);
+
+/* ---- primitives (BASELINE configs 2 and 3, parity tests) ------------------------------------------ */
+/* replaces iciclegnark.MsmOnDevice (icicle.go:302,315,332,355) / curve.G1Jac.MultiExp (prove.go:204-247) */
+int g16_msm_g1(g16_ctx* ctx, const void* scalars, const void* bases, uint64_t n, void* out_affine);
+int g16_msm_g1_dev(g16_ctx* ctx, const void* scalars_d, const void* bases_d, uint64_t n, void* out_affine);
+/* replaces iciclegnark.MsmG2OnDevice (icicle.go:382) / curve.G2Jac.MultiExp (prove.go:293) */
+int g16_msm_g2(g16_ctx* ctx, const void* scalars, const void* bases, uint64_t n, void* out_affine);
+int g16_msm_g2_dev(g16_ctx* ctx, const void* scalars_d, const void* bases_d, uint64_t n, void* out_affine);
+
+/* fft.Domain transforms on n = 2^k Fr elements, in place (prove.go:372-378,396; icicle.go:489,490,502,510).
+ * inverse: 0 = FFT, 1 = FFTInverse (scaled by 1/n);  coset: 1 = fft.OnCoset() (shift g = 5);
+ * decimation: G16_DIF = natural in -> bit-reversed out, G16_DIT = bit-reversed in -> natural out. */
+#define G16_DIF 0
+#define G16_DIT 1
+int g16_ntt(g16_ctx* ctx, void* data, uint64_t n, int inverse, int coset, int decimation);
+int g16_ntt_dev(g16_ctx* ctx, void* data_d, uint64_t n, int inverse, int coset, int decimation);
+
+/* computeH (prove.go:356-399 / icicle.go:453-513): h_out receives domain_n Fr in bit-reversed order */
+int g16_compute_h(g16_ctx* ctx, const void* a, const void* b, const void* c, uint64_t n_constraints,
+                  uint64_t domain_n, void* h_out);
+/* a_d,b_d,c_d: domain_n elements each (zero padded); h is left in a_d, b_d/c_d are clobbered */
+int g16_compute_h_dev(g16_ctx* ctx, void* a_d, void* b_d, void* c_d, uint64_t domain_n);
+
+/* out[i] = a[i] * b[i] in Fr (icicle.go:500 PolyOps building block; minimum parity slice) */
+int g16_fr_mul_vec(g16_ctx* ctx, const void* a, const void* b, uint64_t n, void* out);
+
+/* ---- setup-side tooling ---------------------------------------------------------------------------- */
+/* out[i] = [k_i] G with G the BN254 G1 / G2 generator: device analogue of curve.BatchScalarMultiplicationG1/G2
+ * (setup.go:251,320), used to materialise proving keys at BASELINE sizes. */
+int g16_g1_fixed_base_mul(g16_ctx* ctx, const void* scalars, uint64_t n, void* out_points);
+int g16_g2_fixed_base_mul(g16_ctx* ctx, const void* scalars, uint64_t n, void* out_points);
+int g16_g1_fixed_base_mul_dev(g16_ctx* ctx, const void* scalars_d, uint64_t n, void* out_points_d);
+int g16_g2_fixed_base_mul_dev(g16_ctx* ctx, const void* scalars_d, uint64_t n, void* out_points_d);
+
+/* host-side affine group helpers (epilogue arithmetic for non-Go hosts): out = a + b ; out = [k] a */
+int g16_g1_add(const void* a, const void* b, void* out);
+int g16_g2_add(const void* a, const void* b, void* out);
+int g16_g1_scalar_mul(const void* a, const void* k_fr_mont, void* out);
+int g16_g2_scalar_mul(const void* a, const void* k_fr_mont, void* out);
+
+/* ---- measurement ----------------------------------------------------------------------------------- */
+/* Measured integer-pipe peak on this GPU: independent 32-bit IMAD (mad.lo.u32) and IMAD.WIDE (mad.wide.u32)
+ * issue rates in operations per second over all SMs -- the MSM/NTT roofline denominator. */
+int g16_imad_peak(g16_ctx* ctx, double* imad_per_s, double* imad_wide_per_s);
+/* time one accumulate-only or full MSM etc. is done by the caller with CUDA events on this stream */
+void* g16_ctx_stream(g16_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
