@@ -35,7 +35,7 @@ struct PkDev {
 struct g16_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[16] = {};
+    cudaEvent_t ev[32] = {};
     std::string err;
     std::map<int, NttDomain> domains;
     std::map<uint64_t, PkDev> pks;
@@ -227,6 +227,7 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
     cudaEvent_t* ev = ctx->ev;
     MsmPlan plan[5];
     MsmStats ms[5];
+    for (int i = 0; i < 5; i++) { ms[i].acc_begin = ev[16 + 2 * i]; ms[i].acc_end = ev[17 + 2 * i]; }
     G16_CUDA(cudaEventRecord(ev[0], st));
     compute_h_device(dom, a_d, b_d, c_d, st);                 // h (bit-reversed) in a_d
     G16_CUDA(cudaEventRecord(ev[1], st));
@@ -252,6 +253,7 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
         for (int i = 0; i < 5; i++) {
             G16_CUDA(cudaEventElapsedTime(&stats->ms_msm[i], ev[1 + i], ev[2 + i]));
             stats->msm_c[i] = plan[i].c; stats->msm_windows[i] = plan[i].W; stats->msm_n[i] = ns[i];
+            if (ns[i]) G16_CUDA(cudaEventElapsedTime(&stats->ms_accumulate[i], ev[16 + 2 * i], ev[17 + 2 * i]));
         }
         G16_CUDA(cudaEventElapsedTime(&stats->ms_total, ev[0], ev[6]));
         stats->ms_host = std::chrono::duration<float, std::milli>(t1 - t0).count();
@@ -602,5 +604,87 @@ extern "C" int g16_imad_peak(g16_ctx* ctx, double* imad_per_s, double* imad_wide
         ctx->stage[0].reserve(64);
         if (imad_per_s) *imad_per_s = imad_rate<false>(ctx, ctx->stage[0].as<uint32_t>());
         if (imad_wide_per_s) *imad_wide_per_s = imad_rate<true>(ctx, ctx->stage[0].as<uint32_t>());
+    });
+}
+
+// =================================================================== pipe-rate microbenchmarks (roofline denominators)
+namespace {
+
+// independent carry chains shaped like Field::cmad_n: 4 x (mad.lo.cc, madc.hi.cc) + addc per chain, 4 chains in flight
+__global__ void __launch_bounds__(256) k_wide_carry_peak(uint32_t* sink, uint32_t a0, int iters) {
+#ifdef __CUDA_ARCH__
+    uint32_t a[4] = {a0 + threadIdx.x, a0 * 3 + 1, a0 * 5 + 2, a0 * 7 + 3};
+    uint32_t acc[4][9];
+    for (int c = 0; c < 4; c++)
+        for (int k = 0; k < 9; k++) acc[c][k] = threadIdx.x + c * 9 + k;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            uint32_t bi = acc[c][0] | 1u;
+            acc[c][0] = ptx::mad_lo_cc(a[0], bi, acc[c][0]);
+            acc[c][1] = ptx::madc_hi_cc(a[0], bi, acc[c][1]);
+#pragma unroll
+            for (int j = 2; j < 8; j += 2) {
+                acc[c][j] = ptx::madc_lo_cc(a[j >> 1], bi, acc[c][j]);
+                acc[c][j + 1] = ptx::madc_hi_cc(a[j >> 1], bi, acc[c][j + 1]);
+            }
+            acc[c][8] = ptx::addc(acc[c][8], 0);
+        }
+    }
+    uint32_t x = 0;
+    for (int c = 0; c < 4; c++)
+        for (int k = 0; k < 9; k++) x ^= acc[c][k];
+    if (x == 0x12345678u) sink[0] = x;
+#endif
+}
+
+// 4 independent Montgomery multiplications per iteration, all in registers
+__global__ void __launch_bounds__(256) k_fr_mul_peak(uint32_t* sink, uint32_t seed, int iters) {
+    Fr::T x[4], y = Fr::one();
+    y.l[0] += seed + threadIdx.x;
+    for (int c = 0; c < 4; c++) { x[c] = Fr::r2(); x[c].l[0] += c + threadIdx.x; }
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int c = 0; c < 4; c++) x[c] = Fr::mul(x[c], y);
+    }
+    uint32_t v = 0;
+    for (int c = 0; c < 4; c++)
+        for (int k = 0; k < 8; k++) v ^= x[c].l[k];
+    if (v == 0x12345678u) sink[0] = v;
+}
+
+template <class K>
+double rate_of(g16_ctx* ctx, K launch, double ops_per_launch) {
+    cudaStream_t st = ctx->stream;
+    launch(8);
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; rep++) {
+        G16_CUDA(cudaEventRecord(ctx->ev[10], st));
+        launch(0);
+        G16_CUDA(cudaEventRecord(ctx->ev[11], st));
+        G16_CUDA(cudaStreamSynchronize(st));
+        float ms = 0;
+        G16_CUDA(cudaEventElapsedTime(&ms, ctx->ev[10], ctx->ev[11]));
+        if (ms < best) best = ms;
+    }
+    return ops_per_launch / (best * 1e-3);
+}
+
+}  // namespace
+
+// out[0] = IMAD.WIDE.U32.X (carry chain) issue rate per second; out[1] = in-register Fr multiplications per second
+extern "C" int g16_pipe_rates(g16_ctx* ctx, double* out2) {
+    return guarded(ctx, [&] {
+        if (!out2) throw std::runtime_error("null argument");
+        ctx->stage[0].reserve(64);
+        uint32_t* sink = ctx->stage[0].as<uint32_t>();
+        int sms = 0;
+        G16_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
+        const int blocks = sms * 8, it1 = 2048, it2 = 512;
+        cudaStream_t st = ctx->stream;
+        out2[0] = rate_of(ctx, [&](int small) { k_wide_carry_peak<<<blocks, 256, 0, st>>>(sink, 3, small ? small : it1); G16_LAUNCH_CHECK(); },
+                          (double)blocks * 256 * it1 * 16);
+        out2[1] = rate_of(ctx, [&](int small) { k_fr_mul_peak<<<blocks, 256, 0, st>>>(sink, 3, small ? small : it2); G16_LAUNCH_CHECK(); },
+                          (double)blocks * 256 * it2 * 4);
     });
 }

@@ -106,7 +106,7 @@ struct Curve {
     }
 };
 
-typedef Curve<Fp> G1;
+typedef Curve<FpC> G1;
 typedef Curve<Fp2> G2;
 
 }  // namespace g16

@@ -278,8 +278,19 @@ struct Field {
     G16_HD static T from_u64(uint64_t v) { T t = zero(); t.l[0] = (uint32_t)v; t.l[1] = (uint32_t)(v >> 32); return to_mont(t); }
 };
 
+// Same field, but multiplication is a real (register-ABI) call on the device: the curve kernels issue 10-30
+// multiplications per group operation, and inlining them all makes the loop body (35-90 KB of SASS) overflow
+// the 32 KB L1.5 instruction cache -- ncu showed "no instruction" as the top stall of k_accumulate.
+template <class P>
+struct FieldCall : Field<P> {
+    typedef typename Field<P>::T T;
+    G16_HD_COLD static T mul(T a, T b) { return Field<P>::mul(a, b); }
+    G16_HD static T sqr(const T& a) { return mul(a, a); }
+};
+
 typedef Field<FpBN254> Fp;
 typedef Field<FrBN254> Fr;
+typedef FieldCall<FpBN254> FpC;
 
 // ---------------------------------------------------------------- Fp2 = Fp[u]/(u^2+1)  (gnark E2{A0,A1})
 template <class F>
@@ -313,6 +324,6 @@ struct Ext2 {
         T r; r.a0 = F::mul(a.a0, d); r.a1 = F::neg(F::mul(a.a1, d)); return r;
     }
 };
-typedef Ext2<Fp> Fp2;
+typedef Ext2<FpC> Fp2;
 
 }  // namespace g16

@@ -10,7 +10,7 @@
 // Pipeline (all on one stream, no host synchronisation until the W window sums are read back):
 //   k_digits       from-Montgomery + signed c-bit digit recoding, one biased u16 per (window, scalar)
 //   k_hist         per-(window, point-chunk) shared-memory histogram -> global bucket counts
-//   k_scan         exclusive scan of the W*2^(c-1) counts
+//   k_scan_local/_add  exclusive scan of the W*2^(c-1) counts
 //   k_scatter      in-house counting sort: CTA-aggregated range reservation + shared-memory cursors;
 //                  emits (point index | sign<<31) grouped by (window, bucket)
 //   k_accumulate   balanced segmented reduction: every thread owns S consecutive sorted entries, adds
@@ -25,11 +25,11 @@
 namespace g16 {
 
 struct MsmWorkspace {
-    DevBuf digits, sorted, counts, offsets, cursor, buckets, head, tail, partial, wsum;
+    DevBuf digits, sorted, counts, offsets, cursor, buckets, head, tail, partial, wsum, scan_tmp;
     PinnedBuf host_wsum;
     void release() {
         digits.release(); sorted.release(); counts.release(); offsets.release(); cursor.release();
-        buckets.release(); head.release(); tail.release(); partial.release(); wsum.release(); host_wsum.release();
+        buckets.release(); head.release(); tail.release(); partial.release(); wsum.release(); host_wsum.release(); scan_tmp.release();
     }
 };
 
@@ -125,27 +125,51 @@ static __global__ void k_hist(const uint16_t* __restrict__ digits, uint64_t n, u
     }
 }
 
-// single-CTA exclusive scan; offsets has nb+1 entries, cursor (nb) receives a copy of the starts
-static __global__ void k_scan(const uint32_t* __restrict__ counts, uint32_t* __restrict__ offsets, uint32_t* __restrict__ cursor, uint32_t nb) {
-    __shared__ uint32_t part[1024];
-    uint32_t per = (nb + 1023) / 1024;
-    uint32_t lo = threadIdx.x * per, hi = lo + per;
-    if (lo > nb) lo = nb;
-    if (hi > nb) hi = nb;
-    uint32_t s = 0;
-    for (uint32_t i = lo; i < hi; i++) s += counts[i];
-    part[threadIdx.x] = s;
+// two-kernel exclusive scan over the W*2^(c-1) bucket counts: CTA-local scan of 4096 entries + CTA totals,
+// then every CTA adds the sum of the totals before it.  offsets has nb+1 entries; cursor (nb) gets a copy.
+constexpr int SCAN_BLOCK = 4096;
+static __global__ void __launch_bounds__(1024) k_scan_local(const uint32_t* __restrict__ counts, uint32_t* __restrict__ offsets,
+                                                            uint32_t* __restrict__ block_tot, uint32_t nb) {
+    __shared__ uint32_t warp_tot[32];
+    const uint32_t base = blockIdx.x * SCAN_BLOCK + threadIdx.x * 4;
+    uint32_t v[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) v[k] = base + k < nb ? counts[base + k] : 0;
+    const uint32_t s = v[0] + v[1] + v[2] + v[3];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = s;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, off); if (lane >= off) inc += t; }
+    if (lane == 31) warp_tot[warp] = inc;
     __syncthreads();
-    // Hillis-Steele inclusive scan over 1024 partials
-    for (int off = 1; off < 1024; off <<= 1) {
-        uint32_t v = threadIdx.x >= (unsigned)off ? part[threadIdx.x - off] : 0;
-        __syncthreads();
-        part[threadIdx.x] += v;
-        __syncthreads();
+    if (warp == 0) {
+        uint32_t w = warp_tot[lane], wi = w;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, wi, off); if (lane >= off) wi += t; }
+        warp_tot[lane] = wi - w;
+        if (lane == 31) block_tot[blockIdx.x] = wi;
     }
-    uint32_t run = threadIdx.x ? part[threadIdx.x - 1] : 0;
-    for (uint32_t i = lo; i < hi; i++) { offsets[i] = run; cursor[i] = run; run += counts[i]; }
-    if (threadIdx.x == 1023) offsets[nb] = part[1023];
+    __syncthreads();
+    uint32_t run = inc - s + warp_tot[warp];
+#pragma unroll
+    for (int k = 0; k < 4; k++) { if (base + k < nb) offsets[base + k] = run; run += v[k]; }
+}
+static __global__ void __launch_bounds__(1024) k_scan_add(uint32_t* __restrict__ offsets, uint32_t* __restrict__ cursor,
+                                                          const uint32_t* __restrict__ block_tot, uint32_t nb) {
+    __shared__ uint32_t pre;
+    if (threadIdx.x < 32) {
+        uint32_t s = 0;
+        for (uint32_t i = threadIdx.x; i < blockIdx.x; i += 32) s += block_tot[i];
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+        if (threadIdx.x == 0) pre = s;
+    }
+    __syncthreads();
+    const uint32_t base = blockIdx.x * SCAN_BLOCK + threadIdx.x * 4;
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+        if (base + k < nb) { uint32_t o = offsets[base + k] + pre; offsets[base + k] = o; cursor[base + k] = o; }
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) offsets[nb] = pre + block_tot[blockIdx.x];
 }
 
 static __global__ void k_scatter(const uint16_t* __restrict__ digits, uint64_t n, uint32_t* __restrict__ cursor,
@@ -339,7 +363,7 @@ __global__ void __launch_bounds__(32) k_window_sum(const typename C::Xyzz* __res
 }
 
 // ------------------------------------------------------------------ host driver
-struct MsmStats { int c = 0, W = 0; uint32_t acc_threads = 0; };
+struct MsmStats { int c = 0, W = 0; uint32_t acc_threads = 0; cudaEvent_t acc_begin = nullptr, acc_end = nullptr; };
 
 // Enqueues the whole MSM on `st`; window sums land in ws.host_wsum (pinned) after the stream drains.
 template <class C, int ACC_THREADS, int ACC_MINB>
@@ -369,6 +393,7 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
     ws.counts.reserve((size_t)pl.NB * 4);
     ws.offsets.reserve((size_t)(pl.NB + 1) * 4);
     ws.cursor.reserve((size_t)pl.NB * 4);
+    ws.scan_tmp.reserve((size_t)((pl.NB + SCAN_BLOCK - 1) / SCAN_BLOCK) * 4 + 16);
     ws.buckets.reserve((size_t)pl.NB * sizeof(Xyzz));
     ws.head.reserve((size_t)nthreads * sizeof(Xyzz));
     ws.tail.reserve((size_t)nthreads * sizeof(Xyzz));
@@ -400,14 +425,19 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
     dim3 hgrid(chunks, pl.W);
     k_hist<<<hgrid, 1024, hsmem, st>>>(digits, n, counts, pl.c, per_block);
     G16_LAUNCH_CHECK();
-    k_scan<<<1, 1024, 0, st>>>(counts, offsets, cursor, pl.NB);
+    const uint32_t scan_blocks = (pl.NB + SCAN_BLOCK - 1) / SCAN_BLOCK;
+    k_scan_local<<<scan_blocks, 1024, 0, st>>>(counts, offsets, ws.scan_tmp.as<uint32_t>(), pl.NB);
+    G16_LAUNCH_CHECK();
+    k_scan_add<<<scan_blocks, 1024, 0, st>>>(offsets, cursor, ws.scan_tmp.as<uint32_t>(), pl.NB);
     G16_LAUNCH_CHECK();
     k_scatter<<<hgrid, 1024, hsmem, st>>>(digits, n, cursor, sorted, pl.c, per_block);
     G16_LAUNCH_CHECK();
 
+    if (stats && stats->acc_begin) G16_CUDA(cudaEventRecord(stats->acc_begin, st));
     k_accumulate<C, ACC_THREADS, ACC_MINB><<<(nthreads + ACC_THREADS - 1) / ACC_THREADS, ACC_THREADS, 0, st>>>(
         bases_d, sorted, offsets, pl.NB, nthreads, buckets, ws.head.as<Xyzz>(), ws.tail.as<Xyzz>());
     G16_LAUNCH_CHECK();
+    if (stats && stats->acc_end) G16_CUDA(cudaEventRecord(stats->acc_end, st));
     k_fixup<C><<<(pl.NB + 127) / 128, 128, 0, st>>>(offsets, pl.NB, nthreads, buckets, ws.head.as<Xyzz>(), ws.tail.as<Xyzz>());
     G16_LAUNCH_CHECK();
     dim3 rgrid(pl.red_rb, pl.W);
@@ -416,7 +446,7 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
     k_window_sum<C><<<pl.W, 32, 0, st>>>(ws.partial.as<Xyzz>(), pl.red_rb, ws.wsum.as<Xyzz>());
     G16_LAUNCH_CHECK();
     G16_CUDA(cudaMemcpyAsync(ws.host_wsum.p, ws.wsum.p, (size_t)pl.W * sizeof(Xyzz), cudaMemcpyDeviceToHost, st));
-    if (stats) { stats->c = pl.c; stats->W = pl.W; stats->acc_threads = nthreads; }
+    if (stats) stats->acc_threads = nthreads;
 }
 
 // Horner over the window sums (host, O(W*c) group operations) -> affine

@@ -30,13 +30,15 @@ class Stats(ctypes.Structure):
         ("msm_c", ctypes.c_int32 * 5), ("msm_windows", ctypes.c_int32 * 5), ("msm_n", ctypes.c_uint64 * 5),
         ("h2d_bytes", ctypes.c_uint64), ("d2h_bytes", ctypes.c_uint64),
         ("kernel_launches", ctypes.c_uint32), ("reserved", ctypes.c_uint32),
+        ("ms_accumulate", ctypes.c_float * 5), ("reserved2", ctypes.c_float),
     ]
 
     def as_dict(self):
         return dict(ms_total=self.ms_total, ms_h2d=self.ms_h2d, ms_compute_h=self.ms_compute_h,
                     ms_msm=list(self.ms_msm), ms_host=self.ms_host, msm_c=list(self.msm_c),
                     msm_windows=list(self.msm_windows), msm_n=list(self.msm_n), h2d_bytes=self.h2d_bytes,
-                    d2h_bytes=self.d2h_bytes, kernel_launches=self.kernel_launches)
+                    d2h_bytes=self.d2h_bytes, kernel_launches=self.kernel_launches,
+                    ms_accumulate=list(self.ms_accumulate))
 
 
 class PkDesc(ctypes.Structure):
@@ -61,7 +63,7 @@ SYMBOLS = [
     "g16_msm_g1", "g16_msm_g1_dev", "g16_msm_g2", "g16_msm_g2_dev", "g16_ntt", "g16_ntt_dev",
     "g16_compute_h", "g16_compute_h_dev", "g16_fr_mul_vec",
     "g16_g1_fixed_base_mul", "g16_g2_fixed_base_mul", "g16_g1_fixed_base_mul_dev", "g16_g2_fixed_base_mul_dev",
-    "g16_g1_add", "g16_g2_add", "g16_g1_scalar_mul", "g16_g2_scalar_mul", "g16_imad_peak", "g16_ctx_stream",
+    "g16_g1_add", "g16_g2_add", "g16_g1_scalar_mul", "g16_g2_scalar_mul", "g16_imad_peak", "g16_pipe_rates", "g16_ctx_stream",
 ]
 
 _lib = None
@@ -244,6 +246,15 @@ class Context:
         a, b = ctypes.c_double(0), ctypes.c_double(0)
         self._check(self._lib.g16_imad_peak(self._h, ctypes.byref(a), ctypes.byref(b)), "g16_imad_peak")
         return a.value, b.value
+
+
+def _pipe_rates(self):
+    out = (ctypes.c_double * 2)()
+    self._check(self._lib.g16_pipe_rates(self._h, out), "g16_pipe_rates")
+    return out[0], out[1]
+
+
+Context.pipe_rates = _pipe_rates
 
 
 def kernel_launch_count():

@@ -49,6 +49,8 @@ typedef struct {
     uint64_t d2h_bytes;
     uint32_t kernel_launches; /* kernels of this library launched by the call */
     uint32_t reserved;
+    float ms_accumulate[5]; /* the bucket-accumulation kernel of each MSM (dominant kernel; roofline evidence) */
+    float reserved2;
 } g16_stats;
 
 /* ---- context ------------------------------------------------------------------------------------- */
@@ -146,7 +148,10 @@ int g16_g2_scalar_mul(const void* a, const void* k_fr_mont, void* out);
 /* Measured integer-pipe peak on this GPU: independent 32-bit IMAD (mad.lo.u32) and IMAD.WIDE (mad.wide.u32)
  * issue rates in operations per second over all SMs -- the MSM/NTT roofline denominator. */
 int g16_imad_peak(g16_ctx* ctx, double* imad_per_s, double* imad_wide_per_s);
-/* time one accumulate-only or full MSM etc. is done by the caller with CUDA events on this stream */
+/* out2[0] = IMAD.WIDE.U32.X (carry-chained, the form the Montgomery multiplier issues) rate per second;
+ * out2[1] = in-register Fr Montgomery multiplications per second (the practical field-multiplier peak). */
+int g16_pipe_rates(g16_ctx* ctx, double* out2);
+/* the library's stream, so callers can bracket calls with CUDA events */
 void* g16_ctx_stream(g16_ctx* ctx);
 
 #ifdef __cplusplus
