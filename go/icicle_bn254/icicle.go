@@ -1,0 +1,184 @@
+//go:build icicle
+
+package icicle_bn254
+
+/*
+#cgo CFLAGS: -I${SRCDIR}/../../include
+#cgo LDFLAGS: -L${SRCDIR}/../../gnark_icicle_b200 -lg16b200 -Wl,-rpath,${SRCDIR}/../../gnark_icicle_b200
+#include <stdlib.h>
+#include "g16b200.h"
+*/
+import "C"
+
+import (
+	"fmt"
+	"math/big"
+	"runtime"
+	"time"
+	"unsafe"
+
+	curve "github.com/consensys/gnark-crypto/ecc/bn254"
+	"github.com/consensys/gnark-crypto/ecc/bn254/fr"
+	"github.com/consensys/gnark/backend"
+	groth16_bn254 "github.com/consensys/gnark/backend/groth16/bn254"
+	"github.com/consensys/gnark/backend/witness"
+	"github.com/consensys/gnark/constraint"
+	cs "github.com/consensys/gnark/constraint/bn254"
+	"github.com/consensys/gnark/logger"
+)
+
+// HasIcicle tells the groth16 facade that the accelerated prover is compiled in.
+const HasIcicle = true
+
+type ctxHandle = *C.g16_ctx
+
+func lastError(ctx ctxHandle, what string) error {
+	return fmt.Errorf("%s: %s", what, C.GoString(C.g16_last_error(ctx)))
+}
+
+func boolBytes(b []bool) []byte {
+	out := make([]byte, len(b))
+	for i, v := range b {
+		if v {
+			out[i] = 1
+		}
+	}
+	return out
+}
+
+func ptrOf[T any](s []T) unsafe.Pointer {
+	if len(s) == 0 {
+		return nil
+	}
+	return unsafe.Pointer(&s[0])
+}
+
+// setupDevicePointers uploads the key once.  gnark-crypto elements are already the memory image the library
+// expects (little-endian Montgomery limbs), so slices are handed over as they are -- no conversion, no
+// stripping of infinity points.
+func (pk *ProvingKey) setupDevicePointers() error {
+	if pk.deviceInfo != nil {
+		return nil
+	}
+	var ctx ctxHandle
+	dev := C.int(0)
+	if rc := C.g16_ctx_create(&ctx, C.G16_CURVE_BN254, &dev, 1); rc != 0 {
+		return fmt.Errorf("g16_ctx_create: status %d (no CUDA device? this backend has no CPU fallback)", int(rc))
+	}
+	infA, infB := boolBytes(pk.InfinityA), boolBytes(pk.InfinityB)
+	var pin runtime.Pinner
+	defer pin.Unpin()
+	for _, p := range []unsafe.Pointer{ptrOf(pk.G1.A), ptrOf(pk.G1.B), ptrOf(pk.G1.K), ptrOf(pk.G1.Z), ptrOf(pk.G2.B), ptrOf(infA), ptrOf(infB)} {
+		if p != nil {
+			pin.Pin(p)
+		}
+	}
+	var d C.g16_pk_desc
+	d.domain_n = C.uint64_t(pk.Domain.Cardinality)
+	d.g1_a, d.n_a = ptrOf(pk.G1.A), C.uint64_t(len(pk.G1.A))
+	d.g1_b, d.n_b = ptrOf(pk.G1.B), C.uint64_t(len(pk.G1.B))
+	d.g1_k, d.n_k = ptrOf(pk.G1.K), C.uint64_t(len(pk.G1.K))
+	d.g1_z, d.n_z = ptrOf(pk.G1.Z), C.uint64_t(len(pk.G1.Z))
+	d.g2_b, d.n_b2 = ptrOf(pk.G2.B), C.uint64_t(len(pk.G2.B))
+	d.infinity_a, d.infinity_b = (*C.uint8_t)(ptrOf(infA)), (*C.uint8_t)(ptrOf(infB))
+	d.n_wires = C.uint64_t(len(pk.InfinityA))
+	d.shard_count = 1
+	var h C.uint64_t
+	if rc := C.g16_pk_upload(ctx, &d, &h); rc != 0 {
+		err := lastError(ctx, "g16_pk_upload")
+		C.g16_ctx_destroy(ctx)
+		return err
+	}
+	pk.deviceInfo = &deviceInfo{ctx: ctx, handle: uint64(h)}
+	return nil
+}
+
+// Prove follows the reference prover: CPU fallback unless the accelerator option is set, solve on the CPU,
+// device section (computeH + five MSMs) through one C call, O(1) epilogue on the CPU.
+func Prove(r1cs *cs.R1CS, pk *ProvingKey, fullWitness witness.Witness, opts ...backend.ProverOption) (*groth16_bn254.Proof, error) {
+	opt, err := backend.NewProverConfig(opts...)
+	if err != nil {
+		return nil, fmt.Errorf("new prover config: %w", err)
+	}
+	if opt.Accelerator != "icicle" {
+		return groth16_bn254.Prove(r1cs, &pk.ProvingKey, fullWitness, opts...)
+	}
+	log := logger.Logger().With().Str("curve", r1cs.CurveID().String()).Str("acceleration", "g16b200").Int("nbConstraints", r1cs.GetNbConstraints()).Str("backend", "groth16").Logger()
+	if len(r1cs.CommitmentInfo.(constraint.Groth16Commitments)) != 0 {
+		// BSB22 commitments are handled by the CPU prover until the commitment MSMs move behind the ABI.
+		return groth16_bn254.Prove(r1cs, &pk.ProvingKey, fullWitness, opts...)
+	}
+	if err := pk.setupDevicePointers(); err != nil {
+		return nil, err
+	}
+	_solution, err := r1cs.Solve(fullWitness, opt.SolverOpts...)
+	if err != nil {
+		return nil, err
+	}
+	solution := _solution.(*cs.R1CSSolution)
+	start := time.Now()
+
+	var out [C.G16_PROVE_OUT_BYTES]byte
+	var stats C.g16_stats
+	var pin runtime.Pinner
+	pin.Pin(&solution.W[0])
+	pin.Pin(&solution.A[0])
+	pin.Pin(&solution.B[0])
+	pin.Pin(&solution.C[0])
+	rc := C.g16_prove_bn254(pk.ctx, C.uint64_t(pk.handle), unsafe.Pointer(&solution.W[0]), C.uint64_t(len(solution.W)),
+		unsafe.Pointer(&solution.A[0]), unsafe.Pointer(&solution.B[0]), unsafe.Pointer(&solution.C[0]),
+		C.uint64_t(len(solution.A)), unsafe.Pointer(&out[0]), &stats)
+	pin.Unpin()
+	if rc != 0 {
+		return nil, lastError(pk.ctx, "g16_prove_bn254")
+	}
+	// the five raw MSM results are gnark memory images
+	arMsm := *(*curve.G1Affine)(unsafe.Pointer(&out[0]))
+	bs1Msm := *(*curve.G1Affine)(unsafe.Pointer(&out[64]))
+	krsK := *(*curve.G1Affine)(unsafe.Pointer(&out[128]))
+	krsHZ := *(*curve.G1Affine)(unsafe.Pointer(&out[192]))
+	bs2Msm := *(*curve.G2Affine)(unsafe.Pointer(&out[256]))
+
+	// epilogue: r, s, kr = -r*s; deltas = [r, s, kr] * delta
+	var _r, _s, _kr fr.Element
+	if _, err := _r.SetRandom(); err != nil {
+		return nil, err
+	}
+	if _, err := _s.SetRandom(); err != nil {
+		return nil, err
+	}
+	_kr.Mul(&_r, &_s).Neg(&_kr)
+	var r, s big.Int
+	_r.BigInt(&r)
+	_s.BigInt(&s)
+	deltas := curve.BatchScalarMultiplicationG1(&pk.G1.Delta, []fr.Element{_r, _s, _kr})
+
+	proof := &groth16_bn254.Proof{}
+	var ar, bs1, krs, p1 curve.G1Jac
+	ar.FromAffine(&arMsm)
+	ar.AddMixed(&pk.G1.Alpha)
+	ar.AddMixed(&deltas[0])
+	proof.Ar.FromJacobian(&ar)
+	bs1.FromAffine(&bs1Msm)
+	bs1.AddMixed(&pk.G1.Beta)
+	bs1.AddMixed(&deltas[1])
+	krs.FromAffine(&krsK)
+	krs.AddMixed(&deltas[2])
+	krs.AddMixed(&krsHZ)
+	p1.ScalarMultiplication(&ar, &s)
+	krs.AddAssign(&p1)
+	p1.ScalarMultiplication(&bs1, &r)
+	krs.AddAssign(&p1)
+	proof.Krs.FromJacobian(&krs)
+
+	var bs, deltaS curve.G2Jac
+	bs.FromAffine(&bs2Msm)
+	deltaS.FromAffine(&pk.G2.Delta)
+	deltaS.ScalarMultiplication(&deltaS, &s)
+	bs.AddAssign(&deltaS)
+	bs.AddMixed(&pk.G2.Beta)
+	proof.Bs.FromJacobian(&bs)
+
+	log.Debug().Dur("took", time.Since(start)).Float32("device_ms", float32(stats.ms_total)).Msg("prover done")
+	return proof, nil
+}
