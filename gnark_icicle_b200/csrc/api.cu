@@ -35,6 +35,9 @@ struct PkDev {
 struct g16_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t aux[4] = {};   // the MSMs that do not depend on h
+    cudaStream_t tails[5] = {}; // high-priority streams for the latency-bound MSM tails
+    int streams = 5;
     cudaEvent_t ev[32] = {};
     std::string err;
     std::map<int, NttDomain> domains;
@@ -100,7 +103,12 @@ int g16_ctx_create(g16_ctx** out, int curve_id, const int* device_ids, int n_dev
         c->device = (device_ids && n_devices == 1) ? device_ids[0] : 0;
         G16_CUDA(cudaSetDevice(c->device));
         G16_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+        for (auto& a : c->aux) G16_CUDA(cudaStreamCreateWithFlags(&a, cudaStreamNonBlocking));
+        int prio_lo = 0, prio_hi = 0;
+        G16_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+        for (auto& t : c->tails) G16_CUDA(cudaStreamCreateWithPriority(&t, cudaStreamNonBlocking, prio_hi));
         for (auto& e : c->ev) G16_CUDA(cudaEventCreate(&e));
+        if (const char* e = getenv("G16_STREAMS")) c->streams = atoi(e);
         if (const char* e = getenv("G16_MSM_C")) c->msm_c = atoi(e);
         if (const char* e = getenv("G16_MSM_WAVES")) c->msm_waves = atoi(e);
     } catch (const std::exception& e) {
@@ -121,6 +129,8 @@ void g16_ctx_destroy(g16_ctx* ctx) {
     for (auto& s : ctx->stage) s.release();
     ctx->fb_table_g1.release(); ctx->fb_table_g2.release();
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
+    for (auto& a : ctx->aux) if (a) cudaStreamDestroy(a);
+    for (auto& t : ctx->tails) if (t) cudaStreamDestroy(t);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -132,6 +142,7 @@ int g16_ctx_set(g16_ctx* ctx, const char* key, int64_t value) {
     std::string k(key);
     if (k == "msm_c") ctx->msm_c = (int)value;
     else if (k == "msm_waves") ctx->msm_waves = (int)value;
+    else if (k == "streams") ctx->streams = (int)value;
     else { ctx->err = "unknown tunable " + k; return 1; }
     return 0;
 }
@@ -221,26 +232,47 @@ template <class Aff>
 void copy_out(void* dst, const Aff& p) { memcpy(dst, &p, sizeof(Aff)); }
 
 void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* b_d, Fr::T* c_d, void* out_points,
-                  g16_stats* stats, uint64_t launches0) {
+                  g16_stats* stats, uint64_t launches0, cudaEvent_t w_ready) {
     cudaStream_t st = ctx->stream;
     NttDomain& dom = ctx->domain(pk.logn);
     cudaEvent_t* ev = ctx->ev;
     MsmPlan plan[5];
     MsmStats ms[5];
     for (int i = 0; i < 5; i++) { ms[i].acc_begin = ev[16 + 2 * i]; ms[i].acc_end = ev[17 + 2 * i]; }
+    // The four MSMs over W do not depend on h: with overlap on they run on their own streams next to computeH
+    // (the reference serialises everything, icicle.go:396-410); the sort/reduce tails of one MSM then hide
+    // under the accumulation of another.  Order of issue: G2 first (longest).
+    const bool overlap = ctx->streams > 1;
+    cudaStream_t sA = overlap ? ctx->aux[0] : st, sB = overlap ? ctx->aux[1] : st, sK = overlap ? ctx->aux[2] : st,
+                 s2 = overlap ? ctx->aux[3] : st;
     G16_CUDA(cudaEventRecord(ev[0], st));
+    if (overlap) {
+        cudaEvent_t ready = w_ready ? w_ready : ev[0];
+        for (int i = 0; i < 4; i++) G16_CUDA(cudaStreamWaitEvent(ctx->aux[i], ready, 0));
+    }
+    auto run = [&](int idx, cudaStream_t s, auto&& fn) {
+        G16_CUDA(cudaEventRecord(ev[1 + idx], s));
+        fn(s);
+        G16_CUDA(cudaEventRecord(ev[6 + idx], s));
+    };
+    run(G16_OUT_BS2, s2, [&](cudaStream_t s) {
+        msm_g2_enqueue(ctx->ws[G16_OUT_BS2], W_d, pk.map_b.as<uint32_t>(), pk.g2_b.as<G2::Aff>(), pk.n_b2, ctx->msm_c, ctx->msm_waves, s, plan[4], &ms[4], overlap ? ctx->tails[4] : nullptr); });
+    G16_CUDA(cudaEventRecord(ev[12], st));
     compute_h_device(dom, a_d, b_d, c_d, st);                 // h (bit-reversed) in a_d
-    G16_CUDA(cudaEventRecord(ev[1], st));
-    msm_g1_enqueue(ctx->ws[G16_OUT_AR], W_d, pk.map_a.as<uint32_t>(), pk.g1_a.as<G1::Aff>(), pk.n_a, ctx->msm_c, ctx->msm_waves, st, plan[0], &ms[0]);
-    G16_CUDA(cudaEventRecord(ev[2], st));
-    msm_g1_enqueue(ctx->ws[G16_OUT_BS1], W_d, pk.map_b.as<uint32_t>(), pk.g1_b.as<G1::Aff>(), pk.n_b, ctx->msm_c, ctx->msm_waves, st, plan[1], &ms[1]);
-    G16_CUDA(cudaEventRecord(ev[3], st));
-    msm_g1_enqueue(ctx->ws[G16_OUT_KRS_K], W_d, pk.map_k.as<uint32_t>(), pk.g1_k.as<G1::Aff>(), pk.n_k, ctx->msm_c, ctx->msm_waves, st, plan[2], &ms[2]);
-    G16_CUDA(cudaEventRecord(ev[4], st));
-    msm_g1_enqueue(ctx->ws[G16_OUT_KRS_HZ], a_d + pk.z_off, nullptr, pk.g1_z.as<G1::Aff>(), pk.n_z, ctx->msm_c, ctx->msm_waves, st, plan[3], &ms[3]);
-    G16_CUDA(cudaEventRecord(ev[5], st));
-    msm_g2_enqueue(ctx->ws[G16_OUT_BS2], W_d, pk.map_b.as<uint32_t>(), pk.g2_b.as<G2::Aff>(), pk.n_b2, ctx->msm_c, ctx->msm_waves, st, plan[4], &ms[4]);
-    G16_CUDA(cudaEventRecord(ev[6], st));
+    G16_CUDA(cudaEventRecord(ev[13], st));
+    run(G16_OUT_AR, sA, [&](cudaStream_t s) {
+        msm_g1_enqueue(ctx->ws[G16_OUT_AR], W_d, pk.map_a.as<uint32_t>(), pk.g1_a.as<G1::Aff>(), pk.n_a, ctx->msm_c, ctx->msm_waves, s, plan[0], &ms[0], overlap ? ctx->tails[0] : nullptr); });
+    run(G16_OUT_KRS_HZ, st, [&](cudaStream_t s) {
+        msm_g1_enqueue(ctx->ws[G16_OUT_KRS_HZ], a_d + pk.z_off, nullptr, pk.g1_z.as<G1::Aff>(), pk.n_z, ctx->msm_c, ctx->msm_waves, s, plan[3], &ms[3], overlap ? ctx->tails[3] : nullptr); });
+    run(G16_OUT_BS1, sB, [&](cudaStream_t s) {
+        msm_g1_enqueue(ctx->ws[G16_OUT_BS1], W_d, pk.map_b.as<uint32_t>(), pk.g1_b.as<G1::Aff>(), pk.n_b, ctx->msm_c, ctx->msm_waves, s, plan[1], &ms[1], overlap ? ctx->tails[1] : nullptr); });
+    run(G16_OUT_KRS_K, sK, [&](cudaStream_t s) {
+        msm_g1_enqueue(ctx->ws[G16_OUT_KRS_K], W_d, pk.map_k.as<uint32_t>(), pk.g1_k.as<G1::Aff>(), pk.n_k, ctx->msm_c, ctx->msm_waves, s, plan[2], &ms[2], overlap ? ctx->tails[2] : nullptr); });
+    if (overlap) {
+        const int aux_of[4] = {G16_OUT_AR, G16_OUT_BS1, G16_OUT_KRS_K, G16_OUT_BS2};
+        for (int i = 0; i < 4; i++) G16_CUDA(cudaStreamWaitEvent(st, ev[6 + aux_of[i]], 0));
+    }
+    G16_CUDA(cudaEventRecord(ev[14], st));
     G16_CUDA(cudaStreamSynchronize(st));
     auto t0 = std::chrono::steady_clock::now();
     char* out = (char*)out_points;
@@ -249,13 +281,13 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
     copy_out(out + 256, ns[4] ? msm_g2_finish(ctx->ws[4], plan[4]) : G2::aff_inf());
     auto t1 = std::chrono::steady_clock::now();
     if (stats) {
-        G16_CUDA(cudaEventElapsedTime(&stats->ms_compute_h, ev[0], ev[1]));
+        G16_CUDA(cudaEventElapsedTime(&stats->ms_compute_h, ev[12], ev[13]));
         for (int i = 0; i < 5; i++) {
-            G16_CUDA(cudaEventElapsedTime(&stats->ms_msm[i], ev[1 + i], ev[2 + i]));
+            G16_CUDA(cudaEventElapsedTime(&stats->ms_msm[i], ev[1 + i], ev[6 + i]));
             stats->msm_c[i] = plan[i].c; stats->msm_windows[i] = plan[i].W; stats->msm_n[i] = ns[i];
             if (ns[i]) G16_CUDA(cudaEventElapsedTime(&stats->ms_accumulate[i], ev[16 + 2 * i], ev[17 + 2 * i]));
         }
-        G16_CUDA(cudaEventElapsedTime(&stats->ms_total, ev[0], ev[6]));
+        G16_CUDA(cudaEventElapsedTime(&stats->ms_total, ev[0], ev[14]));
         stats->ms_host = std::chrono::duration<float, std::milli>(t1 - t0).count();
         stats->d2h_bytes = 0;
         for (int i = 0; i < 5; i++) stats->d2h_bytes += (uint64_t)plan[i].W * (i == 4 ? sizeof(G2::Xyzz) : sizeof(G1::Xyzz));
@@ -273,7 +305,7 @@ extern "C" int g16_prove_bn254_dev(g16_ctx* ctx, uint64_t pk_handle, const void*
         if (!W_d || !a_d || !b_d || !c_d || !out_points) throw std::runtime_error("null argument");
         uint64_t l0 = launch_counter().load();
         if (stats) memset(stats, 0, sizeof(*stats));
-        prove_device(ctx, it->second, (const Fr::T*)W_d, (Fr::T*)a_d, (Fr::T*)b_d, (Fr::T*)c_d, out_points, stats, l0);
+        prove_device(ctx, it->second, (const Fr::T*)W_d, (Fr::T*)a_d, (Fr::T*)b_d, (Fr::T*)c_d, out_points, stats, l0, nullptr);
     });
 }
 
@@ -290,21 +322,23 @@ extern "C" int g16_prove_bn254(g16_ctx* ctx, uint64_t pk_handle, const void* W, 
         if (stats) memset(stats, 0, sizeof(*stats));
         cudaStream_t st = ctx->stream;
         const size_t nb = (size_t)pk.domain_n * 32, cb = (size_t)n_constraints * 32;
-        G16_CUDA(cudaEventRecord(ctx->ev[8], st));
+        G16_CUDA(cudaEventRecord(ctx->ev[26], st));
+        // W first: the four MSMs over W start on their own streams while a, b, c are still in flight
+        ctx->stage[3].reserve((size_t)n_wires * 32);
+        G16_CUDA(cudaMemcpyAsync(ctx->stage[3].p, W, (size_t)n_wires * 32, cudaMemcpyHostToDevice, st));
+        G16_CUDA(cudaEventRecord(ctx->ev[15], st));
         const void* src[3] = {a, b, c};
         for (int i = 0; i < 3; i++) {      // pad to the domain size (icicle.go:463-467)
             ctx->stage[i].reserve(nb);
             G16_CUDA(cudaMemcpyAsync(ctx->stage[i].p, src[i], cb, cudaMemcpyHostToDevice, st));
             if (nb > cb) G16_CUDA(cudaMemsetAsync((char*)ctx->stage[i].p + cb, 0, nb - cb, st));
         }
-        ctx->stage[3].reserve((size_t)n_wires * 32);
-        G16_CUDA(cudaMemcpyAsync(ctx->stage[3].p, W, (size_t)n_wires * 32, cudaMemcpyHostToDevice, st));
-        G16_CUDA(cudaEventRecord(ctx->ev[9], st));
+        G16_CUDA(cudaEventRecord(ctx->ev[27], st));
         prove_device(ctx, pk, ctx->stage[3].as<Fr::T>(), ctx->stage[0].as<Fr::T>(), ctx->stage[1].as<Fr::T>(),
-                     ctx->stage[2].as<Fr::T>(), out_points, stats, l0);
+                     ctx->stage[2].as<Fr::T>(), out_points, stats, l0, ctx->ev[15]);
         if (stats) {
-            G16_CUDA(cudaEventElapsedTime(&stats->ms_h2d, ctx->ev[8], ctx->ev[9]));
-            stats->ms_total += stats->ms_h2d;
+            G16_CUDA(cudaEventElapsedTime(&stats->ms_h2d, ctx->ev[26], ctx->ev[27]));
+            G16_CUDA(cudaEventElapsedTime(&stats->ms_total, ctx->ev[26], ctx->ev[14]));
             stats->h2d_bytes = 3 * cb + (uint64_t)n_wires * 32;
         }
     });

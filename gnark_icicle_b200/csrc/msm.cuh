@@ -27,7 +27,11 @@ namespace g16 {
 struct MsmWorkspace {
     DevBuf digits, sorted, counts, offsets, cursor, buckets, head, tail, partial, wsum, scan_tmp;
     PinnedBuf host_wsum;
+    cudaEvent_t acc_done = nullptr, tail_done = nullptr;
     void release() {
+        if (acc_done) cudaEventDestroy(acc_done);
+        if (tail_done) cudaEventDestroy(tail_done);
+        acc_done = tail_done = nullptr;
         digits.release(); sorted.release(); counts.release(); offsets.release(); cursor.release();
         buckets.release(); head.release(); tail.release(); partial.release(); wsum.release(); host_wsum.release(); scan_tmp.release();
     }
@@ -368,7 +372,8 @@ struct MsmStats { int c = 0, W = 0; uint32_t acc_threads = 0; cudaEvent_t acc_be
 // Enqueues the whole MSM on `st`; window sums land in ws.host_wsum (pinned) after the stream drains.
 template <class C, int ACC_THREADS, int ACC_MINB>
 void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const typename C::Aff* bases_d,
-                 uint64_t n, int force_c, int waves, cudaStream_t st, MsmPlan& plan_out, MsmStats* stats) {
+                 uint64_t n, int force_c, int waves, cudaStream_t st, MsmPlan& plan_out, MsmStats* stats,
+                 cudaStream_t tail = nullptr) {
     typedef typename C::Xyzz Xyzz;
     constexpr bool IS_G2 = sizeof(typename C::Aff) > 64;
     MsmPlan pl = msm_plan(n, force_c, IS_G2);
@@ -438,6 +443,15 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
         bases_d, sorted, offsets, pl.NB, nthreads, buckets, ws.head.as<Xyzz>(), ws.tail.as<Xyzz>());
     G16_LAUNCH_CHECK();
     if (stats && stats->acc_end) G16_CUDA(cudaEventRecord(stats->acc_end, st));
+    // the latency-bound tail (stitch, bucket reduction, window sums) may run on a high-priority stream so that it
+    // slips in between the CTAs of whatever big kernel another MSM has in flight
+    if (tail && tail != st) {
+        if (!ws.acc_done) { G16_CUDA(cudaEventCreateWithFlags(&ws.acc_done, cudaEventDisableTiming)); G16_CUDA(cudaEventCreateWithFlags(&ws.tail_done, cudaEventDisableTiming)); }
+        G16_CUDA(cudaEventRecord(ws.acc_done, st));
+        G16_CUDA(cudaStreamWaitEvent(tail, ws.acc_done, 0));
+    }
+    cudaStream_t main_st = st;
+    if (tail) st = tail;
     k_fixup<C><<<(pl.NB + 127) / 128, 128, 0, st>>>(offsets, pl.NB, nthreads, buckets, ws.head.as<Xyzz>(), ws.tail.as<Xyzz>());
     G16_LAUNCH_CHECK();
     dim3 rgrid(pl.red_rb, pl.W);
@@ -446,6 +460,10 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
     k_window_sum<C><<<pl.W, 32, 0, st>>>(ws.partial.as<Xyzz>(), pl.red_rb, ws.wsum.as<Xyzz>());
     G16_LAUNCH_CHECK();
     G16_CUDA(cudaMemcpyAsync(ws.host_wsum.p, ws.wsum.p, (size_t)pl.W * sizeof(Xyzz), cudaMemcpyDeviceToHost, st));
+    if (st != main_st) {   // the MSM's own stream completes when its tail does
+        G16_CUDA(cudaEventRecord(ws.tail_done, st));
+        G16_CUDA(cudaStreamWaitEvent(main_st, ws.tail_done, 0));
+    }
     if (stats) stats->acc_threads = nthreads;
 }
 

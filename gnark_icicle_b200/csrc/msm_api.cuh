@@ -5,10 +5,10 @@
 namespace g16 {
 
 void msm_g1_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const G1::Aff* bases_d, uint64_t n,
-                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats);
+                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail = nullptr);
 G1::Aff msm_g1_finish(const MsmWorkspace& ws, const MsmPlan& plan);
 void msm_g2_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const G2::Aff* bases_d, uint64_t n,
-                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats);
+                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail = nullptr);
 G2::Aff msm_g2_finish(const MsmWorkspace& ws, const MsmPlan& plan);
 
 // out[i] = [scalars[i]] * G (generator), affine Montgomery.  Setup-side tooling: the device analogue of

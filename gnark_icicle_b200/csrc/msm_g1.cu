@@ -5,8 +5,8 @@
 namespace g16 {
 
 void msm_g1_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const G1::Aff* bases_d, uint64_t n,
-                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats) {
-    msm_enqueue<G1, 128, 4>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats);
+                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail) {
+    msm_enqueue<G1, 128, 4>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail);
 }
 G1::Aff msm_g1_finish(const MsmWorkspace& ws, const MsmPlan& plan) { return msm_finish<G1>(ws, plan); }
 

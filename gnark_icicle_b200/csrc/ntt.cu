@@ -24,7 +24,7 @@ int ntt_log_tile() {
     return v;
 }
 int ntt_log_cols() {
-    static int v = [] { const char* e = getenv("G16_NTT_LOG_COLS"); int x = e ? atoi(e) : 1; return x < 0 ? 0 : (x > 3 ? 3 : x); }();
+    static int v = [] { const char* e = getenv("G16_NTT_LOG_COLS"); int x = e ? atoi(e) : 2; return x < 0 ? 0 : (x > 3 ? 3 : x); }();
     return v;
 }
 
