@@ -198,7 +198,11 @@ extern "C" int g16_pk_upload(g16_ctx* ctx, const g16_pk_desc* d, uint64_t* pk_ha
         upload(pk.g1_k, (const char*)d->g1_k + lo * 64, pk.n_k * 64, st);
         upload(pk.map_k, mk.data() + lo, pk.n_k * 4, st);
         uint64_t nz = d->n_z < d->domain_n ? d->n_z : d->domain_n - 1;   // h[:n-1] (prove.go:235-237)
-        slice(nz, si, sc, lo, hi);
+        // Z follows the block distribution of h over the domain (so a distributed computeH leaves each rank's
+        // block of h exactly under its Z slice); the last block loses the dropped degree-(n-1) coefficient
+        slice(d->domain_n, si, sc, lo, hi);
+        if (lo > nz) lo = nz;
+        if (hi > nz) hi = nz;
         pk.n_z = hi - lo;
         pk.z_off = lo;
         upload(pk.g1_z, (const char*)d->g1_z + lo * 64, pk.n_z * 64, st);
@@ -232,7 +236,7 @@ template <class Aff>
 void copy_out(void* dst, const Aff& p) { memcpy(dst, &p, sizeof(Aff)); }
 
 void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* b_d, Fr::T* c_d, void* out_points,
-                  g16_stats* stats, uint64_t launches0, cudaEvent_t w_ready) {
+                  g16_stats* stats, uint64_t launches0, cudaEvent_t w_ready, bool h_given = false) {
     cudaStream_t st = ctx->stream;
     NttDomain& dom = ctx->domain(pk.logn);
     cudaEvent_t* ev = ctx->ev;
@@ -258,12 +262,12 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
     run(G16_OUT_BS2, s2, [&](cudaStream_t s) {
         msm_g2_enqueue(ctx->ws[G16_OUT_BS2], W_d, pk.map_b.as<uint32_t>(), pk.g2_b.as<G2::Aff>(), pk.n_b2, ctx->msm_c, ctx->msm_waves, s, plan[4], &ms[4], overlap ? ctx->tails[4] : nullptr); });
     G16_CUDA(cudaEventRecord(ev[12], st));
-    compute_h_device(dom, a_d, b_d, c_d, st);                 // h (bit-reversed) in a_d
+    if (!h_given) compute_h_device(dom, a_d, b_d, c_d, st);   // h (bit-reversed) in a_d; h_given: a_d is this shard's block of h
     G16_CUDA(cudaEventRecord(ev[13], st));
     run(G16_OUT_AR, sA, [&](cudaStream_t s) {
         msm_g1_enqueue(ctx->ws[G16_OUT_AR], W_d, pk.map_a.as<uint32_t>(), pk.g1_a.as<G1::Aff>(), pk.n_a, ctx->msm_c, ctx->msm_waves, s, plan[0], &ms[0], overlap ? ctx->tails[0] : nullptr); });
     run(G16_OUT_KRS_HZ, st, [&](cudaStream_t s) {
-        msm_g1_enqueue(ctx->ws[G16_OUT_KRS_HZ], a_d + pk.z_off, nullptr, pk.g1_z.as<G1::Aff>(), pk.n_z, ctx->msm_c, ctx->msm_waves, s, plan[3], &ms[3], overlap ? ctx->tails[3] : nullptr); });
+        msm_g1_enqueue(ctx->ws[G16_OUT_KRS_HZ], a_d + (h_given ? 0 : pk.z_off), nullptr, pk.g1_z.as<G1::Aff>(), pk.n_z, ctx->msm_c, ctx->msm_waves, s, plan[3], &ms[3], overlap ? ctx->tails[3] : nullptr); });
     run(G16_OUT_BS1, sB, [&](cudaStream_t s) {
         msm_g1_enqueue(ctx->ws[G16_OUT_BS1], W_d, pk.map_b.as<uint32_t>(), pk.g1_b.as<G1::Aff>(), pk.n_b, ctx->msm_c, ctx->msm_waves, s, plan[1], &ms[1], overlap ? ctx->tails[1] : nullptr); });
     run(G16_OUT_KRS_K, sK, [&](cudaStream_t s) {
@@ -722,3 +726,50 @@ extern "C" int g16_pipe_rates(g16_ctx* ctx, double* out2) {
                           (double)blocks * 256 * it2 * 4);
     });
 }
+
+
+// =================================================================== distributed computeH building blocks + MSM-only prove
+extern "C" {
+
+int g16_dist_ntt_stages_dev(g16_ctx* ctx, void* data_d, int count, uint64_t n_global, int world, int rank, int table, int dif,
+                            int cyclic, int split) {
+    return guarded(ctx, [&] {
+        if (!is_pow2(n_global) || world < 1 || (world & (world - 1)) || count < 1 || count > 3 || table < 0 || table > 3)
+            throw std::runtime_error("g16_dist_ntt_stages_dev: bad arguments");
+        int g = ilog2_ceil((uint64_t)world);
+        NttDomain& d = ctx->domain(ilog2_ceil(n_global));
+        uint64_t n_local = n_global >> g;
+        Fr::T* p = (Fr::T*)data_d;
+        NttBatch b{{p, p + (count > 1 ? n_local : 0), p + (count > 2 ? 2 * n_local : 0)}, count};
+        ntt_dist_stages(d, b, (NttTable)table, dif != 0, g, (uint32_t)rank, cyclic != 0, split, ctx->stream);
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+int g16_dist_permute_dev(g16_ctx* ctx, const void* src_d, void* dst_d, int count, uint64_t n_local, int world, int block_layout, int to_wire) {
+    return guarded(ctx, [&] {
+        if (world < 1 || n_local % (uint64_t)world) throw std::runtime_error("g16_dist_permute_dev: n_local must be a multiple of world");
+        ntt_dist_permute((const Fr::T*)src_d, (Fr::T*)dst_d, count, n_local, (uint32_t)world, block_layout, to_wire, ctx->stream);
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+int g16_dist_pointwise_h_dev(g16_ctx* ctx, void* abc_d, uint64_t n_local, uint64_t n_global) {
+    return guarded(ctx, [&] {
+        if (!is_pow2(n_global)) throw std::runtime_error("bad domain size");
+        NttDomain& d = ctx->domain(ilog2_ceil(n_global));
+        Fr::T* p = (Fr::T*)abc_d;
+        fr_pointwise_h(p, p + n_local, p + 2 * n_local, n_local, d.h_c1, d.h_c2, ctx->stream);
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+int g16_prove_msms_dev(g16_ctx* ctx, uint64_t pk_handle, const void* W_d, const void* h_local_d, void* out_points, g16_stats* stats) {
+    return guarded(ctx, [&] {
+        auto it = ctx->pks.find(pk_handle);
+        if (it == ctx->pks.end()) throw std::runtime_error("unknown proving-key handle");
+        if (!W_d || !h_local_d || !out_points) throw std::runtime_error("null argument");
+        uint64_t l0 = launch_counter().load();
+        if (stats) memset(stats, 0, sizeof(*stats));
+        prove_device(ctx, it->second, (const Fr::T*)W_d, (Fr::T*)h_local_d, nullptr, nullptr, out_points, stats, l0, nullptr, true);
+    });
+}
+
+}  // extern "C"

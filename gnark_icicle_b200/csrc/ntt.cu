@@ -106,6 +106,8 @@ struct PassArgs {
     int s;   // log2 of the row stride (= log2 of the smallest half-size handled by this sweep)
     int k;   // stages in this sweep (tile rows = 2^k)
     int cb;  // log2 of tile columns
+    int g;   // cyclic-distributed sweeps: log2(world); local index q stands for global position q*2^g + rank
+    uint32_t rank;
 };
 
 __device__ __forceinline__ Fr::T ld_planes(const uint4* lo, const uint4* hi, int e) {
@@ -153,7 +155,7 @@ __global__ void __launch_bounds__(NTT_THREADS) k_ntt_pass(PassArgs a) {
     for (int st = 0; st < k; st++) {
         const int m = DIF ? (k - 1 - st) : st;
         const int mmask = (1 << m) - 1;
-        const Fr::T* tws = a.tw + ((1ull << (m + s)) - 1);
+        const Fr::T* tws = a.tw + ((1ull << (m + s + a.g)) - 1);
         for (int bi = threadIdx.x; bi < nb; bi += NTT_THREADS) {
             int c = bi & cmask, rb = bi >> cb;
             int r0 = ((rb >> m) << (m + 1)) | (rb & mmask);
@@ -161,7 +163,7 @@ __global__ void __launch_bounds__(NTT_THREADS) k_ntt_pass(PassArgs a) {
             int e1 = e0 + (1 << (m + cb));
             uint64_t q = qbase + c;
             uint64_t j = ((uint64_t)(r0 & mmask) << s) | (q & smask);
-            Fr::T t = ldg_fr(tws + j);
+            Fr::T t = ldg_fr(tws + ((j << a.g) | a.rank));
             Fr::T u = ld_planes(lo, hi, e0), v = ld_planes(lo, hi, e1);
             if (DIF) {
                 st_planes(lo, hi, e0, Fr::add(u, v));
@@ -187,43 +189,38 @@ __global__ void __launch_bounds__(NTT_THREADS) k_ntt_pass(PassArgs a) {
 
 struct Sweep { int s, k, cb; };
 
-static std::vector<Sweep> plan_sweeps(int logn) {
+// sweeps covering the stages whose (local) log2 half-size lies in [lo, hi), bottom-up
+static std::vector<Sweep> plan_range(int lo, int hi) {
     std::vector<Sweep> v;
-    if (logn == 0) return v;
+    const int nst = hi - lo;
+    if (nst <= 0) return v;
     const int LT = ntt_log_tile();
-    int k0 = logn < LT ? logn : LT;
-    int rem = logn - k0;
-    if (rem == 0) { v.push_back({0, k0, 0}); return v; }
-    int cb = ntt_log_cols();
-    int kmax = LT - cb;
-    int np = (rem + kmax - 1) / kmax;
-    // balance: spread all logn stages over np+1 sweeps, contiguous sweep may take up to LT
-    int total = np + 1;
-    int base = logn / total, extra = logn % total;
-    std::vector<int> ks(total, base);
-    for (int i = 0; i < extra; i++) ks[i]++;
-    // the contiguous sweep (index 0) may be as large as LT; strided ones at most kmax
-    for (int i = 1; i < total; i++) while (ks[i] > kmax) { ks[i]--; ks[0]++; }
-    int s = 0;
+    if (lo == 0 && nst <= LT) { v.push_back({0, nst, 0}); return v; }
+    const int cb = ntt_log_cols();
+    const int kmax = LT - cb;
+    const int total = (nst + kmax - 1) / kmax;
+    std::vector<int> ks(total, nst / total);
+    for (int i = 0; i < nst % total; i++) ks[i]++;
+    int s = lo;
     for (int i = 0; i < total; i++) {
-        int c = (i == 0) ? 0 : cb;
-        if (c > s) c = s;                       // keep a tile row contiguous in memory
+        int c = cb < s ? cb : s;                // keep a tile row contiguous in memory
         while (ks[i] + c > LT) c--;
         v.push_back({s, ks[i], c});
         s += ks[i];
     }
     return v;
 }
+static std::vector<Sweep> plan_sweeps(int logn) { return plan_range(0, logn); }
 
 template <bool DIF>
-static void launch_sweep(NttDomain& d, const NttBatch& b, const Fr::T* tw, const Sweep& sw, cudaStream_t st) {
+static void launch_sweep(uint64_t n_local, const NttBatch& b, const Fr::T* tw, const Sweep& sw, cudaStream_t st, int g = 0, uint32_t rank = 0) {
     PassArgs a;
     for (int i = 0; i < 3; i++) a.p[i] = b.p[i < b.count ? i : 0];
-    a.tw = tw; a.s = sw.s; a.k = sw.k; a.cb = sw.cb;
+    a.tw = tw; a.s = sw.s; a.k = sw.k; a.cb = sw.cb; a.g = g; a.rank = rank;
     size_t smem = (size_t)2 * sizeof(uint4) << (sw.k + sw.cb);
     if (smem > 48 * 1024)
         G16_CUDA(cudaFuncSetAttribute(k_ntt_pass<DIF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    uint64_t gx = (d.n >> sw.k) >> sw.cb;
+    uint64_t gx = (n_local >> sw.k) >> sw.cb;
     dim3 grid((unsigned)gx, (unsigned)b.count);
     k_ntt_pass<DIF><<<grid, NTT_THREADS, smem, st>>>(a);
     G16_LAUNCH_CHECK();
@@ -233,13 +230,13 @@ void ntt_dif(NttDomain& d, const NttBatch& b, NttTable t, cudaStream_t st) {
     if (d.logn == 0) return;
     const Fr::T* tw = d.table(t, st);
     std::vector<Sweep> v = plan_sweeps(d.logn);
-    for (int i = (int)v.size() - 1; i >= 0; i--) launch_sweep<true>(d, b, tw, v[i], st);
+    for (int i = (int)v.size() - 1; i >= 0; i--) launch_sweep<true>(d.n, b, tw, v[i], st);
 }
 void ntt_dit(NttDomain& d, const NttBatch& b, NttTable t, cudaStream_t st) {
     if (d.logn == 0) return;
     const Fr::T* tw = d.table(t, st);
     std::vector<Sweep> v = plan_sweeps(d.logn);
-    for (size_t i = 0; i < v.size(); i++) launch_sweep<false>(d, b, tw, v[i], st);
+    for (size_t i = 0; i < v.size(); i++) launch_sweep<false>(d.n, b, tw, v[i], st);
 }
 
 // ------------------------------------------------------------------ element-wise kernels
@@ -287,6 +284,43 @@ void fr_mul_vec(Fr::T* out, const Fr::T* a, const Fr::T* b, uint64_t n, cudaStre
     unsigned blocks = (unsigned)((n + 255) / 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
     k_mul_vec<<<blocks, 256, 0, st>>>(out, a, b, n);
+    G16_LAUNCH_CHECK();
+}
+
+// ------------------------------------------------------------------ distributed transforms (SURVEY.md 8(e) level 3)
+// A size-n transform over G = 2^g ranks is split at a global stage X: stages with half-size >= 2^X run on the
+// CYCLIC distribution (rank r holds positions q*G + r; pairs stay local because the half-size is a multiple of G),
+// stages below X run on the BLOCK distribution (rank r holds [r n/G, (r+1) n/G)).  One all-to-all between the two
+// (the four-step transpose) -- the twiddles need no extra pass because every stage has its own table.
+void ntt_dist_stages(NttDomain& d, const NttBatch& b, NttTable t, bool dif, int world_log, uint32_t rank, bool cyclic, int split, cudaStream_t st) {
+    const Fr::T* tw = d.table(t, st);
+    const int L = d.logn, g = world_log, Ll = L - g;
+    if (split < g || split > Ll) throw std::runtime_error("distributed NTT: split stage must lie in [log2(world), log2(n/world)]");
+    const uint64_t n_local = d.n >> g;
+    std::vector<Sweep> v = cyclic ? plan_range(split - g, Ll) : plan_range(0, split);
+    if (dif) for (int i = (int)v.size() - 1; i >= 0; i--) launch_sweep<true>(n_local, b, tw, v[i], st, cyclic ? g : 0, cyclic ? rank : 0);
+    else for (size_t i = 0; i < v.size(); i++) launch_sweep<false>(n_local, b, tw, v[i], st, cyclic ? g : 0, cyclic ? rank : 0);
+}
+
+// wire layout of an all-to-all: [peer x][array][q'], q' < m = n_local / G.
+//   cyclic-local index of (x, q') = x*m + q'      block-local index of (x, q') = q'*G + x
+__global__ void k_dist_permute(const uint4* __restrict__ src, uint4* __restrict__ dst, int count, uint64_t n_local, uint32_t G,
+                               int block_layout, int to_wire) {
+    const uint64_t m = n_local / G, total = (uint64_t)count * n_local;
+    for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (uint64_t)gridDim.x * blockDim.x) {
+        uint64_t qp = e % m, rest = e / m;
+        uint32_t arr = (uint32_t)(rest % count), x = (uint32_t)(rest / count);
+        uint64_t local = (uint64_t)arr * n_local + (block_layout ? qp * G + x : (uint64_t)x * m + qp);
+        uint64_t from = to_wire ? local : e, to = to_wire ? e : local;
+        dst[2 * to] = src[2 * from];
+        dst[2 * to + 1] = src[2 * from + 1];
+    }
+}
+void ntt_dist_permute(const Fr::T* src, Fr::T* dst, int count, uint64_t n_local, uint32_t world, int block_layout, int to_wire, cudaStream_t st) {
+    uint64_t total = (uint64_t)count * n_local;
+    unsigned blocks = (unsigned)((total + 255) / 256);
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    k_dist_permute<<<blocks, 256, 0, st>>>(reinterpret_cast<const uint4*>(src), reinterpret_cast<uint4*>(dst), count, n_local, world, block_layout, to_wire);
     G16_LAUNCH_CHECK();
 }
 

@@ -47,6 +47,10 @@ void fr_pointwise_h(Fr::T* a, const Fr::T* b, const Fr::T* c, uint64_t n, const 
 void compute_h_device(NttDomain& d, Fr::T* a, Fr::T* b, Fr::T* c, cudaStream_t st);
 void fr_mul_vec(Fr::T* out, const Fr::T* a, const Fr::T* b, uint64_t n, cudaStream_t st);
 
+// distributed building blocks (see ntt.cu)
+void ntt_dist_stages(NttDomain& d, const NttBatch& b, NttTable t, bool dif, int world_log, uint32_t rank, bool cyclic, int split, cudaStream_t st);
+void ntt_dist_permute(const Fr::T* src, Fr::T* dst, int count, uint64_t n_local, uint32_t world, int block_layout, int to_wire, cudaStream_t st);
+
 // tunables (env G16_NTT_LOG_TILE, G16_NTT_LOG_COLS)
 int ntt_log_tile();
 int ntt_log_cols();

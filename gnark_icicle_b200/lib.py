@@ -62,6 +62,7 @@ SYMBOLS = [
     "g16_pk_upload", "g16_pk_free", "g16_prove_bn254", "g16_prove_bn254_dev", "g16_assemble_proof_bn254",
     "g16_msm_g1", "g16_msm_g1_dev", "g16_msm_g2", "g16_msm_g2_dev", "g16_ntt", "g16_ntt_dev",
     "g16_compute_h", "g16_compute_h_dev", "g16_fr_mul_vec",
+    "g16_dist_ntt_stages_dev", "g16_dist_permute_dev", "g16_dist_pointwise_h_dev", "g16_prove_msms_dev",
     "g16_g1_fixed_base_mul", "g16_g2_fixed_base_mul", "g16_g1_fixed_base_mul_dev", "g16_g2_fixed_base_mul_dev",
     "g16_g1_add", "g16_g2_add", "g16_g1_scalar_mul", "g16_g2_scalar_mul", "g16_imad_peak", "g16_pipe_rates", "g16_ctx_stream",
 ]
@@ -240,6 +241,25 @@ class Context:
         st = Stats()
         self._check(self._lib.g16_prove_bn254_dev(self._h, u64(pk_handle), _ptr(W_ptr), _ptr(a_ptr), _ptr(b_ptr), _ptr(c_ptr),
                                                   _ptr(out), ctypes.byref(st)), "g16_prove_bn254_dev")
+        return out, st.as_dict()
+
+    # ---- distributed computeH building blocks
+    def dist_ntt_stages_dev(self, data_ptr, count, n_global, world, rank, table, dif, cyclic, split):
+        self._check(self._lib.g16_dist_ntt_stages_dev(self._h, _ptr(data_ptr), int(count), u64(n_global), int(world), int(rank),
+                                                      int(table), int(dif), int(cyclic), int(split)), "g16_dist_ntt_stages_dev")
+
+    def dist_permute_dev(self, src_ptr, dst_ptr, count, n_local, world, block_layout, to_wire):
+        self._check(self._lib.g16_dist_permute_dev(self._h, _ptr(src_ptr), _ptr(dst_ptr), int(count), u64(n_local), int(world),
+                                                   int(block_layout), int(to_wire)), "g16_dist_permute_dev")
+
+    def dist_pointwise_h_dev(self, abc_ptr, n_local, n_global):
+        self._check(self._lib.g16_dist_pointwise_h_dev(self._h, _ptr(abc_ptr), u64(n_local), u64(n_global)), "g16_dist_pointwise_h_dev")
+
+    def prove_msms_dev(self, pk_handle, W_ptr, h_local_ptr):
+        out = np.zeros(PROVE_OUT_BYTES // 8, dtype=np.uint64)
+        st = Stats()
+        self._check(self._lib.g16_prove_msms_dev(self._h, u64(pk_handle), _ptr(W_ptr), _ptr(h_local_ptr), _ptr(out), ctypes.byref(st)),
+                    "g16_prove_msms_dev")
         return out, st.as_dict()
 
     def imad_peak(self):

@@ -128,6 +128,24 @@ int g16_compute_h(g16_ctx* ctx, const void* a, const void* b, const void* c, uin
 /* a_d,b_d,c_d: domain_n elements each (zero padded); h is left in a_d, b_d/c_d are clobbered */
 int g16_compute_h_dev(g16_ctx* ctx, void* a_d, void* b_d, void* c_d, uint64_t domain_n);
 
+/* ---- distributed computeH (one context per GPU; the caller moves data between ranks, e.g. NCCL all-to-all) ----
+ * A size-n transform over world = 2^g ranks is split at global stage `split` (g <= split <= log2(n) - g): stages
+ * with half-size >= 2^split run on the CYCLIC distribution (rank r holds positions q*world + r), the others on
+ * the BLOCK distribution (rank r holds [r n/world, (r+1) n/world)); one all-to-all in between -- the four-step
+ * transpose of SURVEY.md 8(e).  data_d = `count` arrays of n/world elements, back to back.
+ * table: 0 forward, 1 inverse, 2 coset forward, 3 coset inverse (no 1/n scaling: computeH folds it) */
+int g16_dist_ntt_stages_dev(g16_ctx* ctx, void* data_d, int count, uint64_t n_global, int world, int rank, int table,
+                            int dif, int cyclic, int split);
+/* layout change around the all-to-all.  Wire layout = [peer][array][q'], q' < n_local/world;
+ * block_layout: 0 = local arrays are cyclic-distributed, 1 = block-distributed; to_wire: 1 pack, 0 unpack */
+int g16_dist_permute_dev(g16_ctx* ctx, const void* src_d, void* dst_d, int count, uint64_t n_local, int world,
+                         int block_layout, int to_wire);
+/* (a*b/n - c) * den/n^2 on this rank's elements; abc_d = a, b, c back to back, result in a (icicle.go:500) */
+int g16_dist_pointwise_h_dev(g16_ctx* ctx, void* abc_d, uint64_t n_local, uint64_t n_global);
+/* the five MSMs only; h_local_d = this shard's block of h (domain_n/shard_count elements, bit-reversed order) */
+int g16_prove_msms_dev(g16_ctx* ctx, uint64_t pk_handle, const void* W_d, const void* h_local_d, void* out_points,
+                       g16_stats* stats);
+
 /* out[i] = a[i] * b[i] in Fr (icicle.go:500 PolyOps building block; minimum parity slice) */
 int g16_fr_mul_vec(g16_ctx* ctx, const void* a, const void* b, uint64_t n, void* out);
 
