@@ -16,7 +16,7 @@
 //   k_accumulate   balanced segmented reduction: every thread owns S consecutive sorted entries, adds
 //                  them with XYZZ mixed additions, and emits whole buckets directly and at most one
 //                  head and one tail piece -- long buckets are split across threads/warps automatically
-//   k_fixup        stitches head/tail pieces of buckets that span threads; empty buckets -> infinity
+//   k_fixup(+_heavy) stitches head/tail pieces of buckets that span threads (a CTA per long bucket); empty -> infinity
 //   k_bucket_reduce / k_window_sum   running-sum reduction sum_b (b+1)*B_b per window, tree-combined
 //   host           Horner over the W window sums (W*c doublings) + one inversion to affine
 #pragma once
@@ -25,7 +25,7 @@
 namespace g16 {
 
 struct MsmWorkspace {
-    DevBuf digits, sorted, counts, offsets, cursor, buckets, head, tail, partial, wsum, scan_tmp;
+    DevBuf digits, sorted, counts, offsets, cursor, buckets, head, tail, partial, wsum, scan_tmp, heavy;
     PinnedBuf host_wsum;
     cudaEvent_t acc_done = nullptr, tail_done = nullptr;
     void release() {
@@ -33,7 +33,7 @@ struct MsmWorkspace {
         if (tail_done) cudaEventDestroy(tail_done);
         acc_done = tail_done = nullptr;
         digits.release(); sorted.release(); counts.release(); offsets.release(); cursor.release();
-        buckets.release(); head.release(); tail.release(); partial.release(); wsum.release(); host_wsum.release(); scan_tmp.release();
+        buckets.release(); head.release(); tail.release(); partial.release(); wsum.release(); host_wsum.release(); scan_tmp.release(); heavy.release();
     }
 };
 
@@ -52,7 +52,8 @@ inline MsmPlan msm_plan(uint64_t n, int force_c, bool g2) {
     for (int c = 8; c <= 16; c++) {
         int W = 255 / c + 1;
         double madd = g2 ? 30.0 : 10.0, fadd = g2 ? 42.0 : 14.0;
-        double cost = (double)n * W * madd + (double)W * (1u << (c - 1)) * (2.0 * fadd + 3.0 * fadd);
+        // per bucket: fixup + 2 running-sum additions + share of the chunk scalar multiplication, fitted on B200
+        double cost = (double)n * W * madd + (double)W * (1u << (c - 1)) * (3.2 * fadd);
         if (cost < best_cost) { best_cost = cost; best = c; }
     }
     p.c = force_c >= 8 && force_c <= 16 ? force_c : best;
@@ -302,10 +303,15 @@ k_accumulate(const typename C::Aff* __restrict__ bases, const uint32_t* __restri
     }
 }
 
+// Buckets whose entries span several accumulate slices are stitched here.  Up to FIXUP_SERIAL pieces: one thread
+// adds them; longer ones (skewed scalars, the short top window, DummySetup-like inputs) go to a work list that
+// k_fixup_heavy reduces with a whole CTA per bucket.
+constexpr uint32_t FIXUP_SERIAL = 8;
+
 template <class C>
 __global__ void k_fixup(const uint32_t* __restrict__ offsets, uint32_t nb, uint32_t nthreads,
                         typename C::Xyzz* __restrict__ buckets, const typename C::Xyzz* __restrict__ head,
-                        const typename C::Xyzz* __restrict__ tail) {
+                        const typename C::Xyzz* __restrict__ tail, uint32_t* __restrict__ heavy /* [0] = count, then ids */) {
     typedef typename C::Xyzz Xyzz;
     uint32_t gb = blockIdx.x * blockDim.x + threadIdx.x;
     if (gb >= nb) return;
@@ -315,9 +321,40 @@ __global__ void k_fixup(const uint32_t* __restrict__ offsets, uint32_t nb, uint3
     if (start == end) { store_xyzz<C>(buckets + gb, C::inf()); return; }
     uint32_t t0 = start / S, t1 = (end - 1) / S;
     if (t0 == t1) return;   // written directly by k_accumulate
+    if (t1 - t0 + 1 > FIXUP_SERIAL) { heavy[1 + atomicAdd(&heavy[0], 1u)] = gb; return; }
     Xyzz acc = (start == t0 * S) ? load_xyzz<C>(head + t0) : load_xyzz<C>(tail + t0);
     for (uint32_t t = t0 + 1; t <= t1; t++) C::add(acc, load_xyzz<C>(head + t));
     store_xyzz<C>(buckets + gb, acc);
+}
+
+template <class C, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+k_fixup_heavy(const uint32_t* __restrict__ offsets, uint32_t nb, uint32_t nthreads, typename C::Xyzz* __restrict__ buckets,
+              const typename C::Xyzz* __restrict__ head, const typename C::Xyzz* __restrict__ tail, const uint32_t* __restrict__ heavy) {
+    typedef typename C::Xyzz Xyzz;
+    extern __shared__ uint4 fix_sm[];
+    Xyzz* sm = reinterpret_cast<Xyzz*>(fix_sm);
+    const uint32_t count = heavy[0];
+    const uint32_t total = offsets[nb];
+    const uint32_t S = msm_slice(total, nthreads);
+    for (uint32_t i = blockIdx.x; i < count; i += gridDim.x) {
+        const uint32_t gb = heavy[1 + i];
+        const uint32_t start = offsets[gb], end = offsets[gb + 1];
+        const uint32_t t0 = start / S, t1 = (end - 1) / S;
+        Xyzz acc = C::inf();
+        for (uint32_t t = t0 + threadIdx.x; t <= t1; t += THREADS) {
+            const Xyzz* piece = (t == t0 && start != t0 * S) ? tail + t : head + t;
+            C::add(acc, load_xyzz<C>(piece));
+        }
+        sm[threadIdx.x] = acc;
+        __syncthreads();
+        for (int stride = THREADS / 2; stride >= 1; stride >>= 1) {
+            if ((int)threadIdx.x < stride) { Xyzz a = sm[threadIdx.x]; C::add(a, sm[threadIdx.x + stride]); sm[threadIdx.x] = a; }
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) store_xyzz<C>(buckets + gb, sm[0]);
+        __syncthreads();
+    }
 }
 
 // ------------------------------------------------------------------ bucket reduction
@@ -398,6 +435,7 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
     ws.counts.reserve((size_t)pl.NB * 4);
     ws.offsets.reserve((size_t)(pl.NB + 1) * 4);
     ws.cursor.reserve((size_t)pl.NB * 4);
+    ws.heavy.reserve((size_t)(pl.NB + 1) * 4);
     ws.scan_tmp.reserve((size_t)((pl.NB + SCAN_BLOCK - 1) / SCAN_BLOCK) * 4 + 16);
     ws.buckets.reserve((size_t)pl.NB * sizeof(Xyzz));
     ws.head.reserve((size_t)nthreads * sizeof(Xyzz));
@@ -452,8 +490,17 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
     }
     cudaStream_t main_st = st;
     if (tail) st = tail;
-    k_fixup<C><<<(pl.NB + 127) / 128, 128, 0, st>>>(offsets, pl.NB, nthreads, buckets, ws.head.as<Xyzz>(), ws.tail.as<Xyzz>());
+    uint32_t* heavy = ws.heavy.as<uint32_t>();
+    G16_CUDA(cudaMemsetAsync(heavy, 0, 4, st));
+    k_fixup<C><<<(pl.NB + 127) / 128, 128, 0, st>>>(offsets, pl.NB, nthreads, buckets, ws.head.as<Xyzz>(), ws.tail.as<Xyzz>(), heavy);
     G16_LAUNCH_CHECK();
+    {
+        constexpr int HT = IS_G2 ? 128 : 256;
+        size_t hs = (size_t)HT * sizeof(Xyzz);
+        if (hs > 48 * 1024) G16_CUDA(cudaFuncSetAttribute(k_fixup_heavy<C, HT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hs));
+        k_fixup_heavy<C, HT><<<sms * 2, HT, hs, st>>>(offsets, pl.NB, nthreads, buckets, ws.head.as<Xyzz>(), ws.tail.as<Xyzz>(), heavy);
+        G16_LAUNCH_CHECK();
+    }
     dim3 rgrid(pl.red_rb, pl.W);
     k_bucket_reduce<C><<<rgrid, MSM_RED_THREADS, 0, st>>>(buckets, pl.B, pl.red_m, ws.partial.as<Xyzz>());
     G16_LAUNCH_CHECK();

@@ -43,7 +43,7 @@ def test_msm_zero_length_is_infinity(ctx):
     assert not ctx.msm_g2(np.zeros((0, 4), np.uint64), np.zeros((0, 16), np.uint64)).any()
 
 
-@pytest.mark.parametrize("c", [8, 11, 13, 16])
+@pytest.mark.parametrize("c", list(range(8, 17)))
 def test_msm_g1_every_window_size(ctx, c):
     n = 3000
     k, pts = g1_bases(500, n)
@@ -108,6 +108,26 @@ def test_msm_g1_skewed_scalars(ctx):
         vals[i * 50] = v
     s = fr_from_ints(vals)
     assert_limbs_equal(ctx.msm_g1(s, pts), trapdoor_g1(s, k), "skewed scalars")
+
+
+def test_msm_heavy_buckets_are_reduced_cooperatively(ctx):
+    """one bucket per window holds everything (all scalars equal): thousands of slice pieces per bucket go through
+    k_fixup_heavy; also every window size must cope with the 2-bit top window of real Fr scalars."""
+    n = 150_000
+    k = fr_rand(950, n)
+    pts = ctx.g1_fixed_base_mul(k)
+    s1 = np.repeat(fr_rand(951, 1), n, axis=0)
+    assert_limbs_equal(ctx.msm_g1(s1, pts), trapdoor_g1(s1, k), "all-equal scalars, distinct bases")
+    s = fr_rand(952, n)
+    for c in (9, 12, 14):
+        ctx.set("msm_c", c)
+        try:
+            assert_limbs_equal(ctx.msm_g1(s, pts), trapdoor_g1(s, k), f"c={c} short top window")
+        finally:
+            ctx.set("msm_c", 0)
+    m = 20_000
+    p2 = ctx.g2_fixed_base_mul(k[:m])
+    assert_limbs_equal(ctx.msm_g2(s1[:m], p2), trapdoor_g2(s1[:m], k[:m]), "G2 all-equal scalars")
 
 
 def test_msm_g2_degenerate(ctx):
