@@ -46,7 +46,7 @@ struct g16_ctx {
     MsmWorkspace ws[5];
     DevBuf stage[4];             // host-pointer variants: staged inputs
     DevBuf fb_table_g1, fb_table_g2;
-    int msm_c = 0, msm_waves = 2;
+    int msm_c = 0, msm_waves = 4;
 
     NttDomain& domain(int logn) {
         auto it = domains.find(logn);

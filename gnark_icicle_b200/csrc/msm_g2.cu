@@ -1,11 +1,15 @@
 // G2 (Fp2) instantiation of the Pippenger pipeline (see msm.cuh).
 #include "msm_api.cuh"
 #include "fixed_base.cuh"
+#include <cstdlib>
 
 namespace g16 {
 
 void msm_g2_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const G2::Aff* bases_d, uint64_t n,
                     int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail) {
+    static const int variant = [] { const char* e = getenv("G16_ACC_VARIANT_G2"); return e ? atoi(e) : 0; }();
+    // 128 x 2 (194 registers): forcing 3 or 4 CTAs/SM spills and is 30-80 % slower (profiles/README.md)
+    (void)variant;
     msm_enqueue<G2, 128, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail);
 }
 G2::Aff msm_g2_finish(const MsmWorkspace& ws, const MsmPlan& plan) { return msm_finish<G2>(ws, plan); }

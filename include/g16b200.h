@@ -60,7 +60,7 @@ typedef struct {
 int g16_ctx_create(g16_ctx** out, int curve_id, const int* device_ids, int n_devices);
 void g16_ctx_destroy(g16_ctx* ctx);
 const char* g16_last_error(const g16_ctx* ctx);
-/* tunables: "msm_c" (0 = auto, 8..16), "msm_waves" (accumulate waves, default 2),
+/* tunables: "msm_c" (0 = auto, 8..16), "msm_waves" (accumulate waves, default 4),
  * "streams" (1 = run the five MSMs back to back; default 5 = overlap the MSMs that do not depend on h) */
 int g16_ctx_set(g16_ctx* ctx, const char* key, int64_t value);
 /* total kernels launched by this library in this process (bench.py's gpu_launches evidence) */
