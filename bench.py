@@ -326,6 +326,16 @@ def run_ours(args):
             "share_of_step": (g1_ms + g2_ms) / st["ms_total"],
             "note": "kernel times from one extra step with the five MSMs serialised (streams=1); the timed steps overlap them"}
     pk_, src = peaks()
+    # HBM view of the same kernel: 64 B affine point + 4 B sorted index per bucket entry; `traffic` is
+    # dram__bytes_read+write per launch of the 2^22-point launch from the ncu --set full capture in profiles/
+    g1_bytes = sum(st["msm_n"][i] * st["msm_windows"][i] for i in range(4)) * 68
+    roof["hbm"] = {"bound": "hbm", "achieved": g1_bytes / (g1_ms * 1e-3) / 1e9, "peak": pk_["hbm_gbs"], "unit": "GB/s",
+                   "frac": g1_bytes / (g1_ms * 1e-3) / 1e9 / pk_["hbm_gbs"], "peak_source": src,
+                   "algorithmic_bytes_per_launch_2p22": (1 << 22) * 16 * 68,
+                   "note": "the accumulate kernel is bound by the integer multiplier, not HBM: it moves <10 % of the copy bandwidth"}
+    if args.log_n == 22:
+        roof["traffic"] = 7.06e9
+        roof["traffic_source"] = "profiles/r01b_accumulate_2p22_ncu_raw.csv: 6.95 GB read + 0.11 GB written per 2^22-point launch (12.04 ms)"
     ntt_bytes = 7 * 64 * n
     if st["ms_compute_h"] > 0:
       roof["compute_h"] = {"bound": "hbm", "achieved": ntt_bytes / (st["ms_compute_h"] * 1e-3) / 1e9, "peak": pk_["hbm_gbs"],
@@ -345,7 +355,7 @@ def run_ours(args):
             "stages_ms": {"serialised_total": st["ms_total"], "compute_h": st["ms_compute_h"], "msm": st["ms_msm"], "accumulate": st["ms_accumulate"],
                           "host_epilogue": st["ms_host"], "msm_c": st["msm_c"], "e2e_h2d": st_e["ms_h2d"]}}
     if world == 1 and not args.no_extras:
-        line["extras"] = extras(torch, ctx, ext, dev, pk_, imad)
+        line["extras"] = extras(torch, ctx, ext, dev, pk_, imad, full=args.sweep)
         ms_cpu, cores = cpu_prove_sample(args.cpu_log_n)
         scale = cpu_scale(args.cpu_log_n, args.log_n)
         line["cpu_baseline"] = {"value": ms_cpu * scale, "unit": "ms", "cores": cores, "kind": "port",
@@ -356,8 +366,9 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
-def extras(torch, ctx, ext, dev, pk_, imad):
-    """the other two headline numbers of BASELINE.json's metric: G1 MSM Mpoints/s @ 2^24 and NTT GB/s."""
+def extras(torch, ctx, ext, dev, pk_, imad, full=False):
+    """the other two headline numbers of BASELINE.json's metric: G1 MSM Mpoints/s @ 2^24 and NTT GB/s.
+    full=True (--sweep): the whole 2^16..2^26 sweeps of configs 2 and 3."""
     out = {}
     gen = torch.Generator(device=dev)
     gen.manual_seed(7)
@@ -375,7 +386,7 @@ def extras(torch, ctx, ext, dev, pk_, imad):
             best = min(best, e0.elapsed_time(e1))
         return best
 
-    for logn in (20, 22, 24):
+    for logn in (range(16, 27) if full else (20, 22, 24)):
         m = 1 << logn
         k = rand_fr_cuda(torch, m, gen, dev)
         bases = torch.empty((m, 8), dtype=torch.int64, device=dev)
@@ -392,9 +403,19 @@ def extras(torch, ctx, ext, dev, pk_, imad):
     ms = ev_time(lambda: ctx.msm_g2_dev(s.data_ptr(), b2.data_ptr(), m))
     out["msm_g2_2p20"] = {"ms": ms, "mpts_per_s": m / ms / 1e3}
     del k, b2, s
-    for logn in (20, 22, 24, 26):
+    for logn in (range(16, 27) if full else (20, 22, 24, 26)):
         m = 1 << logn
         x = rand_fr_cuda(torch, m, gen, dev)
+        if full:
+            for name, kw in (("ntt_fwd_dit", dict(inverse=False, coset=False, decimation=1)),
+                             ("intt_dif", dict(inverse=True, coset=False, decimation=0)),
+                             ("intt_coset_dif", dict(inverse=True, coset=True, decimation=0))):
+                ms = ev_time(lambda: ctx.ntt_dev(x.data_ptr(), m, **kw))
+                out[f"{name}_2p{logn}"] = {"ms": ms, "gb_per_s": 64.0 * m / (ms * 1e-3) / 1e9}
+            abc = [rand_fr_cuda(torch, m, gen, dev) for _ in range(3)]
+            ms = ev_time(lambda: ctx.compute_h_dev(abc[0].data_ptr(), abc[1].data_ptr(), abc[2].data_ptr(), m))
+            out[f"compute_h_2p{logn}"] = {"ms": ms, "gb_per_s": 448.0 * m / (ms * 1e-3) / 1e9}
+            del abc
         ms = ev_time(lambda: ctx.ntt_dev(x.data_ptr(), m, inverse=False, coset=True, decimation=1))
         gbs = 64.0 * m / (ms * 1e-3) / 1e9
         muls = (m // 2) * logn
@@ -413,6 +434,7 @@ def main():
     ap.add_argument("--log-n", type=int, default=22, help="log2 of the constraint count (BASELINE: 22)")
     ap.add_argument("--cpu-log-n", type=int, default=18, help="log2 constraints of the bounded CPU sample")
     ap.add_argument("--no-extras", action="store_true")
+    ap.add_argument("--sweep", action="store_true", help="extras = the full 2^16..2^26 MSM and NTT sweeps (configs 2, 3)")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.impl == "ours" and args.gpus > 1 and world == 1:

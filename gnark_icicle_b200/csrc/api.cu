@@ -7,11 +7,14 @@
 #include <cstdlib>
 #include <memory>
 
+#include "curve_select.h"
 #include "../../include/g16b200.h"
 #include "msm_api.cuh"
 #include "ntt.cuh"
 
 using namespace g16;
+
+static constexpr size_t G1SZ = sizeof(G1::Aff), G2SZ = sizeof(G2::Aff);   // 64 / 128 B (BN254), 96 / 192 B (BLS12-377)
 
 namespace {
 
@@ -93,7 +96,7 @@ extern "C" {
 int g16_ctx_create(g16_ctx** out, int curve_id, const int* device_ids, int n_devices) {
     if (!out) return 1;
     *out = nullptr;
-    if (curve_id != G16_CURVE_BN254) return 3;
+    if (curve_id != (G16_CURVE == 377 ? G16_CURVE_BLS12_377 : G16_CURVE_BN254)) return 3;   // one entry-point set per curve (curve_select.h)
     if (n_devices > 1) return 4;
     std::unique_ptr<g16_ctx> c(new g16_ctx());
     try {
@@ -186,16 +189,16 @@ extern "C" int g16_pk_upload(g16_ctx* ctx, const g16_pk_desc* d, uint64_t* pk_ha
         uint64_t lo, hi;
         slice(d->n_a, si, sc, lo, hi);
         pk.n_a = hi - lo;
-        upload(pk.g1_a, (const char*)d->g1_a + lo * 64, pk.n_a * 64, st);
+        upload(pk.g1_a, (const char*)d->g1_a + lo * G1SZ, pk.n_a * G1SZ, st);
         upload(pk.map_a, ma.data() + lo, pk.n_a * 4, st);
         slice(d->n_b, si, sc, lo, hi);
         pk.n_b = pk.n_b2 = hi - lo;
-        upload(pk.g1_b, (const char*)d->g1_b + lo * 64, pk.n_b * 64, st);
-        upload(pk.g2_b, (const char*)d->g2_b + lo * 128, pk.n_b * 128, st);
+        upload(pk.g1_b, (const char*)d->g1_b + lo * G1SZ, pk.n_b * G1SZ, st);
+        upload(pk.g2_b, (const char*)d->g2_b + lo * G2SZ, pk.n_b * G2SZ, st);
         upload(pk.map_b, mb.data() + lo, pk.n_b * 4, st);
         slice(d->n_k, si, sc, lo, hi);
         pk.n_k = hi - lo;
-        upload(pk.g1_k, (const char*)d->g1_k + lo * 64, pk.n_k * 64, st);
+        upload(pk.g1_k, (const char*)d->g1_k + lo * G1SZ, pk.n_k * G1SZ, st);
         upload(pk.map_k, mk.data() + lo, pk.n_k * 4, st);
         uint64_t nz = d->n_z < d->domain_n ? d->n_z : d->domain_n - 1;   // h[:n-1] (prove.go:235-237)
         // Z follows the block distribution of h over the domain (so a distributed computeH leaves each rank's
@@ -205,7 +208,7 @@ extern "C" int g16_pk_upload(g16_ctx* ctx, const g16_pk_desc* d, uint64_t* pk_ha
         if (hi > nz) hi = nz;
         pk.n_z = hi - lo;
         pk.z_off = lo;
-        upload(pk.g1_z, (const char*)d->g1_z + lo * 64, pk.n_z * 64, st);
+        upload(pk.g1_z, (const char*)d->g1_z + lo * G1SZ, pk.n_z * G1SZ, st);
 
         // twiddles of the domain (replaces icicle.go:44-75)
         NttDomain& dom = ctx->domain(pk.logn);
@@ -281,8 +284,8 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
     auto t0 = std::chrono::steady_clock::now();
     char* out = (char*)out_points;
     const uint64_t ns[5] = {pk.n_a, pk.n_b, pk.n_k, pk.n_z, pk.n_b2};
-    for (int i = 0; i < 4; i++) copy_out(out + 64 * i, ns[i] ? msm_g1_finish(ctx->ws[i], plan[i]) : G1::aff_inf());
-    copy_out(out + 256, ns[4] ? msm_g2_finish(ctx->ws[4], plan[4]) : G2::aff_inf());
+    for (int i = 0; i < 4; i++) copy_out(out + G1SZ * i, ns[i] ? msm_g1_finish(ctx->ws[i], plan[i]) : G1::aff_inf());
+    copy_out(out + 4 * G1SZ, ns[4] ? msm_g2_finish(ctx->ws[4], plan[4]) : G2::aff_inf());
     auto t1 = std::chrono::steady_clock::now();
     if (stats) {
         G16_CUDA(cudaEventElapsedTime(&stats->ms_compute_h, ev[12], ev[13]));
@@ -408,14 +411,14 @@ int g16_msm_g2_dev(g16_ctx* ctx, const void* s_d, const void* b_d, uint64_t n, v
 int g16_msm_g1(g16_ctx* ctx, const void* scalars, const void* bases, uint64_t n, void* out) {
     return guarded(ctx, [&] {
         upload(ctx->stage[0], scalars, n * 32, ctx->stream);
-        upload(ctx->stage[1], bases, n * 64, ctx->stream);
+        upload(ctx->stage[1], bases, n * G1SZ, ctx->stream);
         msm_g1_dev_impl(ctx, ctx->stage[0].p, ctx->stage[1].p, n, out);
     });
 }
 int g16_msm_g2(g16_ctx* ctx, const void* scalars, const void* bases, uint64_t n, void* out) {
     return guarded(ctx, [&] {
         upload(ctx->stage[0], scalars, n * 32, ctx->stream);
-        upload(ctx->stage[1], bases, n * 128, ctx->stream);
+        upload(ctx->stage[1], bases, n * G2SZ, ctx->stream);
         msm_g2_dev_impl(ctx, ctx->stage[0].p, ctx->stage[1].p, n, out);
     });
 }
@@ -483,18 +486,18 @@ int g16_g2_fixed_base_mul_dev(g16_ctx* ctx, const void* s_d, uint64_t n, void* o
 int g16_g1_fixed_base_mul(g16_ctx* ctx, const void* scalars, uint64_t n, void* out) {
     return guarded(ctx, [&] {
         upload(ctx->stage[0], scalars, n * 32, ctx->stream);
-        ctx->stage[1].reserve(n * 64 + 16);
+        ctx->stage[1].reserve(n * G1SZ + 16);
         fixed_base_g1(ctx->fb_table_g1, ctx->stage[0].as<Fr::T>(), n, ctx->stage[1].as<G1::Aff>(), ctx->stream);
-        if (n) G16_CUDA(cudaMemcpyAsync(out, ctx->stage[1].p, n * 64, cudaMemcpyDeviceToHost, ctx->stream));
+        if (n) G16_CUDA(cudaMemcpyAsync(out, ctx->stage[1].p, n * G1SZ, cudaMemcpyDeviceToHost, ctx->stream));
         G16_CUDA(cudaStreamSynchronize(ctx->stream));
     });
 }
 int g16_g2_fixed_base_mul(g16_ctx* ctx, const void* scalars, uint64_t n, void* out) {
     return guarded(ctx, [&] {
         upload(ctx->stage[0], scalars, n * 32, ctx->stream);
-        ctx->stage[1].reserve(n * 128 + 16);
+        ctx->stage[1].reserve(n * G2SZ + 16);
         fixed_base_g2(ctx->fb_table_g2, ctx->stage[0].as<Fr::T>(), n, ctx->stage[1].as<G2::Aff>(), ctx->stream);
-        if (n) G16_CUDA(cudaMemcpyAsync(out, ctx->stage[1].p, n * 128, cudaMemcpyDeviceToHost, ctx->stream));
+        if (n) G16_CUDA(cudaMemcpyAsync(out, ctx->stage[1].p, n * G2SZ, cudaMemcpyDeviceToHost, ctx->stream));
         G16_CUDA(cudaStreamSynchronize(ctx->stream));
     });
 }
@@ -548,22 +551,22 @@ int g16_assemble_proof_bn254(const void* pk_points, const void* r_, const void* 
     if (!pk_points || !r_ || !s_ || !msm_points || !proof_out) return 1;
     const char* pp = (const char*)pk_points;
     const char* mp = (const char*)msm_points;
-    G1::Aff alpha = rd<G1::Aff>(pp), beta = rd<G1::Aff>(pp + 64), delta = rd<G1::Aff>(pp + 128);
-    G2::Aff beta2 = rd<G2::Aff>(pp + 192), delta2 = rd<G2::Aff>(pp + 320);
+    G1::Aff alpha = rd<G1::Aff>(pp), beta = rd<G1::Aff>(pp + G1SZ), delta = rd<G1::Aff>(pp + 2 * G1SZ);
+    G2::Aff beta2 = rd<G2::Aff>(pp + 3 * G1SZ), delta2 = rd<G2::Aff>(pp + 3 * G1SZ + G2SZ);
     Fr::T r = rd<Fr::T>(r_), s = rd<Fr::T>(s_);
     Fr::T kr = Fr::neg(Fr::mul(r, s));
     G1::Aff d_r = aff_mul<G1>(delta, r), d_s = aff_mul<G1>(delta, s), d_kr = aff_mul<G1>(delta, kr);
-    G1::Aff ar = aff_add<G1>(aff_add<G1>(rd<G1::Aff>(mp + 64 * G16_OUT_AR), alpha), d_r);
-    G1::Aff bs1 = aff_add<G1>(aff_add<G1>(rd<G1::Aff>(mp + 64 * G16_OUT_BS1), beta), d_s);
-    G1::Aff krs = aff_add<G1>(rd<G1::Aff>(mp + 64 * G16_OUT_KRS_K), d_kr);
-    krs = aff_add<G1>(krs, rd<G1::Aff>(mp + 64 * G16_OUT_KRS_HZ));
+    G1::Aff ar = aff_add<G1>(aff_add<G1>(rd<G1::Aff>(mp + G1SZ * G16_OUT_AR), alpha), d_r);
+    G1::Aff bs1 = aff_add<G1>(aff_add<G1>(rd<G1::Aff>(mp + G1SZ * G16_OUT_BS1), beta), d_s);
+    G1::Aff krs = aff_add<G1>(rd<G1::Aff>(mp + G1SZ * G16_OUT_KRS_K), d_kr);
+    krs = aff_add<G1>(krs, rd<G1::Aff>(mp + G1SZ * G16_OUT_KRS_HZ));
     krs = aff_add<G1>(krs, aff_mul<G1>(ar, s));
     krs = aff_add<G1>(krs, aff_mul<G1>(bs1, r));
-    G2::Aff bs = aff_add<G2>(aff_add<G2>(rd<G2::Aff>(mp + 256), aff_mul<G2>(delta2, s)), beta2);
+    G2::Aff bs = aff_add<G2>(aff_add<G2>(rd<G2::Aff>(mp + 4 * G1SZ), aff_mul<G2>(delta2, s)), beta2);
     char* o = (char*)proof_out;
     copy_out(o, ar);
-    copy_out(o + 64, bs);
-    copy_out(o + 192, krs);
+    copy_out(o + G1SZ, bs);
+    copy_out(o + G1SZ + G2SZ, krs);
     return 0;
 }
 

@@ -1,6 +1,7 @@
 // Shared host-side plumbing for libg16b200: error propagation, device buffers, the context object.
 // No CPU fallback exists anywhere in this library: every entry point fails loudly when CUDA fails.
 #pragma once
+#include "curve_select.h"
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <atomic>

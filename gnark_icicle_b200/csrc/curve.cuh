@@ -7,6 +7,7 @@
 // observable; XYZZ intermediates are private to this library.
 // Formulas: EFD "xyzz" madd-2008-s (8M+2S), add-2008-s (12M+2S), dbl-2008-s-1, mdbl-2008-s-1.
 #pragma once
+#include "curve_select.h"
 #include "field.cuh"
 
 namespace g16 {

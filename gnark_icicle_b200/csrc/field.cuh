@@ -7,6 +7,7 @@
 // Memory image = gnark-crypto's: N/2 little-endian uint64 limbs == N little-endian uint32 limbs,
 // Montgomery form with R = 2^(32N).
 #pragma once
+#include "curve_select.h"
 #include <cstdint>
 #include <cstring>
 
@@ -60,6 +61,40 @@ struct FrBN254 {
     }
     G16_HD static constexpr uint32_t r2(int i) {
         constexpr uint32_t m[8] = {0xae216da7u, 0x1bb8e645u, 0xe35c59e3u, 0x53fe3ab1u, 0x53bb8085u, 0x8c49833du, 0x7f4e44a5u, 0x0216d0b1u};
+        return m[i];
+    }
+};
+
+// BLS12-377 (BASELINE config 5): 377-bit Fp on 12 limbs, 253-bit Fr on 8 limbs; both moduli are 1 mod 2^32.
+struct FpBLS377 {
+    static constexpr int N = 12;
+    static constexpr uint32_t INV = 0xffffffffu;
+    G16_HD static constexpr uint32_t mod(int i) {
+        constexpr uint32_t m[12] = {0x00000001u, 0x8508c000u, 0x30000000u, 0x170b5d44u, 0xba094800u, 0x1ef3622fu, 0x00f5138fu, 0x1a22d9f3u, 0x6ca1493bu, 0xc63b05c0u, 0x17c510eau, 0x01ae3a46u};
+        return m[i];
+    }
+    G16_HD static constexpr uint32_t one(int i) {
+        constexpr uint32_t m[12] = {0xffffff68u, 0x02cdffffu, 0x7fffffb1u, 0x51409f83u, 0x8a7d3ff2u, 0x9f7db3a9u, 0x6e7c6305u, 0x7b4e97b7u, 0x803c84e8u, 0x4cf495bfu, 0xe2fdf49au, 0x008d6661u};
+        return m[i];
+    }
+    G16_HD static constexpr uint32_t r2(int i) {
+        constexpr uint32_t m[12] = {0x9400cd22u, 0xb786686cu, 0xb00431b1u, 0x0329fcaau, 0x62d6b46du, 0x22a5f111u, 0x827dc3acu, 0xbfdf7d03u, 0x41790bf9u, 0x837e92f0u, 0x1e914b88u, 0x006dfccbu};
+        return m[i];
+    }
+};
+struct FrBLS377 {
+    static constexpr int N = 8;
+    static constexpr uint32_t INV = 0xffffffffu;
+    G16_HD static constexpr uint32_t mod(int i) {
+        constexpr uint32_t m[8] = {0x00000001u, 0x0a118000u, 0xd0000001u, 0x59aa76feu, 0x5c37b001u, 0x60b44d1eu, 0x9a2ca556u, 0x12ab655eu};
+        return m[i];
+    }
+    G16_HD static constexpr uint32_t one(int i) {
+        constexpr uint32_t m[8] = {0xfffffff3u, 0x7d1c7fffu, 0x6ffffff2u, 0x7257f50fu, 0x512c0feeu, 0x16d81575u, 0x2bbb9a9du, 0x0d4bda32u};
+        return m[i];
+    }
+    G16_HD static constexpr uint32_t r2(int i) {
+        constexpr uint32_t m[8] = {0xb861857bu, 0x25d577bau, 0x8860591fu, 0xcc2c27b5u, 0xe5dc8593u, 0xa7cc008fu, 0xeff1c939u, 0x011fdae7u};
         return m[i];
     }
 };
@@ -288,12 +323,21 @@ struct FieldCall : Field<P> {
     G16_HD static T sqr(const T& a) { return mul(a, a); }
 };
 
-typedef Field<FpBN254> Fp;
-typedef Field<FrBN254> Fr;
-typedef FieldCall<FpBN254> FpC;
+#if G16_CURVE == 377
+typedef FpBLS377 FpParams;
+typedef FrBLS377 FrParams;
+constexpr int FP2_NONRESIDUE = 5;    // Fp2 = Fp[u]/(u^2+5)  (gnark-crypto bls12-377 E2)
+#else
+typedef FpBN254 FpParams;
+typedef FrBN254 FrParams;
+constexpr int FP2_NONRESIDUE = 1;    // Fp2 = Fp[u]/(u^2+1)  (gnark-crypto bn254 E2)
+#endif
+typedef Field<FpParams> Fp;
+typedef Field<FrParams> Fr;
+typedef FieldCall<FpParams> FpC;
 
-// ---------------------------------------------------------------- Fp2 = Fp[u]/(u^2+1)  (gnark E2{A0,A1})
-template <class F>
+// ---------------------------------------------------------------- Fp2 = Fp[u]/(u^2 + NR)  (gnark E2{A0,A1})
+template <class F, int NR>
 struct Ext2 {
     struct T { typename F::T a0, a1; };
     G16_HD static T zero() { T r; r.a0 = F::zero(); r.a1 = F::zero(); return r; }
@@ -304,26 +348,37 @@ struct Ext2 {
     G16_HD static T sub(const T& a, const T& b) { T r; r.a0 = F::sub(a.a0, b.a0); r.a1 = F::sub(a.a1, b.a1); return r; }
     G16_HD static T dbl(const T& a) { return add(a, a); }
     G16_HD static T neg(const T& a) { T r; r.a0 = F::neg(a.a0); r.a1 = F::neg(a.a1); return r; }
+    // NR * a for the small non-residues in use (1 and 5)
+    G16_HD static typename F::T mul_nr(const typename F::T& a) {
+        static_assert(NR == 1 || NR == 5, "unsupported non-residue");
+        if (NR == 1) return a;
+        typename F::T a4 = F::dbl(F::dbl(a));
+        return F::add(a4, a);
+    }
     // Karatsuba: 3 base multiplications
     G16_HD static T mul(const T& a, const T& b) {
         typename F::T v0 = F::mul(a.a0, b.a0), v1 = F::mul(a.a1, b.a1);
         typename F::T s = F::mul(F::add(a.a0, a.a1), F::add(b.a0, b.a1));
         T r;
-        r.a0 = F::sub(v0, v1);
+        r.a0 = F::sub(v0, mul_nr(v1));
         r.a1 = F::sub(F::sub(s, v0), v1);
         return r;
     }
-    // (a0+a1)(a0-a1) + 2 a0 a1 u : 2 base multiplications
+    // 2 base multiplications: (a0+a1)(a0 - NR a1) = (a0^2 - NR a1^2) - (NR-1) a0 a1
     G16_HD static T sqr(const T& a) {
-        typename F::T p = F::mul(F::add(a.a0, a.a1), F::sub(a.a0, a.a1));
+        typename F::T p = F::mul(F::add(a.a0, a.a1), F::sub(a.a0, mul_nr(a.a1)));
         typename F::T q = F::mul(a.a0, a.a1);
-        T r; r.a0 = p; r.a1 = F::dbl(q); return r;
+        T r;
+        if (NR == 1) r.a0 = p;
+        else r.a0 = F::add(p, F::dbl(F::dbl(q)));   // NR = 5: + 4 a0 a1
+        r.a1 = F::dbl(q);
+        return r;
     }
     G16_HD static T inv(const T& a) {
-        typename F::T d = F::inv(F::add(F::sqr(a.a0), F::sqr(a.a1)));
+        typename F::T d = F::inv(F::add(F::sqr(a.a0), mul_nr(F::sqr(a.a1))));
         T r; r.a0 = F::mul(a.a0, d); r.a1 = F::neg(F::mul(a.a1, d)); return r;
     }
 };
-typedef Ext2<FpC> Fp2;
+typedef Ext2<FpC, FP2_NONRESIDUE> Fp2;
 
 }  // namespace g16

@@ -1,5 +1,6 @@
 // Fixed-base batch scalar multiplication [k_i]G on device (setup-side tooling; see msm_api.cuh).
 #pragma once
+#include "curve_select.h"
 #include "msm.cuh"
 
 namespace g16 {

@@ -20,6 +20,7 @@
 //   k_bucket_reduce / k_window_sum   running-sum reduction sum_b (b+1)*B_b per window, tree-combined
 //   host           Horner over the W window sums (W*c doublings) + one inversion to affine
 #pragma once
+#include "curve_select.h"
 #include "common.cuh"
 
 namespace g16 {

@@ -1,5 +1,6 @@
 // Non-template entry points of the MSM translation units (msm_g1.cu, msm_g2.cu).
 #pragma once
+#include "curve_select.h"
 #include "msm.cuh"
 
 namespace g16 {

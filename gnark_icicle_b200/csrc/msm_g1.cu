@@ -16,8 +16,17 @@ G1::Aff msm_g1_finish(const MsmWorkspace& ws, const MsmPlan& plan) { return msm_
 
 G1::Aff g1_generator() {
     G1::Aff g;
+#if G16_CURVE == 377
+    // gnark-crypto bls12-377 G1 generator (checked: on y^2 = x^3 + 1, order r -- tests/test_oracle_bls12_377.py)
+    static const uint32_t X[12] = {0xb21be9efu, 0xeab9b16eu, 0xffcd394eu, 0xd5481512u, 0xbd37cb5cu, 0x188282c8u, 0xaa9d41bbu, 0x85951e2cu, 0xbf87ff54u, 0xc8fc6225u, 0xfe740a67u, 0x008848deu};
+    static const uint32_t Y[12] = {0x559c8ea6u, 0xfd82de55u, 0x34a9591au, 0xc2fe3d36u, 0x4fb82305u, 0x6d182ad4u, 0xca3e52d9u, 0xbd7fb348u, 0x30afeec4u, 0x1f674f5du, 0xc5102effu, 0x01914a69u};
+    Fp::T t;
+    memcpy(t.l, X, sizeof(X)); g.x = Fp::to_mont(t);
+    memcpy(t.l, Y, sizeof(Y)); g.y = Fp::to_mont(t);
+#else
     g.x = Fp::one();
     g.y = Fp::add(Fp::one(), Fp::one());
+#endif
     return g;
 }
 void fixed_base_g1(DevBuf& table_d, const Fr::T* scalars_d, uint64_t n, G1::Aff* out_d, cudaStream_t st) {

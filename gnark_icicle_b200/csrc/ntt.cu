@@ -17,7 +17,15 @@
 
 namespace g16 {
 
+// primitive 2^28-th root of unity and coset shift of fft.Domain (gnark-crypto: generator^((r-1)/2^28), generator =
+// FrMultiplicativeGen = 5 for BN254, 22 for BLS12-377 -- whose 2^47-th root squared 19 times is the value below)
+#if G16_CURVE == 377
+static const uint32_t ROOT_2_28[8] = {0xe5f8848au, 0x270a2326u, 0xa727567du, 0x97d14afau, 0x48746fc7u, 0x1a3a5a4eu, 0xa42f077au, 0x0044e4b1u};
+static const uint64_t COSET_GEN = 22;
+#else
 static const uint32_t ROOT_2_28[8] = {0x725b19f0u, 0x9bd61b6eu, 0x41112ed4u, 0x402d111eu, 0x8ef62abcu, 0x00e0a7ebu, 0xa58a7e85u, 0x2a3c09f0u};
+static const uint64_t COSET_GEN = 5;
+#endif
 
 int ntt_log_tile() {
     static int v = [] { const char* e = getenv("G16_NTT_LOG_TILE"); int x = e ? atoi(e) : 10; return x < 4 ? 4 : (x > 12 ? 12 : x); }();
@@ -65,7 +73,7 @@ void NttDomain::init(int logn_) {
     for (int i = logn; i < 28; i++) root = Fr::sqr(root);
     omega = root;
     omega_inv = Fr::inv(root);
-    coset_gen = Fr::from_u64(5);
+    coset_gen = Fr::from_u64(COSET_GEN);
     coset_inv = Fr::inv(coset_gen);
     n_inv = Fr::inv(Fr::from_u64(n));
     Fr::T gn = Fr::pow_u64(coset_gen, n);

@@ -1,5 +1,6 @@
 // Fr NTT domain for the computeH pipeline (declarations).  See ntt.cu.
 #pragma once
+#include "curve_select.h"
 #include "common.cuh"
 
 namespace g16 {
