@@ -2,7 +2,8 @@
 
 This is the Python stand-in for the cgo layer a Go host would use (INTEGRATION.md shows the cgo stub);
 it exists because neither build machine has a Go toolchain.  Arrays are numpy ``uint64`` with a trailing
-limb axis -- Fr ``(n, 4)``, G1 affine ``(n, 8)``, G2 affine ``(n, 16)`` -- i.e. gnark-crypto's memory image.
+limb axis -- Fr ``(n, 4)``, G1 affine ``(n, 8)``, G2 affine ``(n, 16)`` for BN254 (``(n, 12)`` / ``(n, 24)`` for
+BLS12-377, ``Context(curve="bls12_377")``, entry points ``g16_bls12_377_*``) -- i.e. gnark-crypto's memory image.
 Device-resident operands are passed as integer device pointers (``torch.Tensor.data_ptr()``); torch is
 plumbing only.  There is no CPU fallback: a missing library or GPU raises.
 """
@@ -17,6 +18,9 @@ LIB_PATH = os.path.join(_HERE, "libg16b200.so")
 DIF, DIT = 0, 1
 OUT_AR, OUT_BS1, OUT_KRS_K, OUT_KRS_HZ, OUT_BS2 = range(5)
 PROVE_OUT_BYTES = 384
+
+# curve -> (ctx_create curve_id, G1 affine u64 words, G2 affine u64 words)
+CURVES = {"bn254": (0, 8, 16), "bls12_377": (1, 12, 24)}
 
 
 class G16Error(RuntimeError):
@@ -67,17 +71,38 @@ SYMBOLS = [
     "g16_g1_add", "g16_g2_add", "g16_g1_scalar_mul", "g16_g2_scalar_mul", "g16_imad_peak", "g16_pipe_rates", "g16_ctx_stream",
 ]
 
-_lib = None
+def symbol_name(name, curve="bn254"):
+    """public name of entry point `name` (a BN254 name from SYMBOLS) for `curve` (tools/gen_curve_abi.py's rule)."""
+    if curve == "bn254":
+        return name
+    assert curve == "bls12_377", curve
+    return "g16_bls12_377_" + name[len("g16_"):].replace("_bn254", "")
 
 
-def load():
+class _CurveLib:
+    """attribute access by BN254 name, resolved to the curve's own entry point."""
+
+    def __init__(self, cdll, curve):
+        self._cdll, self._curve = cdll, curve
+
+    def __getattr__(self, name):
+        fn = getattr(self._cdll, symbol_name(name, self._curve))
+        setattr(self, name, fn)
+        return fn
+
+
+_libs = {}
+
+
+def load(curve="bn254"):
     """dlopen the in-tree library; raises if it has not been built (no fallback)."""
-    global _lib
-    if _lib is None:
+    if curve not in CURVES:
+        raise G16Error(f"unknown curve {curve!r} (have {sorted(CURVES)})")
+    if curve not in _libs:
         if not os.path.exists(LIB_PATH):
             raise G16Error(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
                            "(make -C gnark_icicle_b200/csrc); there is no CPU fallback")
-        lib = ctypes.CDLL(LIB_PATH)
+        lib = _CurveLib(ctypes.CDLL(LIB_PATH), curve)
         lib.g16_last_error.restype = ctypes.c_char_p
         lib.g16_last_error.argtypes = [ctypes.c_void_p]
         lib.g16_kernel_launch_count.restype = ctypes.c_uint64
@@ -85,8 +110,8 @@ def load():
         lib.g16_ctx_stream.argtypes = [ctypes.c_void_p]
         lib.g16_ctx_destroy.argtypes = [ctypes.c_void_p]
         lib.g16_ctx_destroy.restype = None
-        _lib = lib
-    return _lib
+        _libs[curve] = lib
+    return _libs[curve]
 
 
 def _ptr(a):
@@ -111,11 +136,14 @@ u64 = ctypes.c_uint64
 class Context:
     """One GPU, one call in flight (g16_ctx)."""
 
-    def __init__(self, device=0):
-        self._lib = load()
+    def __init__(self, device=0, curve="bn254"):
+        self._lib = load(curve)
+        self.curve = curve
+        curve_id, self.g1w, self.g2w = CURVES[curve]
+        self.prove_out_words = 4 * self.g1w + self.g2w
         self._h = ctypes.c_void_p()
         ids = (ctypes.c_int * 1)(device)
-        rc = self._lib.g16_ctx_create(ctypes.byref(self._h), 0, ids, 1)
+        rc = self._lib.g16_ctx_create(ctypes.byref(self._h), curve_id, ids, 1)
         if rc != 0:
             self._h = ctypes.c_void_p()
             raise G16Error(f"g16_ctx_create failed with status {rc} (no usable CUDA device? there is no CPU fallback)")
@@ -151,16 +179,16 @@ class Context:
         return out
 
     def msm_g1(self, scalars, bases):
-        s, p = _arr(scalars, 4), _arr(bases, 8)
+        s, p = _arr(scalars, 4), _arr(bases, self.g1w)
         assert len(s) == len(p)
-        out = np.zeros(8, dtype=np.uint64)
+        out = np.zeros(self.g1w, dtype=np.uint64)
         self._check(self._lib.g16_msm_g1(self._h, _ptr(s), _ptr(p), u64(len(s)), _ptr(out)), "g16_msm_g1")
         return out
 
     def msm_g2(self, scalars, bases):
-        s, p = _arr(scalars, 4), _arr(bases, 16)
+        s, p = _arr(scalars, 4), _arr(bases, self.g2w)
         assert len(s) == len(p)
-        out = np.zeros(16, dtype=np.uint64)
+        out = np.zeros(self.g2w, dtype=np.uint64)
         self._check(self._lib.g16_msm_g2(self._h, _ptr(s), _ptr(p), u64(len(s)), _ptr(out)), "g16_msm_g2")
         return out
 
@@ -178,24 +206,24 @@ class Context:
 
     def g1_fixed_base_mul(self, scalars):
         s = _arr(scalars, 4)
-        out = np.empty((len(s), 8), dtype=np.uint64)
+        out = np.empty((len(s), self.g1w), dtype=np.uint64)
         self._check(self._lib.g16_g1_fixed_base_mul(self._h, _ptr(s), u64(len(s)), _ptr(out)), "g16_g1_fixed_base_mul")
         return out
 
     def g2_fixed_base_mul(self, scalars):
         s = _arr(scalars, 4)
-        out = np.empty((len(s), 16), dtype=np.uint64)
+        out = np.empty((len(s), self.g2w), dtype=np.uint64)
         self._check(self._lib.g16_g2_fixed_base_mul(self._h, _ptr(s), u64(len(s)), _ptr(out)), "g16_g2_fixed_base_mul")
         return out
 
     # ---- primitives, device pointers (ints); results on host
     def msm_g1_dev(self, scalars_ptr, bases_ptr, n):
-        out = np.zeros(8, dtype=np.uint64)
+        out = np.zeros(self.g1w, dtype=np.uint64)
         self._check(self._lib.g16_msm_g1_dev(self._h, _ptr(scalars_ptr), _ptr(bases_ptr), u64(n), _ptr(out)), "g16_msm_g1_dev")
         return out
 
     def msm_g2_dev(self, scalars_ptr, bases_ptr, n):
-        out = np.zeros(16, dtype=np.uint64)
+        out = np.zeros(self.g2w, dtype=np.uint64)
         self._check(self._lib.g16_msm_g2_dev(self._h, _ptr(scalars_ptr), _ptr(bases_ptr), u64(n), _ptr(out)), "g16_msm_g2_dev")
         return out
 
@@ -214,7 +242,8 @@ class Context:
     # ---- proving key + prove
     def pk_upload(self, domain_n, g1_a, g1_b, g1_k, g1_z, g2_b, infinity_a, infinity_b, n_wires, k_index=None,
                   shard_index=0, shard_count=1):
-        g1_a, g1_b, g1_k, g1_z, g2_b = _arr(g1_a, 8), _arr(g1_b, 8), _arr(g1_k, 8), _arr(g1_z, 8), _arr(g2_b, 16)
+        g1_a, g1_b, g1_k, g1_z, g2_b = (_arr(g1_a, self.g1w), _arr(g1_b, self.g1w), _arr(g1_k, self.g1w),
+                                        _arr(g1_z, self.g1w), _arr(g2_b, self.g2w))
         ia = np.ascontiguousarray(infinity_a, dtype=np.uint8)
         ib = np.ascontiguousarray(infinity_b, dtype=np.uint8)
         ki = None if k_index is None else np.ascontiguousarray(k_index, dtype=np.uint32)
@@ -230,14 +259,14 @@ class Context:
     def prove(self, pk_handle, W, a, b, c):
         """host arrays in, (5 raw MSM points as a 48-limb array, stats dict) out."""
         W, a, b, c = _arr(W, 4), _arr(a, 4), _arr(b, 4), _arr(c, 4)
-        out = np.zeros(PROVE_OUT_BYTES // 8, dtype=np.uint64)
+        out = np.zeros(self.prove_out_words, dtype=np.uint64)
         st = Stats()
         self._check(self._lib.g16_prove_bn254(self._h, u64(pk_handle), _ptr(W), u64(len(W)), _ptr(a), _ptr(b), _ptr(c),
                                               u64(len(a)), _ptr(out), ctypes.byref(st)), "g16_prove_bn254")
         return out, st.as_dict()
 
     def prove_dev(self, pk_handle, W_ptr, a_ptr, b_ptr, c_ptr):
-        out = np.zeros(PROVE_OUT_BYTES // 8, dtype=np.uint64)
+        out = np.zeros(self.prove_out_words, dtype=np.uint64)
         st = Stats()
         self._check(self._lib.g16_prove_bn254_dev(self._h, u64(pk_handle), _ptr(W_ptr), _ptr(a_ptr), _ptr(b_ptr), _ptr(c_ptr),
                                                   _ptr(out), ctypes.byref(st)), "g16_prove_bn254_dev")
@@ -256,7 +285,7 @@ class Context:
         self._check(self._lib.g16_dist_pointwise_h_dev(self._h, _ptr(abc_ptr), u64(n_local), u64(n_global)), "g16_dist_pointwise_h_dev")
 
     def prove_msms_dev(self, pk_handle, W_ptr, h_local_ptr):
-        out = np.zeros(PROVE_OUT_BYTES // 8, dtype=np.uint64)
+        out = np.zeros(self.prove_out_words, dtype=np.uint64)
         st = Stats()
         self._check(self._lib.g16_prove_msms_dev(self._h, u64(pk_handle), _ptr(W_ptr), _ptr(h_local_ptr), _ptr(out), ctypes.byref(st)),
                     "g16_prove_msms_dev")
@@ -277,45 +306,50 @@ def _pipe_rates(self):
 Context.pipe_rates = _pipe_rates
 
 
-def kernel_launch_count():
-    return int(load().g16_kernel_launch_count())
+def kernel_launch_count(curve="bn254"):
+    return int(load(curve).g16_kernel_launch_count())
 
 
 # ---- host-only helpers (no GPU needed)
-def g1_add(a, b):
-    a, b = _arr(a, 8), _arr(b, 8)
-    out = np.zeros(8, dtype=np.uint64)
-    assert load().g16_g1_add(_ptr(a), _ptr(b), _ptr(out)) == 0
+def g1_add(a, b, curve="bn254"):
+    w = CURVES[curve][1]
+    a, b = _arr(a, w), _arr(b, w)
+    out = np.zeros(w, dtype=np.uint64)
+    assert load(curve).g16_g1_add(_ptr(a), _ptr(b), _ptr(out)) == 0
     return out
 
 
-def g2_add(a, b):
-    a, b = _arr(a, 16), _arr(b, 16)
-    out = np.zeros(16, dtype=np.uint64)
-    assert load().g16_g2_add(_ptr(a), _ptr(b), _ptr(out)) == 0
+def g2_add(a, b, curve="bn254"):
+    w = CURVES[curve][2]
+    a, b = _arr(a, w), _arr(b, w)
+    out = np.zeros(w, dtype=np.uint64)
+    assert load(curve).g16_g2_add(_ptr(a), _ptr(b), _ptr(out)) == 0
     return out
 
 
-def g1_scalar_mul(a, k):
-    a, k = _arr(a, 8), _arr(k, 4)
-    out = np.zeros(8, dtype=np.uint64)
-    assert load().g16_g1_scalar_mul(_ptr(a), _ptr(k), _ptr(out)) == 0
+def g1_scalar_mul(a, k, curve="bn254"):
+    w = CURVES[curve][1]
+    a, k = _arr(a, w), _arr(k, 4)
+    out = np.zeros(w, dtype=np.uint64)
+    assert load(curve).g16_g1_scalar_mul(_ptr(a), _ptr(k), _ptr(out)) == 0
     return out
 
 
-def g2_scalar_mul(a, k):
-    a, k = _arr(a, 16), _arr(k, 4)
-    out = np.zeros(16, dtype=np.uint64)
-    assert load().g16_g2_scalar_mul(_ptr(a), _ptr(k), _ptr(out)) == 0
+def g2_scalar_mul(a, k, curve="bn254"):
+    w = CURVES[curve][2]
+    a, k = _arr(a, w), _arr(k, 4)
+    out = np.zeros(w, dtype=np.uint64)
+    assert load(curve).g16_g2_scalar_mul(_ptr(a), _ptr(k), _ptr(out)) == 0
     return out
 
 
-def assemble_proof(pk_points, r, s, msm_points):
-    """pk_points: 80 limbs (alpha, beta, delta G1; beta, delta G2); returns 32 limbs Ar||Bs||Krs."""
+def assemble_proof(pk_points, r, s, msm_points, curve="bn254"):
+    """pk_points: alpha, beta, delta (G1), beta, delta (G2) = 56 limbs for BN254; returns Ar||Bs||Krs (32 limbs)."""
+    _, w1, w2 = CURVES[curve]
     pk_points = np.ascontiguousarray(pk_points, dtype=np.uint64).reshape(-1)
     msm_points = np.ascontiguousarray(msm_points, dtype=np.uint64).reshape(-1)
-    assert pk_points.size == 56 and msm_points.size == 48, (pk_points.size, msm_points.size)
+    assert pk_points.size == 3 * w1 + 2 * w2 and msm_points.size == 4 * w1 + w2, (pk_points.size, msm_points.size)
     r, s = _arr(r, 4), _arr(s, 4)
-    out = np.zeros(32, dtype=np.uint64)
-    assert load().g16_assemble_proof_bn254(_ptr(pk_points), _ptr(r), _ptr(s), _ptr(msm_points), _ptr(out)) == 0
+    out = np.zeros(2 * w1 + w2, dtype=np.uint64)
+    assert load(curve).g16_assemble_proof_bn254(_ptr(pk_points), _ptr(r), _ptr(s), _ptr(msm_points), _ptr(out)) == 0
     return out

@@ -1,258 +1,3 @@
-"""BN254 fields and groups on Python big ints (oracle; test infrastructure only).
-
-Restates the arithmetic the reference gets from gnark-crypto (not vendored,
-go.mod:11): fr/fp elements, E2, G1/G2 affine+Jacobian.  Memory layout follows
-gnark-crypto: an element is 4 little-endian uint64 limbs in Montgomery form,
-R = 2^256; G1Affine = X||Y, G2Affine = X.A0||X.A1||Y.A0||Y.A1;
-the point at infinity is (0,0).
-"""
-
-P = 21888242871839275222246405745257275088696311157297823662689037894645226208583
-R = 21888242871839275222246405745257275088548364400416034343698204186575808495617
-MONT_R = 1 << 256
-B1 = 3  # G1: y^2 = x^3 + 3
-G1_GEN = (1, 2)
-# G2 generator (EIP-197 / gnark-crypto bn254.Generators), Fp2 = Fp[u]/(u^2+1)
-G2_GEN = (
-    (10857046999023057135944570762232829481370756359578518086990519993285655852781,
-     11559732032986387107991004021392285783925812861821192530917403151452391805634),
-    (8495653923123431417604973247489272438418190587263600148770280649306958101930,
-     4082367875863433681332203403145435568316851327593401208105741076214120093531),
-)
-FR_GEN = 5          # fft.Domain FrMultiplicativeGen for BN254 (coset shift)
-FR_TWO_ADICITY = 28
-# primitive 2^28-th root of unity of Fr (5^((r-1)/2^28))
-FR_ROOT_2_28 = pow(5, (R - 1) >> 28, R)
-
-
-def inv(a, m):
-    return pow(a, -1, m)
-
-
-# ---------------------------------------------------------------- Fp2
-def f2_add(a, b):
-    return ((a[0] + b[0]) % P, (a[1] + b[1]) % P)
-
-
-def f2_sub(a, b):
-    return ((a[0] - b[0]) % P, (a[1] - b[1]) % P)
-
-
-def f2_neg(a):
-    return ((-a[0]) % P, (-a[1]) % P)
-
-
-def f2_mul(a, b):
-    return ((a[0] * b[0] - a[1] * b[1]) % P, (a[0] * b[1] + a[1] * b[0]) % P)
-
-
-def f2_sqr(a):
-    return f2_mul(a, a)
-
-
-def f2_scalar(a, k):
-    return (a[0] * k % P, a[1] * k % P)
-
-
-def f2_inv(a):
-    d = inv((a[0] * a[0] + a[1] * a[1]) % P, P)
-    return (a[0] * d % P, (-a[1]) * d % P)
-
-
-F2_ZERO = (0, 0)
-F2_ONE = (1, 0)
-# twist coefficient b' = 3/(9+u)
-B2 = f2_mul((3, 0), f2_inv((9, 1)))
-
-
-class _Fp:
-    zero = 0
-    one = 1
-    add = staticmethod(lambda a, b: (a + b) % P)
-    sub = staticmethod(lambda a, b: (a - b) % P)
-    mul = staticmethod(lambda a, b: a * b % P)
-    neg = staticmethod(lambda a: (-a) % P)
-    inv = staticmethod(lambda a: inv(a, P))
-    b = B1
-
-
-class _Fp2:
-    zero = F2_ZERO
-    one = F2_ONE
-    add = staticmethod(f2_add)
-    sub = staticmethod(f2_sub)
-    mul = staticmethod(f2_mul)
-    neg = staticmethod(f2_neg)
-    inv = staticmethod(f2_inv)
-    b = B2
-
-
-# ---------------------------------------------------------------- curve ops
-# Affine points are (x, y) or None for infinity.  Jacobian points are (X,Y,Z).
-def _is_on_curve(F, pt):
-    if pt is None:
-        return True
-    x, y = pt
-    return F.mul(y, y) == F.add(F.mul(F.mul(x, x), x), F.b)
-
-
-def _aff_neg(F, pt):
-    return None if pt is None else (pt[0], F.neg(pt[1]))
-
-
-def _jac_double(F, p):
-    X, Y, Z = p
-    if Z == F.zero:
-        return p
-    A = F.mul(X, X)
-    Bq = F.mul(Y, Y)
-    C = F.mul(Bq, Bq)
-    t = F.add(X, Bq)
-    D = F.sub(F.sub(F.mul(t, t), A), C)
-    D = F.add(D, D)
-    E = F.add(F.add(A, A), A)
-    Fq = F.mul(E, E)
-    X3 = F.sub(Fq, F.add(D, D))
-    C8 = F.add(C, C)
-    C8 = F.add(C8, C8)
-    C8 = F.add(C8, C8)
-    Y3 = F.sub(F.mul(E, F.sub(D, X3)), C8)
-    Z3 = F.mul(Y, Z)
-    Z3 = F.add(Z3, Z3)
-    return (X3, Y3, Z3)
-
-
-def _jac_add(F, p, q):
-    if p[2] == F.zero:
-        return q
-    if q[2] == F.zero:
-        return p
-    X1, Y1, Z1 = p
-    X2, Y2, Z2 = q
-    Z1Z1 = F.mul(Z1, Z1)
-    Z2Z2 = F.mul(Z2, Z2)
-    U1 = F.mul(X1, Z2Z2)
-    U2 = F.mul(X2, Z1Z1)
-    S1 = F.mul(F.mul(Y1, Z2), Z2Z2)
-    S2 = F.mul(F.mul(Y2, Z1), Z1Z1)
-    if U1 == U2:
-        if S1 == S2:
-            return _jac_double(F, p)
-        return (F.one, F.one, F.zero)
-    H = F.sub(U2, U1)
-    Rr = F.sub(S2, S1)
-    HH = F.mul(H, H)
-    HHH = F.mul(H, HH)
-    V = F.mul(U1, HH)
-    X3 = F.sub(F.sub(F.mul(Rr, Rr), HHH), F.add(V, V))
-    Y3 = F.sub(F.mul(Rr, F.sub(V, X3)), F.mul(S1, HHH))
-    Z3 = F.mul(F.mul(Z1, Z2), H)
-    return (X3, Y3, Z3)
-
-
-def _to_jac(F, pt):
-    return (F.one, F.one, F.zero) if pt is None else (pt[0], pt[1], F.one)
-
-
-def _to_aff(F, p):
-    if p[2] == F.zero:
-        return None
-    zi = F.inv(p[2])
-    zi2 = F.mul(zi, zi)
-    return (F.mul(p[0], zi2), F.mul(p[1], F.mul(zi2, zi)))
-
-
-def _scalar_mul(F, pt, k):
-    """double-and-add, affine in / affine out; k reduced mod r."""
-    k %= R
-    acc = (F.one, F.one, F.zero)
-    base = _to_jac(F, pt)
-    while k:
-        if k & 1:
-            acc = _jac_add(F, acc, base)
-        base = _jac_double(F, base)
-        k >>= 1
-    return _to_aff(F, acc)
-
-
-def _aff_add(F, a, b):
-    return _to_aff(F, _jac_add(F, _to_jac(F, a), _to_jac(F, b)))
-
-
-# G1
-def g1_on_curve(pt): return _is_on_curve(_Fp, pt)
-def g1_neg(pt): return _aff_neg(_Fp, pt)
-def g1_add(a, b): return _aff_add(_Fp, a, b)
-def g1_mul(pt, k): return _scalar_mul(_Fp, pt, k)
-def g1_jac_add(p, q): return _jac_add(_Fp, p, q)
-def g1_jac_double(p): return _jac_double(_Fp, p)
-def g1_to_jac(pt): return _to_jac(_Fp, pt)
-def g1_to_aff(p): return _to_aff(_Fp, p)
-
-
-# G2
-def g2_on_curve(pt): return _is_on_curve(_Fp2, pt)
-def g2_neg(pt): return _aff_neg(_Fp2, pt)
-def g2_add(a, b): return _aff_add(_Fp2, a, b)
-def g2_mul(pt, k): return _scalar_mul(_Fp2, pt, k)
-def g2_jac_add(p, q): return _jac_add(_Fp2, p, q)
-def g2_jac_double(p): return _jac_double(_Fp2, p)
-def g2_to_jac(pt): return _to_jac(_Fp2, pt)
-def g2_to_aff(p): return _to_aff(_Fp2, p)
-
-
-# ---------------------------------------------------------------- gnark memory layout
-def _enc(v, m):
-    return ((v * MONT_R) % m).to_bytes(32, "little")
-
-
-def _dec(b, m):
-    return (int.from_bytes(b, "little") * inv(MONT_R, m)) % m
-
-
-_RINV_R = inv(MONT_R, R)
-_RINV_P = inv(MONT_R, P)
-
-
-def fr_to_bytes(v): return _enc(v % R, R)
-def fr_from_bytes(b): return int.from_bytes(b, "little") * _RINV_R % R
-def fp_to_bytes(v): return _enc(v % P, P)
-def fp_from_bytes(b): return int.from_bytes(b, "little") * _RINV_P % P
-
-
-def fr_vec_to_bytes(vs):
-    return b"".join(fr_to_bytes(v) for v in vs)
-
-
-def fr_vec_from_bytes(buf):
-    return [fr_from_bytes(buf[i:i + 32]) for i in range(0, len(buf), 32)]
-
-
-def g1_to_bytes(pt):
-    if pt is None:
-        return bytes(64)
-    return fp_to_bytes(pt[0]) + fp_to_bytes(pt[1])
-
-
-def g1_from_bytes(b):
-    if b == bytes(64):
-        return None
-    return (fp_from_bytes(b[:32]), fp_from_bytes(b[32:64]))
-
-
-def g2_to_bytes(pt):
-    if pt is None:
-        return bytes(128)
-    (x0, x1), (y0, y1) = pt
-    return fp_to_bytes(x0) + fp_to_bytes(x1) + fp_to_bytes(y0) + fp_to_bytes(y1)
-
-
-def g2_from_bytes(b):
-    if b == bytes(128):
-        return None
-    v = [fp_from_bytes(b[i:i + 32]) for i in range(0, 128, 32)]
-    return ((v[0], v[1]), (v[2], v[3]))
-
-
-def g1_vec_to_bytes(pts): return b"".join(g1_to_bytes(p) for p in pts)
-def g2_vec_to_bytes(pts): return b"".join(g2_to_bytes(p) for p in pts)
+"""BN254 instance of oracle.curve (kept as the historical import name)."""
+from .curve import *  # noqa: F401,F403
+from .curve import _Fp, _Fp2  # noqa: F401

@@ -7,11 +7,14 @@ have none; commitment handling is SURVEY.md 8(f) N3).  r, s and the toxic waste
 are injected so proofs are reproducible byte for byte.
 """
 import heapq
-from . import bn254 as C
-from .bn254 import R, inv
+from . import curve as C
+from .curve import R, inv
 from .ntt import Domain, bit_reverse_list, compute_h
 from .msm import batch_scalar_mul_gen, msm_pippenger
-from .pairing import pairing_product, F12_ONE
+if C.NAME == "bn254":
+    from .pairing import pairing_product
+else:
+    pairing_product = None   # BLS12-377: no restated pairing; proofs are checked on the exponent side (trapdoor)
 
 
 def filter_heap(slice_, first_index, to_remove):
@@ -108,7 +111,7 @@ def setup(cs, rng, tw=None):
     pk.g2_beta, pk.g2_delta = g2[len(B_nz)], g2[len(B_nz) + 1]
     vk.g2_delta, vk.g2_gamma = g2[len(B_nz) + 1], g2[len(B_nz) + 2]
     vk.g1_alpha, vk.g2_beta = pk.g1_alpha, pk.g2_beta
-    vk.e = pairing_product([(vk.g1_alpha, vk.g2_beta)])   # vk.Precompute setup.go:353-362
+    vk.e = pairing_product([(vk.g1_alpha, vk.g2_beta)]) if pairing_product else None   # vk.Precompute setup.go:353-362
     pk.domain = d
     pk.nb_public = nb_pub
     scal = dict(A=A_nz, B=B_nz, Z=Zbr, K=pkK, tw=tw)
@@ -158,6 +161,8 @@ def proof_bytes(proof):
 
 def verify(proof, vk, public_witness):
     """verify.go:49-148 (no commitments): e(Krs,-delta) e(Ar,Bs) e(kSum,-gamma) == e(alpha,beta)."""
+    if pairing_product is None:
+        raise NotImplementedError("the restated pairing check exists for BN254 only")
     if len(public_witness) != len(vk.g1_k) - 1:
         raise ValueError("invalid witness size")
     for pt, on in ((proof["ar"], C.g1_on_curve), (proof["krs"], C.g1_on_curve), (proof["bs"], C.g2_on_curve)):

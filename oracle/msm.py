@@ -6,7 +6,7 @@ the group element sum_i s_i * P_i, compared in affine form.
 Two independent algorithms (double-and-add, bucket method) cross-check each
 other in tests/test_oracle_msm.py.
 """
-from . import bn254 as C
+from . import curve as C
 
 
 def msm_naive(points, scalars, g2=False):

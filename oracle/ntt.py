@@ -10,7 +10,7 @@ Restates gnark-crypto's fft.Domain as the reference uses it
 Results are exact field elements, so any correct algorithm is byte-identical
 (SURVEY.md F6).
 """
-from .bn254 import R, FR_GEN, FR_ROOT_2_28, FR_TWO_ADICITY, inv
+from .curve import R, FR_GEN, FR_ROOT, FR_TWO_ADICITY, inv
 
 
 def bitrev(i, logn):
@@ -38,7 +38,7 @@ class Domain:
         self.n = n
         self.logn = n.bit_length() - 1
         assert self.logn <= FR_TWO_ADICITY
-        self.gen = pow(FR_ROOT_2_28, 1 << (FR_TWO_ADICITY - self.logn), R)
+        self.gen = pow(FR_ROOT, 1 << (FR_TWO_ADICITY - self.logn), R)
         self.gen_inv = inv(self.gen, R)
         self.n_inv = inv(n, R)
         self.coset = FR_GEN

@@ -7,7 +7,7 @@ same proofs, so this follows the textbook construction: Fp12 = Fp[w]/(w^12 -
 18 w^6 + 82), G2 untwisted into E(Fp12), Miller loop over 6x+2 with the two
 Frobenius correction steps, final exponent (p^12-1)/r.
 """
-from .bn254 import P, R, inv
+from .curve import P, R, inv
 
 _MOD = (82, 0, 0, 0, 0, 0, -18, 0, 0, 0, 0, 0)   # w^12 = 18 w^6 - 82
 ATE_LOOP = 29793968203157093288                  # 6x+2, x = 4965661367192848881

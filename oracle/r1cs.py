@@ -6,7 +6,7 @@ internal...].  A constraint is (L, R, O), each a list of (coeff, wire) with
 L.w * R.w == O.w (constraint/bn254/solver.go:540-628 accumulates exactly these
 three inner products into a[c], b[c], c[c]).
 """
-from .bn254 import R
+from .curve import R
 
 
 class R1CS:
@@ -64,15 +64,18 @@ def cubic_witness(x, y):
     return [1, y % R, x, x * x % R, x * x * x % R]
 
 
-def mimc_chain(nb_constraints, rng):
-    """MiMC-shaped chain (std/hash/mimc/encrypt.go:124-128,147-153, pow5 rounds):
+def mimc_chain(nb_constraints, rng, power=5):
+    """MiMC-shaped chain (std/hash/mimc/encrypt.go:124-128,147-153, pow5 rounds; power=17 gives the BLS12-377
+    round of encrypt.go:137-143: four squarings and one product, 5 constraints per round):
     x <- (x + k + c_i)^5, 3 constraints per round, then one assertion that binds
     the public output; filler squarings bring the count to exactly nb_constraints.
     Wires: 0=ONE 1=OUT(public) 2=X0(secret) 3=K(secret).  Returns (cs, consts)."""
     cs = R1CS(nb_public=2, nb_secret=2)
     consts = []
     x = [(1, 2)]            # linear expression for the running state
-    rounds = (nb_constraints - 1) // 3
+    assert power in (5, 17)
+    per_round = 3 if power == 5 else 5
+    rounds = (nb_constraints - 1) // per_round
     for _ in range(rounds):
         ci = rng.field(R)
         consts.append(ci)
@@ -81,6 +84,11 @@ def mimc_chain(nb_constraints, rng):
         cs.add(t, t, [(1, u)])
         v = cs.new_internal()
         cs.add([(1, u)], [(1, u)], [(1, v)])
+        if power == 17:
+            for _ in range(2):
+                v2 = cs.new_internal()
+                cs.add([(1, v)], [(1, v)], [(1, v2)])
+                v = v2
         nx = cs.new_internal()
         cs.add([(1, v)], t, [(1, nx)])
         x = [(1, nx)]
