@@ -23,7 +23,8 @@ import numpy as np
 from . import lib as _lib
 
 HasIcicle = True
-_FR_MOD = 21888242871839275222246405745257275088548364400416034343698204186575808495617
+_FR_MOD = {"bn254": 21888242871839275222246405745257275088548364400416034343698204186575808495617,
+           "bls12_377": 8444461749428370424248824938781546531375899335154063827935233455917409239041}
 
 
 # ---- backend.ProverOption (backend/backend.go:66-147)
@@ -75,8 +76,8 @@ class R1CSSolution:
 @dataclass
 class Proof:
     """prove.go:44-49 (no commitments): raw gnark memory images."""
-    Ar: np.ndarray    # (8,)  G1Affine
-    Bs: np.ndarray    # (16,) G2Affine
+    Ar: np.ndarray    # (8,)  G1Affine   ((12,) for BLS12-377)
+    Bs: np.ndarray    # (16,) G2Affine   ((24,))
     Krs: np.ndarray   # (8,)  G1Affine
 
     def raw(self):
@@ -103,13 +104,14 @@ class ProvingKey:
     nb_public: int
     commitment_keys: list = _field(default_factory=list)
     device: object = None     # deviceInfo (provingkey.go:10-23): (Context, handle)
+    curve: str = "bn254"      # "bls12_377": 12/24-limb points, the g16_bls12_377_* entry points (config 5)
 
     def setup_device_pointers(self, cfg=None):
         """icicle.go:31-130: one-time upload; lazily on first Prove (icicle.go:145-150)."""
         if self.device is not None:
             return
         cfg = cfg or ProverConfig()
-        ctx = _lib.Context(cfg.device)
+        ctx = _lib.Context(cfg.device, curve=self.curve)
         handle = ctx.pk_upload(self.domain_n, self.g1_a, self.g1_b, self.g1_k, self.g1_z, self.g2_b,
                                self.infinity_a, self.infinity_b, self.nb_wires,
                                shard_index=cfg.shard_index, shard_count=cfg.shard_count)
@@ -127,8 +129,8 @@ class ProvingKey:
             self.device = None
 
 
-def _random_fr():
-    v = secrets.randbelow(_FR_MOD)
+def _random_fr(curve="bn254"):
+    v = secrets.randbelow(_FR_MOD[curve])
     return np.array([(v >> (64 * i)) & 0xFFFFFFFFFFFFFFFF for i in range(4)], dtype=np.uint64)
 
 
@@ -155,8 +157,8 @@ def Prove(r1cs, pk, full_witness, *opts):
         raise NotImplementedError("BSB22 commitments are outside this round's scope (SURVEY.md 8(f) N3)")
     sol = full_witness if r1cs is None else r1cs.solve(full_witness)
     points, stats = prove_msms(pk, sol, cfg)
-    r = cfg.r if cfg.r is not None else _random_fr()
-    s = cfg.s if cfg.s is not None else _random_fr()
+    r = cfg.r if cfg.r is not None else _random_fr(pk.curve)
+    s = cfg.s if cfg.s is not None else _random_fr(pk.curve)
     proof = assemble(pk, points, r, s)
     proof.stats = stats
     return proof
@@ -164,16 +166,18 @@ def Prove(r1cs, pk, full_witness, *opts):
 
 def assemble(pk, msm_points, r, s):
     """host epilogue (icicle.go:281-295,306-307,319-321,362-372,386-391) on already-combined MSM points."""
-    out = _lib.assemble_proof(pk.pk_points(), r, s, msm_points)
-    return Proof(Ar=out[0:8].copy(), Bs=out[8:24].copy(), Krs=out[24:32].copy())
+    out = _lib.assemble_proof(pk.pk_points(), r, s, msm_points, curve=pk.curve)
+    _, w1, w2 = _lib.CURVES[pk.curve]
+    return Proof(Ar=out[0:w1].copy(), Bs=out[w1:w1 + w2].copy(), Krs=out[w1 + w2:].copy())
 
 
-def combine_shards(point_blocks):
-    """Sum the per-shard raw MSM blocks (each 48 limbs) of a point-range-sharded prove."""
+def combine_shards(point_blocks, curve="bn254"):
+    """Sum the per-shard raw MSM blocks (each 48 limbs for BN254) of a point-range-sharded prove."""
+    _, w1, w2 = _lib.CURVES[curve]
     acc = np.array(point_blocks[0], dtype=np.uint64).copy()
     for blk in point_blocks[1:]:
         blk = np.asarray(blk, dtype=np.uint64)
         for i in range(4):
-            acc[8 * i:8 * i + 8] = _lib.g1_add(acc[8 * i:8 * i + 8], blk[8 * i:8 * i + 8])
-        acc[32:48] = _lib.g2_add(acc[32:48], blk[32:48])
+            acc[w1 * i:w1 * i + w1] = _lib.g1_add(acc[w1 * i:w1 * i + w1], blk[w1 * i:w1 * i + w1], curve=curve)
+        acc[4 * w1:] = _lib.g2_add(acc[4 * w1:], blk[4 * w1:], curve=curve)
     return acc
