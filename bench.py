@@ -25,9 +25,11 @@ sys.path.insert(0, ROOT)
 
 import numpy as np  # noqa: E402
 
-FR_TOP_MASK = 0x0FFFFFFFFFFFFFFF   # any 252-bit value is a valid (Montgomery) Fr / scalar
-IMAD_EQ_PER_FP_MUL = 272           # (2*8^2 + 8) limb-MACs x 2
+FR_TOP_MASK = 0x0FFFFFFFFFFFFFFF   # any 252-bit value is a valid (Montgomery) Fr / scalar (both curves: r > 2^252)
+IMAD_EQ_PER_FP_MUL = 272           # (2*8^2 + 8) limb-MACs x 2; 8-limb fields: BN254 Fp/Fr, BLS12-377 Fr
+IMAD_EQ_PER_FP_MUL_12 = 600        # same formula for the 12-limb BLS12-377 Fp
 MADD_MULS = {"g1": 10, "g2": 30}
+CURVE_NAMES = {"bn254": "bn254", "bls12_377": "bls12_377"}
 
 
 def peaks():
@@ -81,13 +83,17 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ workload
-def chain_shape(nc):
-    """infinity masks with the MiMC-chain shape (the u = t*t wires never appear in R)."""
+def chain_shape(nc, power=5):
+    """infinity masks with the MiMC-chain shape (pow5 rounds, the u = t*t wires never appear in R; pow17
+    rounds (BLS12-377, encrypt.go:137-143) are 5 constraints of which the t^16 wire only appears in L)."""
     nw = nc + 3
     inf_a = np.zeros(nw, dtype=np.uint8)
     inf_b = np.zeros(nw, dtype=np.uint8)
     inf_a[1] = 1
-    inf_b[4::3] = 1
+    if power == 5:
+        inf_b[4::3] = 1
+    else:
+        inf_b[7::5] = 1
     inf_b[1] = 1
     return nw, inf_a, inf_b
 
@@ -103,21 +109,21 @@ def build_inputs(torch, ctx, nc, dev, seed=20260422):
     n = 1
     while n < nc:
         n <<= 1
-    nw, inf_a, inf_b = chain_shape(nc)
+    nw, inf_a, inf_b = chain_shape(nc, 5 if ctx.curve == "bn254" else 17)
     gen = torch.Generator(device=dev)
     gen.manual_seed(seed)
     na, nb, nk, nz = int((inf_a == 0).sum()), int((inf_b == 0).sum()), nw - 2, n - 1
 
     def g1_bases(cnt):
         k = rand_fr_cuda(torch, cnt, gen, dev)
-        out = torch.empty((cnt, 8), dtype=torch.int64, device=dev)
+        out = torch.empty((cnt, ctx.g1w), dtype=torch.int64, device=dev)
         ctx.g1_fixed_base_mul_dev(k.data_ptr(), cnt, out.data_ptr())
         return out.cpu().numpy().view(np.uint64)
 
     key = dict(domain_n=n, n_wires=nw, inf_a=inf_a, inf_b=inf_b,
                g1_a=g1_bases(na), g1_b=g1_bases(nb), g1_k=g1_bases(nk), g1_z=g1_bases(nz))
     k2 = rand_fr_cuda(torch, nb, gen, dev)
-    out2 = torch.empty((nb, 16), dtype=torch.int64, device=dev)
+    out2 = torch.empty((nb, ctx.g2w), dtype=torch.int64, device=dev)
     ctx.g2_fixed_base_mul_dev(k2.data_ptr(), nb, out2.data_ptr())
     key["g2_b"] = out2.cpu().numpy().view(np.uint64)
     del k2, out2
@@ -227,7 +233,8 @@ def run_ours(args):
         if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
             os.environ["NCCL_DEBUG"] = "WARN"       # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
         dist.init_process_group("nccl", device_id=dev)
-    ctx = lib.Context(local)
+    ctx = lib.Context(local, curve=args.curve)
+    fp_eq = IMAD_EQ_PER_FP_MUL if args.curve == "bn254" else IMAD_EQ_PER_FP_MUL_12
     ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
     nc = 1 << args.log_n
     key, sd, sh, n, nw = build_inputs(torch, ctx, nc, dev)
@@ -236,7 +243,7 @@ def run_ours(args):
     sizes = {k: int(len(key[k])) for k in ("g1_a", "g1_b", "g1_k", "g1_z", "g2_b")}
     del key
     wa, wb, wc = (torch.empty_like(sd[k]) for k in ("a", "b", "c"))
-    gather = [torch.empty(48, dtype=torch.int64, device=dev) for _ in range(world)] if world > 1 else None
+    gather = [torch.empty(ctx.prove_out_words, dtype=torch.int64, device=dev) for _ in range(world)] if world > 1 else None
 
     def combine(pts):
         if world == 1:
@@ -245,7 +252,7 @@ def run_ours(args):
         dist.all_gather(gather, t)                      # 384 B per rank over NCCL/NVLink
         if rank != 0:
             return pts
-        return g16.combine_shards([g.cpu().numpy().view(np.uint64) for g in gather])
+        return g16.combine_shards([g.cpu().numpy().view(np.uint64) for g in gather], curve=args.curve)
 
     hW, ha, hb, hc = (sh[k].numpy().view(np.uint64) for k in ("W", "a", "b", "c"))
     if world == 1:
@@ -288,10 +295,10 @@ def run_ours(args):
             st["h2d_bytes"] = W_stage.numel() * 8 + abc_pin.numel() * 8
             return pts, st
 
-    l0 = lib.kernel_launch_count()
+    l0 = lib.kernel_launch_count(args.curve)
     with ClockSampler(local) as clk:
         ms_dev, (pts_dev, st) = timed(torch, ext, step_dev, args.steps, args.warmup, world, dist)
-    launches = (lib.kernel_launch_count() - l0) * args.steps // (args.steps + args.warmup)
+    launches = (lib.kernel_launch_count(args.curve) - l0) * args.steps // (args.steps + args.warmup)
     ms_e2e, (pts_e2e, st_e) = timed(torch, ext, step_e2e, args.steps, args.warmup, world, dist)
     if rank == 0 and not np.array_equal(pts_dev, pts_e2e):
         raise SystemExit("bench.py: device-resident and host-buffer proofs differ")
@@ -307,20 +314,20 @@ def run_ours(args):
             dist.destroy_process_group()
         return
     imad, wide = ctx.imad_peak()
-    wide_x, fr_mul = ctx.pipe_rates()
+    wide_x, fr_mul, fp_mul = ctx.pipe_rates()
     # dominant kernel: k_accumulate<G1> (4 launches per step); algorithmic IMAD-equivalents per launch =
     # entries (points x windows) x 10 Fp multiplications per XYZZ mixed add x 272
-    g1_ops = sum(st["msm_n"][i] * st["msm_windows"][i] for i in range(4)) * MADD_MULS["g1"] * IMAD_EQ_PER_FP_MUL
+    g1_ops = sum(st["msm_n"][i] * st["msm_windows"][i] for i in range(4)) * MADD_MULS["g1"] * fp_eq
     g1_ms = sum(st["ms_accumulate"][:4])
-    g2_ops = st["msm_n"][4] * st["msm_windows"][4] * MADD_MULS["g2"] * IMAD_EQ_PER_FP_MUL
+    g2_ops = st["msm_n"][4] * st["msm_windows"][4] * MADD_MULS["g2"] * fp_eq
     g2_ms = st["ms_accumulate"][4]
     ach = g1_ops / (g1_ms * 1e-3) / 1e12
     roof = {"bound": "int32-imad", "kernel": "k_accumulate<G1> (4 launches/step)", "achieved": ach, "peak": imad / 1e12,
             "unit": "TIMAD/s", "frac": ach / (imad / 1e12), "traffic": None,
             "peak_source": "g16_imad_peak microbenchmark, same run (independent mad.lo.u32 chains on all SMs)",
             "imad_wide_peak_tops": wide / 1e12, "imad_wide_carry_peak_tops": wide_x / 1e12,
-            "field_mul_peak_g_per_s": fr_mul / 1e9, "field_mul_achieved_g_per_s": g1_ops / IMAD_EQ_PER_FP_MUL / (g1_ms * 1e-3) / 1e9,
-            "frac_of_multiplier_ceiling": g1_ops / IMAD_EQ_PER_FP_MUL / (g1_ms * 1e-3) / fr_mul,
+            "field_mul_peak_g_per_s": fp_mul / 1e9, "field_mul_achieved_g_per_s": g1_ops / fp_eq / (g1_ms * 1e-3) / 1e9,
+            "frac_of_multiplier_ceiling": g1_ops / fp_eq / (g1_ms * 1e-3) / fp_mul,
             "g2": {"kernel": "k_accumulate<G2>", "achieved": g2_ops / (g2_ms * 1e-3) / 1e12,
                    "frac": g2_ops / (g2_ms * 1e-3) / imad},
             "share_of_step": (g1_ms + g2_ms) / st["ms_total"],
@@ -328,12 +335,12 @@ def run_ours(args):
     pk_, src = peaks()
     # HBM view of the same kernel: 64 B affine point + 4 B sorted index per bucket entry; `traffic` is
     # dram__bytes_read+write per launch of the 2^22-point launch from the ncu --set full capture in profiles/
-    g1_bytes = sum(st["msm_n"][i] * st["msm_windows"][i] for i in range(4)) * 68
+    g1_bytes = sum(st["msm_n"][i] * st["msm_windows"][i] for i in range(4)) * (8 * ctx.g1w + 4)
     roof["hbm"] = {"bound": "hbm", "achieved": g1_bytes / (g1_ms * 1e-3) / 1e9, "peak": pk_["hbm_gbs"], "unit": "GB/s",
                    "frac": g1_bytes / (g1_ms * 1e-3) / 1e9 / pk_["hbm_gbs"], "peak_source": src,
                    "algorithmic_bytes_per_launch_2p22": (1 << 22) * 16 * 68,
                    "note": "the accumulate kernel is bound by the integer multiplier, not HBM: it moves <10 % of the copy bandwidth"}
-    if args.log_n == 22:
+    if args.log_n == 22 and args.curve == "bn254":
         roof["traffic"] = 7.06e9
         roof["traffic_source"] = "profiles/r01b_accumulate_2p22_ncu_raw.csv: 6.95 GB read + 0.11 GB written per 2^22-point launch (12.04 ms)"
     ntt_bytes = 7 * 64 * n
@@ -343,10 +350,11 @@ def run_ours(args):
                          "peak_source": src, "note": "7 transforms x 64n B algorithmic; the butterflies are IMAD-bound at 254 bits"}
     else:
       roof["compute_h"] = {"note": "distributed four-step computeH: timed inside the step, not per kernel"}
-    line = {"metric": "groth16_bn254_prove_ms", "value": ms_dev, "unit": "ms", "n_gpus": world, "steps": args.steps,
+    cname, shape = args.curve, ("mimc_chain" if args.curve == "bn254" else "mimc17_chain")
+    line = {"metric": f"groth16_{cname}_prove_ms", "value": ms_dev, "unit": "ms", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_dev, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
-            "dtype": "u32x8-montgomery", "data": "synthetic",
-            "config": {"workload": f"groth16_bn254_prove_2p{args.log_n}_mimc_chain", "constraints": nc, "domain": n,
+            "dtype": "u32x8-montgomery" if cname == "bn254" else "u32x12-montgomery", "data": "synthetic",
+            "config": {"workload": f"groth16_{cname}_prove_2p{args.log_n}_{shape}", "constraints": nc, "domain": n,
                        "msm_sizes": sizes, "parallelism": f"MSM point-range shards x{world}" + (", four-step computeH (NCCL all-to-all)" if world > 1 else ""), "l2": "inputs larger than L2",
                        "key": "synthetic distinct bases (fixed-base kernel), MiMC-chain infinity shape"},
             "e2e": {"value": ms_e2e, "unit": "ms", "h2d_bytes_per_step": int(st_e["h2d_bytes"]),
@@ -354,7 +362,13 @@ def run_ours(args):
             "gpu_launches": int(launches), "clocks": clk.summary(), "roofline": roof,
             "stages_ms": {"serialised_total": st["ms_total"], "compute_h": st["ms_compute_h"], "msm": st["ms_msm"], "accumulate": st["ms_accumulate"],
                           "host_epilogue": st["ms_host"], "msm_c": st["msm_c"], "e2e_h2d": st_e["ms_h2d"]}}
-    if world == 1 and not args.no_extras:
+    if world == 1 and args.curve != "bn254":
+        line["cpu_baseline"] = None
+        line["cpu_baseline_note"] = ("the C restatement of the CPU prover (oracle/c) exists for BN254 only; the BLS12-377 "
+                                     "oracle is Python big-int code and is a checker, not a timing baseline")
+        if not args.no_extras:
+            line["extras"] = extras(torch, ctx, ext, dev, pk_, imad, full=args.sweep)
+    elif world == 1 and not args.no_extras:
         line["extras"] = extras(torch, ctx, ext, dev, pk_, imad, full=args.sweep)
         ms_cpu, cores = cpu_prove_sample(args.cpu_log_n)
         scale = cpu_scale(args.cpu_log_n, args.log_n)
@@ -389,7 +403,7 @@ def extras(torch, ctx, ext, dev, pk_, imad, full=False):
     for logn in (range(16, 27) if full else (20, 22, 24)):
         m = 1 << logn
         k = rand_fr_cuda(torch, m, gen, dev)
-        bases = torch.empty((m, 8), dtype=torch.int64, device=dev)
+        bases = torch.empty((m, ctx.g1w), dtype=torch.int64, device=dev)
         ctx.g1_fixed_base_mul_dev(k.data_ptr(), m, bases.data_ptr())
         s = rand_fr_cuda(torch, m, gen, dev)
         ms = ev_time(lambda: ctx.msm_g1_dev(s.data_ptr(), bases.data_ptr(), m))
@@ -397,7 +411,7 @@ def extras(torch, ctx, ext, dev, pk_, imad, full=False):
         del k, bases, s
     m = 1 << 20
     k = rand_fr_cuda(torch, m, gen, dev)
-    b2 = torch.empty((m, 16), dtype=torch.int64, device=dev)
+    b2 = torch.empty((m, ctx.g2w), dtype=torch.int64, device=dev)
     ctx.g2_fixed_base_mul_dev(k.data_ptr(), m, b2.data_ptr())
     s = rand_fr_cuda(torch, m, gen, dev)
     ms = ev_time(lambda: ctx.msm_g2_dev(s.data_ptr(), b2.data_ptr(), m))
@@ -433,6 +447,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--log-n", type=int, default=22, help="log2 of the constraint count (BASELINE: 22)")
     ap.add_argument("--cpu-log-n", type=int, default=18, help="log2 constraints of the bounded CPU sample")
+    ap.add_argument("--curve", default="bn254", choices=["bn254", "bls12_377"],
+                    help="bls12_377 = BASELINE config 5 (use --log-n 24); the default line is the BN254 headline")
     ap.add_argument("--no-extras", action="store_true")
     ap.add_argument("--sweep", action="store_true", help="extras = the full 2^16..2^26 MSM and NTT sweeps (configs 2, 3)")
     args = ap.parse_args()

@@ -680,17 +680,18 @@ __global__ void __launch_bounds__(256) k_wide_carry_peak(uint32_t* sink, uint32_
 }
 
 // 4 independent Montgomery multiplications per iteration, all in registers
+template <class F>
 __global__ void __launch_bounds__(256) k_fr_mul_peak(uint32_t* sink, uint32_t seed, int iters) {
-    Fr::T x[4], y = Fr::one();
+    typename F::T x[4], y = F::one();
     y.l[0] += seed + threadIdx.x;
-    for (int c = 0; c < 4; c++) { x[c] = Fr::r2(); x[c].l[0] += c + threadIdx.x; }
+    for (int c = 0; c < 4; c++) { x[c] = F::r2(); x[c].l[0] += c + threadIdx.x; }
     for (int i = 0; i < iters; i++) {
 #pragma unroll
-        for (int c = 0; c < 4; c++) x[c] = Fr::mul(x[c], y);
+        for (int c = 0; c < 4; c++) x[c] = F::mul(x[c], y);
     }
     uint32_t v = 0;
     for (int c = 0; c < 4; c++)
-        for (int k = 0; k < 8; k++) v ^= x[c].l[k];
+        for (int k = 0; k < F::N; k++) v ^= x[c].l[k];
     if (v == 0x12345678u) sink[0] = v;
 }
 
@@ -713,7 +714,7 @@ double rate_of(g16_ctx* ctx, K launch, double ops_per_launch) {
 
 }  // namespace
 
-// out[0] = IMAD.WIDE.U32.X (carry chain) issue rate per second; out[1] = in-register Fr multiplications per second
+// out[0] = IMAD.WIDE.U32.X (carry chain) issue rate per second; out[1] / out[2] = in-register Fr / Fp multiplications per second
 extern "C" int g16_pipe_rates(g16_ctx* ctx, double* out2) {
     return guarded(ctx, [&] {
         if (!out2) throw std::runtime_error("null argument");
@@ -725,7 +726,9 @@ extern "C" int g16_pipe_rates(g16_ctx* ctx, double* out2) {
         cudaStream_t st = ctx->stream;
         out2[0] = rate_of(ctx, [&](int small) { k_wide_carry_peak<<<blocks, 256, 0, st>>>(sink, 3, small ? small : it1); G16_LAUNCH_CHECK(); },
                           (double)blocks * 256 * it1 * 16);
-        out2[1] = rate_of(ctx, [&](int small) { k_fr_mul_peak<<<blocks, 256, 0, st>>>(sink, 3, small ? small : it2); G16_LAUNCH_CHECK(); },
+        out2[1] = rate_of(ctx, [&](int small) { k_fr_mul_peak<Fr><<<blocks, 256, 0, st>>>(sink, 3, small ? small : it2); G16_LAUNCH_CHECK(); },
+                          (double)blocks * 256 * it2 * 4);
+        out2[2] = rate_of(ctx, [&](int small) { k_fr_mul_peak<Fp><<<blocks, 256, 0, st>>>(sink, 3, small ? small : it2); G16_LAUNCH_CHECK(); },
                           (double)blocks * 256 * it2 * 4);
     });
 }

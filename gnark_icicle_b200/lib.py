@@ -298,9 +298,9 @@ class Context:
 
 
 def _pipe_rates(self):
-    out = (ctypes.c_double * 2)()
+    out = (ctypes.c_double * 3)()
     self._check(self._lib.g16_pipe_rates(self._h, out), "g16_pipe_rates")
-    return out[0], out[1]
+    return out[0], out[1], out[2]
 
 
 Context.pipe_rates = _pipe_rates

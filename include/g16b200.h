@@ -26,7 +26,7 @@ extern "C" {
 typedef struct g16_ctx g16_ctx;
 
 #define G16_CURVE_BN254 0
-#define G16_CURVE_BLS12_377 1 /* reserved: not built in this round */
+#define G16_CURVE_BLS12_377 1 /* accepted by g16_bls12_377_ctx_create only (g16b200_bls12_377.h) */
 
 /* index of each MSM result in g16_prove_bn254's output block */
 #define G16_OUT_AR 0      /* sum wA_j * G1.A_j            64 B at offset 0   (icicle.go:312-324 before the epilogue) */
@@ -167,9 +167,10 @@ int g16_g2_scalar_mul(const void* a, const void* k_fr_mont, void* out);
 /* Measured integer-pipe peak on this GPU: independent 32-bit IMAD (mad.lo.u32) and IMAD.WIDE (mad.wide.u32)
  * issue rates in operations per second over all SMs -- the MSM/NTT roofline denominator. */
 int g16_imad_peak(g16_ctx* ctx, double* imad_per_s, double* imad_wide_per_s);
-/* out2[0] = IMAD.WIDE.U32.X (carry-chained, the form the Montgomery multiplier issues) rate per second;
- * out2[1] = in-register Fr Montgomery multiplications per second (the practical field-multiplier peak). */
-int g16_pipe_rates(g16_ctx* ctx, double* out2);
+/* out3[0] = IMAD.WIDE.U32.X (carry-chained, the form the Montgomery multiplier issues) rate per second;
+ * out3[1], out3[2] = in-register Fr / Fp Montgomery multiplications per second (the practical multiplier peaks;
+ * the two differ only for BLS12-377, whose Fp has 12 limbs). */
+int g16_pipe_rates(g16_ctx* ctx, double* out3);
 /* the library's stream, so callers can bracket calls with CUDA events */
 void* g16_ctx_stream(g16_ctx* ctx);
 
