@@ -14,6 +14,7 @@ namespace g16 {
 
 template <class BF>
 struct Curve {
+    typedef BF BaseField;
     typedef typename BF::T E;
     struct Aff { E x, y; };            // (0,0) = point at infinity (gnark layout)
     struct Xyzz { E x, y, zz, zzz; };  // zz == 0 = point at infinity

@@ -22,6 +22,7 @@
 #pragma once
 #include "curve_select.h"
 #include "common.cuh"
+#include <type_traits>
 
 namespace g16 {
 
@@ -245,7 +246,65 @@ __host__ __device__ __forceinline__ uint32_t msm_slice(uint32_t total, uint32_t 
     return s < 4 ? 4 : s;
 }
 
-template <class C, int THREADS, int MINB>
+// The running bucket sum of an accumulate thread, in registers (G1) or word-interleaved in shared memory (G2: the
+// XYZZ accumulator alone is 64 / 96 registers; parking it in shared memory -- word w of component k of thread t at
+// [(k*EW + w) * THREADS + t], conflict-free -- frees enough registers for one more CTA per SM).
+template <class C>
+struct RegAcc {
+    typename C::Xyzz a;
+    __device__ __forceinline__ void reset() { a = C::inf(); }
+    __device__ __forceinline__ void add(const typename C::Aff& p) { C::madd(a, p); }
+    __device__ __forceinline__ void store(typename C::Xyzz* dst) const { store_xyzz<C>(dst, a); }
+};
+template <class C, int THREADS>
+struct SmemAcc {
+    typedef typename C::E E;
+    typedef typename C::BaseField BF;
+    static constexpr int EW = sizeof(E) / 4;
+    static constexpr size_t BYTES = (size_t)4 * EW * THREADS * 4;
+    uint32_t* s;     // shared base + threadIdx.x
+    bool is_inf;
+    __device__ __forceinline__ E ld(int k) const {
+        E r; uint32_t* d = reinterpret_cast<uint32_t*>(&r);
+#pragma unroll
+        for (int w = 0; w < EW; w++) d[w] = s[(k * EW + w) * THREADS];
+        return r;
+    }
+    __device__ __forceinline__ void st(int k, const E& v) {
+        const uint32_t* d = reinterpret_cast<const uint32_t*>(&v);
+#pragma unroll
+        for (int w = 0; w < EW; w++) s[(k * EW + w) * THREADS] = d[w];
+    }
+    __device__ __forceinline__ void reset() { is_inf = true; }
+    // madd-2008-s with every accumulator coordinate loaded right before its use and stored as soon as it is final
+    __device__ __forceinline__ void add(const typename C::Aff& p) {
+        if (C::is_inf(p)) return;
+        if (is_inf) { st(0, p.x); st(1, p.y); st(2, BF::one()); st(3, BF::one()); is_inf = false; return; }
+        E pp = BF::sub(BF::mul(p.x, ld(2)), ld(0));
+        E r = BF::sub(BF::mul(p.y, ld(3)), ld(1));
+        if (BF::is_zero(pp)) {
+            if (BF::is_zero(r)) { typename C::Xyzz d = C::dbl_aff(p); st(0, d.x); st(1, d.y); st(2, d.zz); st(3, d.zzz); }
+            else is_inf = true;
+            return;
+        }
+        E p2 = BF::sqr(pp);
+        E p3 = BF::mul(pp, p2);
+        st(2, BF::mul(ld(2), p2));
+        E q = BF::mul(ld(0), p2);
+        st(3, BF::mul(ld(3), p3));
+        E x3 = BF::sub(BF::sub(BF::sub(BF::sqr(r), p3), q), q);
+        st(0, x3);
+        st(1, BF::sub(BF::mul(r, BF::sub(q, x3)), BF::mul(ld(1), p3)));
+    }
+    __device__ __forceinline__ void store(typename C::Xyzz* dst) const {
+        typename C::Xyzz v;
+        if (is_inf) v = C::inf();
+        else { v.x = ld(0); v.y = ld(1); v.zz = ld(2); v.zzz = ld(3); }
+        store_xyzz<C>(dst, v);
+    }
+};
+
+template <class C, int THREADS, int MINB, bool SMEM_ACC>
 __global__ void __launch_bounds__(THREADS, MINB)
 k_accumulate(const typename C::Aff* __restrict__ bases, const uint32_t* __restrict__ sorted,
              const uint32_t* __restrict__ offsets, uint32_t nb, uint32_t nthreads,
@@ -270,7 +329,10 @@ k_accumulate(const typename C::Aff* __restrict__ bases, const uint32_t* __restri
     uint32_t gb = lo;
     uint32_t b_start = offsets[gb], b_end = offsets[gb + 1];
     uint32_t seg_start = my_start;
-    Xyzz acc = C::inf();
+    extern __shared__ uint32_t acc_smem[];
+    typename std::conditional<SMEM_ACC, SmemAcc<C, THREADS>, RegAcc<C>>::type acc;
+    if constexpr (SMEM_ACC) acc.s = acc_smem + threadIdx.x;
+    acc.reset();
 
     for (uint32_t p = my_start; p < my_end; p += 4) {
         uint4 idx4 = *reinterpret_cast<const uint4*>(sorted + p);   // padded allocation: reading past `total` is safe
@@ -281,9 +343,9 @@ k_accumulate(const typename C::Aff* __restrict__ bases, const uint32_t* __restri
             if (pos >= my_end) break;
             while (pos == b_end) {   // bucket boundary (also steps over empty buckets)
                 if (pos > seg_start) {
-                    if (b_start >= my_start) store_xyzz<C>(buckets + gb, acc);   // bucket lies wholly inside my slice
-                    else store_xyzz<C>(head + t, acc);                           // started in an earlier slice
-                    acc = C::inf();
+                    if (b_start >= my_start) acc.store(buckets + gb);   // bucket lies wholly inside my slice
+                    else acc.store(head + t);                           // started in an earlier slice
+                    acc.reset();
                     seg_start = pos;
                 }
                 gb++;
@@ -292,15 +354,15 @@ k_accumulate(const typename C::Aff* __restrict__ bases, const uint32_t* __restri
             }
             Aff pt = load_aff<C>(bases + (idx[k] & 0x7fffffffu));
             if (idx[k] >> 31) pt = C::neg(pt);
-            C::madd(acc, pt);
+            acc.add(pt);
         }
     }
     // final piece [seg_start, my_end) of bucket gb
     if (my_end > seg_start) {
         bool starts_inside = b_start >= my_start, ends_inside = b_end <= my_end;
-        if (starts_inside && ends_inside) store_xyzz<C>(buckets + gb, acc);
-        else if (seg_start == my_start) store_xyzz<C>(head + t, acc);
-        else store_xyzz<C>(tail + t, acc);
+        if (starts_inside && ends_inside) acc.store(buckets + gb);
+        else if (seg_start == my_start) acc.store(head + t);
+        else acc.store(tail + t);
     }
 }
 
@@ -408,12 +470,12 @@ __global__ void __launch_bounds__(32) k_window_sum(const typename C::Xyzz* __res
 struct MsmStats { int c = 0, W = 0; uint32_t acc_threads = 0; cudaEvent_t acc_begin = nullptr, acc_end = nullptr; };
 
 // Enqueues the whole MSM on `st`; window sums land in ws.host_wsum (pinned) after the stream drains.
-template <class C, int ACC_THREADS, int ACC_MINB>
+template <class C, int ACC_THREADS, int ACC_MINB, bool SMEM_ACC = false>
 void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const typename C::Aff* bases_d,
                  uint64_t n, int force_c, int waves, cudaStream_t st, MsmPlan& plan_out, MsmStats* stats,
                  cudaStream_t tail = nullptr) {
     typedef typename C::Xyzz Xyzz;
-    constexpr bool IS_G2 = sizeof(typename C::Aff) > 64;
+    constexpr bool IS_G2 = sizeof(typename C::E) > sizeof(Fp::T);   // the base field is Fp2
     MsmPlan pl = msm_plan(n, force_c, IS_G2);
     plan_out = pl;
     if (stats) { stats->c = pl.c; stats->W = pl.W; stats->acc_threads = 0; }
@@ -425,7 +487,10 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
     G16_CUDA(cudaGetDevice(&dev));
     G16_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     int occ = 0;
-    G16_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_accumulate<C, ACC_THREADS, ACC_MINB>, ACC_THREADS, 0));
+    auto acc_kernel = k_accumulate<C, ACC_THREADS, ACC_MINB, SMEM_ACC>;
+    const size_t acc_smem = SMEM_ACC ? SmemAcc<C, ACC_THREADS>::BYTES : 0;
+    if (acc_smem > 48 * 1024) G16_CUDA(cudaFuncSetAttribute(acc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)acc_smem));
+    G16_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, acc_kernel, ACC_THREADS, acc_smem));
     if (occ < 1) occ = 1;
     uint32_t nthreads = (uint32_t)sms * occ * ACC_THREADS * (waves > 0 ? waves : 2);
     uint32_t cap = (total_max + 3) / 4;
@@ -478,7 +543,7 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
     G16_LAUNCH_CHECK();
 
     if (stats && stats->acc_begin) G16_CUDA(cudaEventRecord(stats->acc_begin, st));
-    k_accumulate<C, ACC_THREADS, ACC_MINB><<<(nthreads + ACC_THREADS - 1) / ACC_THREADS, ACC_THREADS, 0, st>>>(
+    acc_kernel<<<(nthreads + ACC_THREADS - 1) / ACC_THREADS, ACC_THREADS, acc_smem, st>>>(
         bases_d, sorted, offsets, pl.NB, nthreads, buckets, ws.head.as<Xyzz>(), ws.tail.as<Xyzz>());
     G16_LAUNCH_CHECK();
     if (stats && stats->acc_end) G16_CUDA(cudaEventRecord(stats->acc_end, st));

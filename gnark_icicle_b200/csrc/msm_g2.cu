@@ -8,9 +8,17 @@ namespace g16 {
 void msm_g2_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const G2::Aff* bases_d, uint64_t n,
                     int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail) {
     static const int variant = [] { const char* e = getenv("G16_ACC_VARIANT_G2"); return e ? atoi(e) : 0; }();
-    // 128 x 2 (194 registers): forcing 3 or 4 CTAs/SM spills and is 30-80 % slower (profiles/README.md)
-    (void)variant;
-    msm_enqueue<G2, 128, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail);
+    // 128 x 2.  Measured (profiles/README.md): the G2 kernel is issue-bound -- every integer instruction, IADD3 included,
+    // takes the same two-cycle slot as an IMAD -- so more CTAs/SM do not help (3-4 CTAs/SM: +15..50 %).  Parking the
+    // accumulator in shared memory (SmemAcc) costs 15 % on BN254 (extra LDS/STS issue slots) but removes enough spills
+    // on the 12-limb BLS12-377 field to win 5 % there.
+#if G16_CURVE == 377
+    const bool smem_acc = variant != 1;
+#else
+    const bool smem_acc = variant == 1;
+#endif
+    if (smem_acc) msm_enqueue<G2, 128, 2, true>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail);
+    else msm_enqueue<G2, 128, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail);
 }
 G2::Aff msm_g2_finish(const MsmWorkspace& ws, const MsmPlan& plan) { return msm_finish<G2>(ws, plan); }
 
