@@ -8,7 +8,9 @@ The directory ``gnark-icicle_b200`` at the repo root is a link to this package (
 """
 from . import lib
 from .groth16 import (HasIcicle, Prove, ProvingKey, Proof, R1CSSolution, WithIcicleAcceleration, WithRandomness,
-                      WithDevice, NewProverConfig, prove_msms, assemble, combine_shards)
+                      WithDevice, NewProverConfig, prove_msms, assemble, combine_shards, ConstraintSystem,
+                      prove_msms_wires)
 
 __all__ = ["lib", "HasIcicle", "Prove", "ProvingKey", "Proof", "R1CSSolution", "WithIcicleAcceleration",
-           "WithRandomness", "WithDevice", "NewProverConfig", "prove_msms", "assemble", "combine_shards"]
+           "WithRandomness", "WithDevice", "NewProverConfig", "prove_msms", "assemble", "combine_shards",
+           "ConstraintSystem", "prove_msms_wires"]

@@ -11,6 +11,7 @@
 #include "../../include/g16b200.h"
 #include "msm_api.cuh"
 #include "ntt.cuh"
+#include "r1cs.cuh"
 
 using namespace g16;
 
@@ -45,6 +46,7 @@ struct g16_ctx {
     std::string err;
     std::map<int, NttDomain> domains;
     std::map<uint64_t, PkDev> pks;
+    std::map<uint64_t, R1csDev> r1cs;
     uint64_t next_pk = 1;
     MsmWorkspace ws[5];
     DevBuf stage[4];             // host-pointer variants: staged inputs
@@ -127,6 +129,7 @@ void g16_ctx_destroy(g16_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
     for (auto& kv : ctx->pks) kv.second.release();
+    for (auto& kv : ctx->r1cs) kv.second.release();
     for (auto& kv : ctx->domains) kv.second.release();
     for (auto& w : ctx->ws) w.release();
     for (auto& s : ctx->stage) s.release();
@@ -347,6 +350,97 @@ extern "C" int g16_prove_bn254(g16_ctx* ctx, uint64_t pk_handle, const void* W, 
             G16_CUDA(cudaEventElapsedTime(&stats->ms_h2d, ctx->ev[26], ctx->ev[27]));
             G16_CUDA(cudaEventElapsedTime(&stats->ms_total, ctx->ev[26], ctx->ev[14]));
             stats->h2d_bytes = 3 * cb + (uint64_t)n_wires * 32;
+        }
+    });
+}
+
+// =================================================================== a, b, c on the device
+extern "C" int g16_r1cs_upload(g16_ctx* ctx, const g16_r1cs_desc* d, uint64_t* handle) {
+    return guarded(ctx, [&] {
+        if (!d || !handle) throw std::runtime_error("null argument");
+        if (d->n_constraints >= 0xffffffffull || d->n_wires >= 0xffffffffull) throw std::runtime_error("constraint system too large for 32-bit indices");
+        if (d->n_coeffs && !d->coeffs) throw std::runtime_error("null coefficient table");
+        R1csDev r;
+        r.n_constraints = d->n_constraints; r.n_wires = d->n_wires; r.n_coeffs = d->n_coeffs;
+        cudaStream_t st = ctx->stream;
+        try {
+            upload(r.coeffs, d->coeffs, (size_t)d->n_coeffs * 32, st);
+            for (int m = 0; m < 3; m++) {
+                const uint32_t* rp = d->row_ptr[m];
+                if (!rp) throw std::runtime_error("null row_ptr");
+                const uint64_t nnz = rp[d->n_constraints];
+                if (rp[0] != 0) throw std::runtime_error("row_ptr must start at 0");
+                for (uint64_t i = 0; i < d->n_constraints; i++)
+                    if (rp[i] > rp[i + 1]) throw std::runtime_error("row_ptr is not monotone");
+                if (nnz && (!d->wire[m] || !d->coeff_id[m])) throw std::runtime_error("null term arrays");
+                for (uint64_t t = 0; t < nnz; t++) {
+                    if (d->wire[m][t] >= d->n_wires) throw std::runtime_error("term wire id out of range");
+                    if (d->coeff_id[m][t] >= d->n_coeffs) throw std::runtime_error("term coefficient id out of range");
+                }
+                upload(r.row_ptr[m], rp, (size_t)(d->n_constraints + 1) * 4, st);
+                upload(r.wire[m], d->wire[m], (size_t)nnz * 4, st);
+                upload(r.cid[m], d->coeff_id[m], (size_t)nnz * 4, st);
+            }
+            G16_CUDA(cudaStreamSynchronize(st));
+        } catch (...) {
+            r.release();
+            throw;
+        }
+        uint64_t h = ctx->next_pk++;
+        ctx->r1cs[h] = r;
+        *handle = h;
+    });
+}
+
+extern "C" int g16_r1cs_free(g16_ctx* ctx, uint64_t handle) {
+    return guarded(ctx, [&] {
+        auto it = ctx->r1cs.find(handle);
+        if (it == ctx->r1cs.end()) throw std::runtime_error("unknown R1CS handle");
+        it->second.release();
+        ctx->r1cs.erase(it);
+    });
+}
+
+extern "C" int g16_r1cs_eval_dev(g16_ctx* ctx, uint64_t handle, const void* W_d, void* a_d, void* b_d, void* c_d, uint64_t domain_n) {
+    return guarded(ctx, [&] {
+        auto it = ctx->r1cs.find(handle);
+        if (it == ctx->r1cs.end()) throw std::runtime_error("unknown R1CS handle");
+        if (!W_d || !a_d || !b_d || !c_d) throw std::runtime_error("null argument");
+        if (domain_n < it->second.n_constraints) throw std::runtime_error("domain smaller than the constraint count");
+        r1cs_eval(it->second, (const Fr::T*)W_d, (Fr::T*)a_d, (Fr::T*)b_d, (Fr::T*)c_d, domain_n, ctx->stream);
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+
+extern "C" int g16_prove_bn254_wires(g16_ctx* ctx, uint64_t pk_handle, uint64_t r1cs_handle, const void* W, uint64_t n_wires,
+                                     void* out_points, g16_stats* stats) {
+    return guarded(ctx, [&] {
+        auto it = ctx->pks.find(pk_handle);
+        if (it == ctx->pks.end()) throw std::runtime_error("unknown proving-key handle");
+        auto ir = ctx->r1cs.find(r1cs_handle);
+        if (ir == ctx->r1cs.end()) throw std::runtime_error("unknown R1CS handle");
+        PkDev& pk = it->second;
+        const R1csDev& r = ir->second;
+        if (!W || !out_points) throw std::runtime_error("null argument");
+        if (n_wires != pk.n_wires || n_wires != r.n_wires) throw std::runtime_error("witness length does not match the key / constraint system");
+        if (r.n_constraints > pk.domain_n) throw std::runtime_error("more constraints than the domain holds");
+        uint64_t l0 = launch_counter().load();
+        if (stats) memset(stats, 0, sizeof(*stats));
+        cudaStream_t st = ctx->stream;
+        const size_t nb = (size_t)pk.domain_n * 32;
+        G16_CUDA(cudaEventRecord(ctx->ev[26], st));
+        ctx->stage[3].reserve((size_t)n_wires * 32);
+        G16_CUDA(cudaMemcpyAsync(ctx->stage[3].p, W, (size_t)n_wires * 32, cudaMemcpyHostToDevice, st));
+        G16_CUDA(cudaEventRecord(ctx->ev[15], st));
+        G16_CUDA(cudaEventRecord(ctx->ev[27], st));
+        for (int i = 0; i < 3; i++) ctx->stage[i].reserve(nb);
+        r1cs_eval(r, ctx->stage[3].as<Fr::T>(), ctx->stage[0].as<Fr::T>(), ctx->stage[1].as<Fr::T>(), ctx->stage[2].as<Fr::T>(), pk.domain_n, st);
+        prove_device(ctx, pk, ctx->stage[3].as<Fr::T>(), ctx->stage[0].as<Fr::T>(), ctx->stage[1].as<Fr::T>(),
+                     ctx->stage[2].as<Fr::T>(), out_points, stats, l0, ctx->ev[15]);
+        if (stats) {
+            G16_CUDA(cudaEventElapsedTime(&stats->ms_h2d, ctx->ev[26], ctx->ev[27]));
+            G16_CUDA(cudaEventElapsedTime(&stats->ms_total, ctx->ev[26], ctx->ev[14]));
+            stats->h2d_bytes = (uint64_t)n_wires * 32;
         }
     });
 }

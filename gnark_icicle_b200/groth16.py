@@ -74,6 +74,35 @@ class R1CSSolution:
 
 
 @dataclass
+class ConstraintSystem:
+    """The part of cs.R1CS (constraint/bn254/system.go, constraint/r1cs.go) the device needs to produce a = L.w,
+    b = R.w, c = O.w itself: the coefficient table and the three matrices in CSR form over the
+    constraints, a term being (coefficient id, wire id) like constraint.Term{CID, VID}.  Uploaded once, lazily,
+    next to the proving key; a Prove call then only ships the wire vector."""
+    nb_constraints: int
+    nb_wires: int
+    coefficients: np.ndarray          # (k, 4) Fr, Montgomery
+    L: tuple                          # (row_ptr, wire, coeff_id) uint32 arrays
+    R: tuple
+    O: tuple
+    device: object = None             # (Context, handle)
+
+    def setup_device(self, ctx):
+        if self.device is not None and self.device[0] is ctx:
+            return self.device[1]
+        self.free_device()
+        h = ctx.r1cs_upload(self.nb_constraints, self.nb_wires, self.coefficients, (self.L, self.R, self.O))
+        self.device = (ctx, h)
+        return h
+
+    def free_device(self):
+        if self.device is not None:
+            ctx, h = self.device
+            ctx.r1cs_free(h)
+            self.device = None
+
+
+@dataclass
 class Proof:
     """prove.go:44-49 (no commitments): raw gnark memory images."""
     Ar: np.ndarray    # (8,)  G1Affine   ((12,) for BLS12-377)
@@ -141,11 +170,19 @@ def prove_msms(pk, sol, cfg=None):
     return ctx.prove(handle, sol.W, sol.A, sol.B, sol.C)
 
 
+def prove_msms_wires(pk, cs, W, cfg=None):
+    """prove_msms with a, b, c evaluated on the device from the resident constraint matrices."""
+    pk.setup_device_pointers(cfg)
+    ctx, handle = pk.device
+    return ctx.prove_wires(handle, cs.setup_device(ctx), W)
+
+
 def Prove(r1cs, pk, full_witness, *opts):
     """icicle_bn254.Prove (icicle.go:133-422).
 
     ``r1cs`` must offer ``solve(full_witness) -> R1CSSolution`` (constraint/bn254/system.go:65; the solver
-    is host code outside the accelerated path) -- or pass ``r1cs=None`` and an R1CSSolution as the witness.
+    is host code outside the accelerated path) -- or pass ``r1cs=None`` and an R1CSSolution as the witness, or a
+    ``ConstraintSystem`` and the solved wire vector (a, b, c are then computed on the device).
     Without WithIcicleAcceleration() the reference falls back to the CPU prover (icicle.go:141-143); this
     package has no CPU prover, so that is an error here.
     """
@@ -155,8 +192,12 @@ def Prove(r1cs, pk, full_witness, *opts):
                             "(the CPU prover lives in gnark, not in this package)")
     if pk.commitment_keys:
         raise NotImplementedError("BSB22 commitments are outside this round's scope (SURVEY.md 8(f) N3)")
-    sol = full_witness if r1cs is None else r1cs.solve(full_witness)
-    points, stats = prove_msms(pk, sol, cfg)
+    if isinstance(r1cs, ConstraintSystem):
+        # the wire vector is the whole witness-side input: the device evaluates the constraint matrices
+        points, stats = prove_msms_wires(pk, r1cs, full_witness, cfg)
+    else:
+        sol = full_witness if r1cs is None else r1cs.solve(full_witness)
+        points, stats = prove_msms(pk, sol, cfg)
     r = cfg.r if cfg.r is not None else _random_fr(pk.curve)
     s = cfg.s if cfg.s is not None else _random_fr(pk.curve)
     proof = assemble(pk, points, r, s)

@@ -60,10 +60,19 @@ class PkDesc(ctypes.Structure):
     ]
 
 
+class R1csDesc(ctypes.Structure):
+    _fields_ = [
+        ("n_constraints", ctypes.c_uint64), ("n_wires", ctypes.c_uint64),
+        ("coeffs", ctypes.c_void_p), ("n_coeffs", ctypes.c_uint64),
+        ("row_ptr", ctypes.c_void_p * 3), ("wire", ctypes.c_void_p * 3), ("coeff_id", ctypes.c_void_p * 3),
+    ]
+
+
 # every symbol include/g16b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "g16_ctx_create", "g16_ctx_destroy", "g16_last_error", "g16_ctx_set", "g16_kernel_launch_count",
     "g16_pk_upload", "g16_pk_free", "g16_prove_bn254", "g16_prove_bn254_dev", "g16_assemble_proof_bn254",
+    "g16_r1cs_upload", "g16_r1cs_free", "g16_r1cs_eval_dev", "g16_prove_bn254_wires",
     "g16_msm_g1", "g16_msm_g1_dev", "g16_msm_g2", "g16_msm_g2_dev", "g16_ntt", "g16_ntt_dev",
     "g16_compute_h", "g16_compute_h_dev", "g16_fr_mul_vec",
     "g16_dist_ntt_stages_dev", "g16_dist_permute_dev", "g16_dist_pointwise_h_dev", "g16_prove_msms_dev",
@@ -270,6 +279,38 @@ class Context:
         st = Stats()
         self._check(self._lib.g16_prove_bn254_dev(self._h, u64(pk_handle), _ptr(W_ptr), _ptr(a_ptr), _ptr(b_ptr), _ptr(c_ptr),
                                                   _ptr(out), ctypes.byref(st)), "g16_prove_bn254_dev")
+        return out, st.as_dict()
+
+    # ---- constraint matrices on the device
+    def r1cs_upload(self, n_constraints, n_wires, coeffs, matrices):
+        """matrices: three (row_ptr, wire, coeff_id) uint32 triples for L, R, O (CSR over the constraints)."""
+        coeffs = _arr(coeffs, 4) if len(coeffs) else np.zeros((0, 4), dtype=np.uint64)
+        keep = []
+        d = R1csDesc()
+        d.n_constraints, d.n_wires, d.coeffs, d.n_coeffs = n_constraints, n_wires, coeffs.ctypes.data, len(coeffs)
+        for m, (rp, wi, ci) in enumerate(matrices):
+            rp, wi, ci = (np.ascontiguousarray(x, dtype=np.uint32) for x in (rp, wi, ci))
+            assert len(rp) == n_constraints + 1 and len(wi) == len(ci) == int(rp[-1]), (len(rp), len(wi), len(ci))
+            keep += [rp, wi, ci]
+            d.row_ptr[m], d.wire[m], d.coeff_id[m] = rp.ctypes.data, wi.ctypes.data, ci.ctypes.data
+        h = u64(0)
+        self._check(self._lib.g16_r1cs_upload(self._h, ctypes.byref(d), ctypes.byref(h)), "g16_r1cs_upload")
+        return h.value
+
+    def r1cs_free(self, handle):
+        self._check(self._lib.g16_r1cs_free(self._h, u64(handle)), "g16_r1cs_free")
+
+    def r1cs_eval_dev(self, handle, W_ptr, a_ptr, b_ptr, c_ptr, domain_n):
+        self._check(self._lib.g16_r1cs_eval_dev(self._h, u64(handle), _ptr(W_ptr), _ptr(a_ptr), _ptr(b_ptr), _ptr(c_ptr),
+                                                u64(domain_n)), "g16_r1cs_eval_dev")
+
+    def prove_wires(self, pk_handle, r1cs_handle, W):
+        """only the wire vector crosses the boundary: a, b, c are evaluated on the device from the resident matrices."""
+        W = _arr(W, 4)
+        out = np.zeros(self.prove_out_words, dtype=np.uint64)
+        st = Stats()
+        self._check(self._lib.g16_prove_bn254_wires(self._h, u64(pk_handle), u64(r1cs_handle), _ptr(W), u64(len(W)), _ptr(out),
+                                                    ctypes.byref(st)), "g16_prove_bn254_wires")
         return out, st.as_dict()
 
     # ---- distributed computeH building blocks

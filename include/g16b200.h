@@ -100,6 +100,28 @@ int g16_prove_bn254(g16_ctx* ctx, uint64_t pk_handle, const void* W, uint64_t n_
 int g16_prove_bn254_dev(g16_ctx* ctx, uint64_t pk_handle, const void* W_d, void* a_d, void* b_d, void* c_d,
                         void* out_points, g16_stats* stats);
 
+/* ---- a, b, c on the device ---------------------------------------------------------- */
+/* The reference's solver produces a = L.w, b = R.w, c = O.w on the CPU (constraint/bn254/solver.go:540-628) and the
+ * prover uploads all three (icicle.go:219,478-480: 3 x n x 32 B per proof).  With the constraint matrices resident
+ * (uploaded once, like the key) only the wire vector crosses PCIe.  Matrices are CSR over the constraints; every
+ * term is (coefficient id, wire id) exactly like gnark's constraint.Term{CID, VID} with the table cs.Coefficients. */
+typedef struct {
+    uint64_t n_constraints;
+    uint64_t n_wires;
+    const void* coeffs; uint64_t n_coeffs;     /* cs.Coefficients: Fr, Montgomery */
+    const uint32_t* row_ptr[3];                /* L, R, O: n_constraints + 1 offsets into wire / coeff_id */
+    const uint32_t* wire[3];                   /* Term.VID */
+    const uint32_t* coeff_id[3];               /* Term.CID */
+} g16_r1cs_desc;
+int g16_r1cs_upload(g16_ctx* ctx, const g16_r1cs_desc* desc, uint64_t* r1cs_handle);
+int g16_r1cs_free(g16_ctx* ctx, uint64_t r1cs_handle);
+/* a_d, b_d, c_d: domain_n Fr each; rows >= n_constraints are zeroed (the padding of icicle.go:463-467) */
+int g16_r1cs_eval_dev(g16_ctx* ctx, uint64_t r1cs_handle, const void* W_d, void* a_d, void* b_d, void* c_d,
+                      uint64_t domain_n);
+/* g16_prove_bn254 without a, b, c: uploads W (host, n_wires Fr), evaluates the matrices, proves */
+int g16_prove_bn254_wires(g16_ctx* ctx, uint64_t pk_handle, uint64_t r1cs_handle, const void* W, uint64_t n_wires,
+                          void* out_points, g16_stats* stats);
+
 /* Host epilogue of prove.go:180-195,209-224,251-279,297-302 with injected randomness r, s (Fr, Montgomery):
  * pk_points = G1.Alpha || G1.Beta || G1.Delta (3 x 64 B) || G2.Beta || G2.Delta (2 x 128 B);
  * proof_out = Ar (64) || Bs (128) || Krs (64). */

@@ -388,6 +388,11 @@ typedef struct { uint64_t nc, rounds; xo_t g; uint64_t j, xw, next; } chain_it;
 static void chain_begin(chain_it *it, uint64_t nc, uint64_t seed) {
     it->nc = nc; it->rounds = (nc - 1) / 3; xo_seed(&it->g, seed); it->j = 0; it->xw = 2; it->next = 4;
 }
+/* the (nc-1)/3 round constants of the chain, Montgomery (tests build the constraint matrices from them) */
+void orc_mimc_chain_constants(uint64_t nc, uint64_t seed, fe *out) {
+    chain_it it; chain_begin(&it, nc, seed);
+    for (uint64_t r = 0; r < it.rounds; r++) xo_field(&it.g, &FR, &out[r]);
+}
 /* W (nc+3), a,b,c (nc): solved witness and per-constraint L.w, R.w, O.w; all Montgomery */
 void orc_mimc_chain_witness(uint64_t nc, uint64_t seed, const fe *x0, const fe *k, fe *W, fe *a, fe *b, fe *c) {
     chain_it it; chain_begin(&it, nc, seed);

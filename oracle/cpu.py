@@ -151,6 +151,12 @@ def mimc_chain_witness(nc, seed, x0, k):
     return W, a, b, c
 
 
+def mimc_chain_constants(nc, seed):
+    out = np.empty(((nc - 1) // 3, 4), dtype=np.uint64)
+    lib().orc_mimc_chain_constants(u64(nc), u64(seed), _p(out))
+    return out
+
+
 def mimc_chain_setup_scalars(nc, n, seed, tw):
     """tw: (5,4) Montgomery {t, alpha, beta, gamma, delta}. Returns A,B,K (nc+3), Z (n, natural order)."""
     tw = _c(tw)

@@ -123,3 +123,65 @@ class ChainCase:
         return np.concatenate([
             trapdoor_g1(wa, self.sA), trapdoor_g1(wb, self.sB), trapdoor_g1(wk, self.sK),
             trapdoor_g1(h[: self.n - 1], self.sZ), trapdoor_g2(wb, self.sB)])
+
+
+# ---------------------------------------------------------------- constraint matrices for the device (8(f) N1)
+def csr_from_oracle(cs, fr_arr):
+    """oracle.r1cs.R1CS -> gnark_icicle_b200.ConstraintSystem (coefficient table de-duplicated like cs.Coefficients)."""
+    from gnark_icicle_b200 import ConstraintSystem
+    table, ids = [], {}
+    mats = []
+    for m in range(3):
+        rp, wi, ci = [0], [], []
+        for row in cs.constraints:
+            for cf, w in row[m]:
+                cf %= R
+                if cf not in ids:
+                    ids[cf] = len(table)
+                    table.append(cf)
+                wi.append(w)
+                ci.append(ids[cf])
+            rp.append(len(wi))
+        mats.append(tuple(np.array(x, dtype=np.uint32) for x in (rp, wi, ci)))
+    return ConstraintSystem(nb_constraints=cs.nb_constraints, nb_wires=cs.nb_wires, coefficients=fr_arr(table),
+                            L=mats[0], R=mats[1], O=mats[2])
+
+
+def chain_csr(nc, cseed):
+    """the constraint matrices of ChainCase's MiMC-shaped chain (oracle/c orc_mimc_chain_*), built with numpy."""
+    from gnark_icicle_b200 import ConstraintSystem
+    consts = ocpu.mimc_chain_constants(nc, cseed)
+    rounds = len(consts)
+    one = ocpu.fr_arr([1])
+    coeffs = np.concatenate([one, consts]) if rounds else one
+    r = np.arange(rounds, dtype=np.int64)
+    xw = np.where(r == 0, 2, 3 * r + 3)            # state wire entering round r (wires: 0 ONE, 1 OUT, 2 X0, 3 K)
+    u, v, nx = 3 * r + 4, 3 * r + 5, 3 * r + 6
+    nfill = nc - 1 - 3 * rounds
+    f = np.arange(nfill, dtype=np.int64)
+    last_state = int(nx[-1]) if rounds else 2
+    fx_in = np.where(f == 0, last_state, 3 * rounds + 3 + f)
+    fx_out = 3 * rounds + 4 + f
+    final_state = int(fx_out[-1]) if nfill else last_state
+    t_w = np.stack([xw, np.full(rounds, 3), np.zeros(rounds, dtype=np.int64)], axis=1)        # t = x + k + c_i * ONE
+    t_c = np.stack([np.zeros(rounds, dtype=np.int64), np.zeros(rounds, dtype=np.int64), 1 + r], axis=1)
+
+    z1 = np.zeros((rounds, 1), dtype=np.int64)
+    col = lambda a: a.reshape(-1, 1)
+
+    def matrix(per_round, fill_w, last_w):
+        """per_round: the three rows of a round as (wires, coeff ids) pairs of (rounds, k) arrays"""
+        lens = [p[0].shape[1] for p in per_round]
+        w = np.concatenate([p[0] for p in per_round], axis=1).reshape(-1)
+        c = np.concatenate([p[1] for p in per_round], axis=1).reshape(-1)
+        row_len = np.concatenate([np.tile(lens, rounds), np.ones(nfill, dtype=np.int64), [len(last_w)]])
+        rp = np.zeros(nc + 1, dtype=np.uint32)
+        rp[1:] = np.cumsum(row_len)
+        w = np.concatenate([w, fill_w, last_w])
+        c = np.concatenate([c, np.zeros(nfill + len(last_w), dtype=np.int64)])
+        return rp, w.astype(np.uint32), c.astype(np.uint32)
+
+    L = matrix([(t_w, t_c), (col(u), z1), (col(v), z1)], fx_in, [final_state, 3])
+    Rm = matrix([(t_w, t_c), (col(u), z1), (t_w, t_c)], fx_in, [0])
+    O = matrix([(col(u), z1), (col(v), z1), (col(nx), z1)], fx_out, [1])
+    return ConstraintSystem(nb_constraints=nc, nb_wires=nc + 3, coefficients=coeffs, L=L, R=Rm, O=O)
