@@ -27,6 +27,7 @@ struct PkDev {
     DevBuf g1_a, g1_b, g1_k, g1_z, g2_b;
     DevBuf map_a, map_b, map_k;   // u32 wire index per base
     uint64_t n_a = 0, n_b = 0, n_k = 0, n_z = 0, n_b2 = 0;
+    int pre_c[5] = {0, 0, 0, 0, 0}; // window bits of the precomputed-multiples table per MSM (G16_OUT_* order); 0 = none
     uint64_t z_off = 0;           // first h index of this shard's Z slice
     void release() {
         g1_a.release(); g1_b.release(); g1_k.release(); g1_z.release(); g2_b.release();
@@ -52,6 +53,7 @@ struct g16_ctx {
     DevBuf stage[4];             // host-pointer variants: staged inputs
     DevBuf fb_table_g1, fb_table_g2;
     int msm_c = 0, msm_waves = 4;
+    int msm_precompute = 1;      // keep 2^(c j) multiples of every key base resident (one shared bucket set, larger windows)
 
     NttDomain& domain(int logn) {
         auto it = domains.find(logn);
@@ -89,6 +91,30 @@ void slice(uint64_t len, uint32_t idx, uint32_t cnt, uint64_t& lo, uint64_t& hi)
 void upload(DevBuf& dst, const void* src, size_t bytes, cudaStream_t st) {
     dst.reserve(bytes ? bytes : 16);
     if (bytes) G16_CUDA(cudaMemcpyAsync(dst.p, src, bytes, cudaMemcpyHostToDevice, st));
+}
+
+// Key bases: row 0 of a table that, when it fits comfortably (less than half of the free HBM) and the array is
+// large enough to pay for it, also holds the 2^(c j) multiples used by the shared-bucket MSM (msm.cuh, precomputed
+// mode).  pre_c = window bits of the table, 0 = bases only.
+constexpr uint64_t PRECOMPUTE_MIN_POINTS = 1 << 14;
+template <class C>
+void upload_bases(g16_ctx* ctx, DevBuf& dst, const void* src, uint64_t n, int& pre_c, cudaStream_t st) {
+    constexpr bool IS_G2 = sizeof(typename C::E) > sizeof(Fp::T);
+    const size_t row = (size_t)n * sizeof(typename C::Aff);
+    pre_c = 0;
+    if (ctx->msm_precompute && n >= PRECOMPUTE_MIN_POINTS) {
+        const int c = msm_pre_choose_c(n, IS_G2);
+        const size_t total = row * (size_t)(255 / c + 1);
+        size_t free_b = 0, total_b = 0;
+        G16_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        if (total <= free_b / 2) pre_c = c;
+    }
+    dst.reserve(pre_c ? row * (size_t)(255 / pre_c + 1) : (row ? row : 16));
+    if (row) G16_CUDA(cudaMemcpyAsync(dst.p, src, row, cudaMemcpyHostToDevice, st));
+    if (pre_c) {
+        if constexpr (IS_G2) msm_g2_precompute(dst.as<G2::Aff>(), n, pre_c, st);
+        else msm_g1_precompute(dst.as<G1::Aff>(), n, pre_c, st);
+    }
 }
 
 }  // namespace
@@ -149,6 +175,7 @@ int g16_ctx_set(g16_ctx* ctx, const char* key, int64_t value) {
     if (k == "msm_c") ctx->msm_c = (int)value;
     else if (k == "msm_waves") ctx->msm_waves = (int)value;
     else if (k == "streams") ctx->streams = (int)value;
+    else if (k == "msm_precompute") ctx->msm_precompute = (int)value;
     else { ctx->err = "unknown tunable " + k; return 1; }
     return 0;
 }
@@ -192,16 +219,16 @@ extern "C" int g16_pk_upload(g16_ctx* ctx, const g16_pk_desc* d, uint64_t* pk_ha
         uint64_t lo, hi;
         slice(d->n_a, si, sc, lo, hi);
         pk.n_a = hi - lo;
-        upload(pk.g1_a, (const char*)d->g1_a + lo * G1SZ, pk.n_a * G1SZ, st);
+        upload_bases<G1>(ctx, pk.g1_a, (const char*)d->g1_a + lo * G1SZ, pk.n_a, pk.pre_c[G16_OUT_AR], st);
         upload(pk.map_a, ma.data() + lo, pk.n_a * 4, st);
         slice(d->n_b, si, sc, lo, hi);
         pk.n_b = pk.n_b2 = hi - lo;
-        upload(pk.g1_b, (const char*)d->g1_b + lo * G1SZ, pk.n_b * G1SZ, st);
-        upload(pk.g2_b, (const char*)d->g2_b + lo * G2SZ, pk.n_b * G2SZ, st);
+        upload_bases<G1>(ctx, pk.g1_b, (const char*)d->g1_b + lo * G1SZ, pk.n_b, pk.pre_c[G16_OUT_BS1], st);
+        upload_bases<G2>(ctx, pk.g2_b, (const char*)d->g2_b + lo * G2SZ, pk.n_b, pk.pre_c[G16_OUT_BS2], st);
         upload(pk.map_b, mb.data() + lo, pk.n_b * 4, st);
         slice(d->n_k, si, sc, lo, hi);
         pk.n_k = hi - lo;
-        upload(pk.g1_k, (const char*)d->g1_k + lo * G1SZ, pk.n_k * G1SZ, st);
+        upload_bases<G1>(ctx, pk.g1_k, (const char*)d->g1_k + lo * G1SZ, pk.n_k, pk.pre_c[G16_OUT_KRS_K], st);
         upload(pk.map_k, mk.data() + lo, pk.n_k * 4, st);
         uint64_t nz = d->n_z < d->domain_n ? d->n_z : d->domain_n - 1;   // h[:n-1] (prove.go:235-237)
         // Z follows the block distribution of h over the domain (so a distributed computeH leaves each rank's
@@ -211,7 +238,7 @@ extern "C" int g16_pk_upload(g16_ctx* ctx, const g16_pk_desc* d, uint64_t* pk_ha
         if (hi > nz) hi = nz;
         pk.n_z = hi - lo;
         pk.z_off = lo;
-        upload(pk.g1_z, (const char*)d->g1_z + lo * G1SZ, pk.n_z * G1SZ, st);
+        upload_bases<G1>(ctx, pk.g1_z, (const char*)d->g1_z + lo * G1SZ, pk.n_z, pk.pre_c[G16_OUT_KRS_HZ], st);
 
         // twiddles of the domain (replaces icicle.go:44-75)
         NttDomain& dom = ctx->domain(pk.logn);
@@ -253,6 +280,8 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
     // (the reference serialises everything, icicle.go:396-410); the sort/reduce tails of one MSM then hide
     // under the accumulation of another.  Order of issue: G2 first (longest).
     const bool overlap = ctx->streams > 1;
+    // precomputed tables are used unless the caller forces a window size ("msm_c") or switched them off after upload
+    auto pre = [&](int i) { return (ctx->msm_c == 0 && ctx->msm_precompute) ? pk.pre_c[i] : 0; };
     cudaStream_t sA = overlap ? ctx->aux[0] : st, sB = overlap ? ctx->aux[1] : st, sK = overlap ? ctx->aux[2] : st,
                  s2 = overlap ? ctx->aux[3] : st;
     G16_CUDA(cudaEventRecord(ev[0], st));
@@ -266,18 +295,19 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
         G16_CUDA(cudaEventRecord(ev[6 + idx], s));
     };
     run(G16_OUT_BS2, s2, [&](cudaStream_t s) {
-        msm_g2_enqueue(ctx->ws[G16_OUT_BS2], W_d, pk.map_b.as<uint32_t>(), pk.g2_b.as<G2::Aff>(), pk.n_b2, ctx->msm_c, ctx->msm_waves, s, plan[4], &ms[4], overlap ? ctx->tails[4] : nullptr); });
+        msm_g2_enqueue(ctx->ws[G16_OUT_BS2], W_d, pk.map_b.as<uint32_t>(), pk.g2_b.as<G2::Aff>(), pk.n_b2, ctx->msm_c, ctx->msm_waves, s, plan[4], &ms[4], overlap ? ctx->tails[4] : nullptr, pre(G16_OUT_BS2)); });
     G16_CUDA(cudaEventRecord(ev[12], st));
     if (!h_given) compute_h_device(dom, a_d, b_d, c_d, st);   // h (bit-reversed) in a_d; h_given: a_d is this shard's block of h
     G16_CUDA(cudaEventRecord(ev[13], st));
     run(G16_OUT_AR, sA, [&](cudaStream_t s) {
-        msm_g1_enqueue(ctx->ws[G16_OUT_AR], W_d, pk.map_a.as<uint32_t>(), pk.g1_a.as<G1::Aff>(), pk.n_a, ctx->msm_c, ctx->msm_waves, s, plan[0], &ms[0], overlap ? ctx->tails[0] : nullptr); });
+        msm_g1_enqueue(ctx->ws[G16_OUT_AR], W_d, pk.map_a.as<uint32_t>(), pk.g1_a.as<G1::Aff>(), pk.n_a, ctx->msm_c, ctx->msm_waves, s, plan[0], &ms[0], overlap ? ctx->tails[0] : nullptr, pre(G16_OUT_AR)); });
     run(G16_OUT_KRS_HZ, st, [&](cudaStream_t s) {
-        msm_g1_enqueue(ctx->ws[G16_OUT_KRS_HZ], a_d + (h_given ? 0 : pk.z_off), nullptr, pk.g1_z.as<G1::Aff>(), pk.n_z, ctx->msm_c, ctx->msm_waves, s, plan[3], &ms[3], overlap ? ctx->tails[3] : nullptr); });
+        msm_g1_enqueue(ctx->ws[G16_OUT_KRS_HZ], a_d + (h_given ? 0 : pk.z_off), nullptr, pk.g1_z.as<G1::Aff>(), pk.n_z, ctx->msm_c, ctx->msm_waves, s, plan[3], &ms[3], overlap ? ctx->tails[3] : nullptr, pre(G16_OUT_KRS_HZ)); });
     run(G16_OUT_BS1, sB, [&](cudaStream_t s) {
-        msm_g1_enqueue(ctx->ws[G16_OUT_BS1], W_d, pk.map_b.as<uint32_t>(), pk.g1_b.as<G1::Aff>(), pk.n_b, ctx->msm_c, ctx->msm_waves, s, plan[1], &ms[1], overlap ? ctx->tails[1] : nullptr); });
+        msm_g1_enqueue(ctx->ws[G16_OUT_BS1], W_d, pk.map_b.as<uint32_t>(), pk.g1_b.as<G1::Aff>(), pk.n_b, ctx->msm_c, ctx->msm_waves, s, plan[1], &ms[1], overlap ? ctx->tails[1] : nullptr, pre(G16_OUT_BS1),
+                       pk.n_b == pk.n_b2 ? &ctx->ws[G16_OUT_BS2] : nullptr); });   // same scalars, same map: reuse the G2 MSM's sort
     run(G16_OUT_KRS_K, sK, [&](cudaStream_t s) {
-        msm_g1_enqueue(ctx->ws[G16_OUT_KRS_K], W_d, pk.map_k.as<uint32_t>(), pk.g1_k.as<G1::Aff>(), pk.n_k, ctx->msm_c, ctx->msm_waves, s, plan[2], &ms[2], overlap ? ctx->tails[2] : nullptr); });
+        msm_g1_enqueue(ctx->ws[G16_OUT_KRS_K], W_d, pk.map_k.as<uint32_t>(), pk.g1_k.as<G1::Aff>(), pk.n_k, ctx->msm_c, ctx->msm_waves, s, plan[2], &ms[2], overlap ? ctx->tails[2] : nullptr, pre(G16_OUT_KRS_K)); });
     if (overlap) {
         const int aux_of[4] = {G16_OUT_AR, G16_OUT_BS1, G16_OUT_KRS_K, G16_OUT_BS2};
         for (int i = 0; i < 4; i++) G16_CUDA(cudaStreamWaitEvent(st, ev[6 + aux_of[i]], 0));
@@ -294,7 +324,7 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
         G16_CUDA(cudaEventElapsedTime(&stats->ms_compute_h, ev[12], ev[13]));
         for (int i = 0; i < 5; i++) {
             G16_CUDA(cudaEventElapsedTime(&stats->ms_msm[i], ev[1 + i], ev[6 + i]));
-            stats->msm_c[i] = plan[i].c; stats->msm_windows[i] = plan[i].W; stats->msm_n[i] = ns[i];
+            stats->msm_c[i] = plan[i].c; stats->msm_windows[i] = plan[i].Wd; stats->msm_n[i] = ns[i];
             if (ns[i]) G16_CUDA(cudaEventElapsedTime(&stats->ms_accumulate[i], ev[16 + 2 * i], ev[17 + 2 * i]));
         }
         G16_CUDA(cudaEventElapsedTime(&stats->ms_total, ev[0], ev[14]));

@@ -27,23 +27,27 @@
 namespace g16 {
 
 struct MsmWorkspace {
-    DevBuf digits, sorted, counts, offsets, cursor, buckets, head, tail, partial, wsum, scan_tmp, heavy;
+    DevBuf digits, sorted, counts, offsets, cursor, buckets, head, tail, partial, wsum, scan_tmp, heavy, pairs, level1;
     PinnedBuf host_wsum;
-    cudaEvent_t acc_done = nullptr, tail_done = nullptr;
+    cudaEvent_t acc_done = nullptr, tail_done = nullptr, sort_done = nullptr;
+    uint64_t sort_n = 0; int sort_c = 0; bool sort_pre = false;   // what `sorted` / `offsets` currently describe
     void release() {
         if (acc_done) cudaEventDestroy(acc_done);
         if (tail_done) cudaEventDestroy(tail_done);
-        acc_done = tail_done = nullptr;
+        if (sort_done) cudaEventDestroy(sort_done);
+        acc_done = tail_done = sort_done = nullptr;
         digits.release(); sorted.release(); counts.release(); offsets.release(); cursor.release();
-        buckets.release(); head.release(); tail.release(); partial.release(); wsum.release(); host_wsum.release(); scan_tmp.release(); heavy.release();
+        buckets.release(); head.release(); tail.release(); partial.release(); wsum.release(); host_wsum.release(); scan_tmp.release(); heavy.release(); pairs.release(); level1.release();
     }
 };
 
 struct MsmPlan {
-    int c, W;
-    uint32_t B;        // buckets per window = 2^(c-1)
+    int c, W;          // window bits; number of bucket SETS (= windows; 1 with precomputed multiples)
+    uint32_t B;        // buckets per set = 2^(c-1)
     uint32_t NB;       // W * B
-    int red_m, red_rb; // bucket-reduce: buckets per thread, CTAs per window
+    int red_m, red_rb; // bucket-reduce: buckets per thread, CTAs per set
+    int Wd;            // digits (bucket entries) per scalar: = W, or the window count when W == 1 (precomputed mode)
+    bool pre;          // bases are a table [Wd][n] of 2^(c j) P_i: every window feeds the same bucket set
 };
 
 constexpr int MSM_RED_THREADS = 64;
@@ -66,6 +70,35 @@ inline MsmPlan msm_plan(uint64_t n, int force_c, bool g2) {
     if (m < 1) m = 1;
     p.red_m = (int)m;
     p.red_rb = (int)(p.B / (MSM_RED_THREADS * m));
+    p.Wd = p.W;
+    p.pre = false;
+    return p;
+}
+
+// Precomputed mode (table of 2^(c j) P_i resident next to the key): one shared bucket set, so a larger window is
+// affordable -- the bucket count no longer multiplies with the window count.  Entries per scalar drop from
+// ceil(255/16) = 16 to ceil(255/20) = 13 at 2^22 points.
+constexpr int MSM_PRE_CMIN = 16, MSM_PRE_CMAX = 21, MSM_PRE_HI_BITS = 8;
+inline int msm_pre_choose_c(uint64_t n, bool g2) {
+    int best = MSM_PRE_CMIN; double best_cost = 1e300;
+    for (int c = MSM_PRE_CMIN; c <= MSM_PRE_CMAX; c++) {
+        int W = 255 / c + 1;
+        double madd = g2 ? 30.0 : 10.0, fadd = g2 ? 42.0 : 14.0;
+        double cost = (double)n * W * madd + (double)(1u << (c - 1)) * (3.2 * fadd);
+        if (cost < best_cost) { best_cost = cost; best = c; }
+    }
+    return best;
+}
+inline MsmPlan msm_plan_pre(int c) {
+    MsmPlan p;
+    p.c = c;
+    p.W = 1;
+    p.Wd = 255 / c + 1;
+    p.B = 1u << (c - 1);
+    p.NB = p.B;
+    p.red_m = 16;
+    p.red_rb = (int)(p.B / (MSM_RED_THREADS * 16));
+    p.pre = true;
     return p;
 }
 
@@ -206,6 +239,135 @@ static __global__ void k_scatter(const uint16_t* __restrict__ digits, uint64_t n
             uint32_t pos = atomicAdd(&h[bucket], 1u);
             sorted[pos] = (uint32_t)i | (neg << 31);
         }
+    }
+}
+
+// ------------------------------------------------------------------ precomputed mode: two-level counting sort
+// Entries are (bucket, value) pairs, value = sign << 31 | (window * n + point) = an index into the table of
+// precomputed multiples.  The 2^(c-1) buckets do not fit a shared-memory histogram, so the sort is MSD in two
+// levels: level 1 splits on the top 8 bucket bits (256 groups, CTA-aggregated reservation on 256 global cursors),
+// level 2 is the same counting sort as k_hist / k_scatter inside every group on the remaining bits.
+template <class F>
+__device__ __forceinline__ void for_each_digit(const Fr::T* __restrict__ scalars, const uint32_t* __restrict__ map, uint64_t i,
+                                               int c, int W, F&& f) {
+    uint64_t src = map ? map[i] : i;
+    const uint4* q = reinterpret_cast<const uint4*>(scalars + src);
+    uint4 a = __ldg(q), b = __ldg(q + 1);
+    Fr::T s;
+    s.l[0] = a.x; s.l[1] = a.y; s.l[2] = a.z; s.l[3] = a.w; s.l[4] = b.x; s.l[5] = b.y; s.l[6] = b.z; s.l[7] = b.w;
+    s = Fr::from_mont(s);
+    uint32_t l[9];
+#pragma unroll
+    for (int k = 0; k < 8; k++) l[k] = s.l[k];
+    l[8] = 0;
+    const uint32_t mask = (1u << c) - 1, half = 1u << (c - 1);
+    uint32_t carry = 0;
+    for (int w = 0; w < W; w++) {
+        int bit = w * c;
+        uint32_t raw = 0;
+        if (bit < 256) {
+            int limb = bit >> 5, sh = bit & 31;
+            uint64_t two = (uint64_t)l[limb] | ((uint64_t)l[limb + 1] << 32);
+            raw = (uint32_t)(two >> sh) & mask;
+        }
+        raw += carry;
+        int d;
+        if (raw >= half) { carry = 1; d = (int)raw - (int)(half << 1); } else { carry = 0; d = (int)raw; }
+        if (d != 0) f(w, (uint32_t)(d < 0 ? -d : d) - 1, d < 0 ? 1u : 0u);
+    }
+}
+
+static __global__ void __launch_bounds__(1024) k_pre_hist1(const Fr::T* __restrict__ scalars, const uint32_t* __restrict__ map, uint64_t n,
+                                                           int c, int W, int lo_bits, uint32_t* __restrict__ counts1) {
+    __shared__ uint32_t h[256];
+    if (threadIdx.x < 256) h[threadIdx.x] = 0;
+    __syncthreads();
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) for_each_digit(scalars, map, i, c, W, [&](int, uint32_t bucket, uint32_t) { atomicAdd(&h[bucket >> lo_bits], 1u); });
+    __syncthreads();
+    if (threadIdx.x < 256 && h[threadIdx.x]) atomicAdd(&counts1[threadIdx.x], h[threadIdx.x]);
+}
+// counts1[256] -> off1[257], cursor1[256]  (one CTA of 256 threads)
+static __global__ void __launch_bounds__(256) k_pre_scan1(const uint32_t* __restrict__ counts1, uint32_t* __restrict__ off1, uint32_t* __restrict__ cursor1) {
+    __shared__ uint32_t s[256];
+    s[threadIdx.x] = counts1[threadIdx.x];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t run = 0;
+        for (int k = 0; k < 256; k++) { uint32_t v = s[k]; s[k] = run; run += v; }
+        off1[256] = run;
+    }
+    __syncthreads();
+    off1[threadIdx.x] = s[threadIdx.x];
+    cursor1[threadIdx.x] = s[threadIdx.x];
+}
+static __global__ void __launch_bounds__(1024) k_pre_scatter1(const Fr::T* __restrict__ scalars, const uint32_t* __restrict__ map, uint64_t n,
+                                                              int c, int W, int lo_bits, uint32_t* __restrict__ cursor1, uint2* __restrict__ pairs) {
+    __shared__ uint32_t h[256];
+    if (threadIdx.x < 256) h[threadIdx.x] = 0;
+    __syncthreads();
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) for_each_digit(scalars, map, i, c, W, [&](int, uint32_t bucket, uint32_t) { atomicAdd(&h[bucket >> lo_bits], 1u); });
+    __syncthreads();
+    if (threadIdx.x < 256) { uint32_t v = h[threadIdx.x]; if (v) h[threadIdx.x] = atomicAdd(&cursor1[threadIdx.x], v); }
+    __syncthreads();
+    if (i < n) for_each_digit(scalars, map, i, c, W, [&](int w, uint32_t bucket, uint32_t neg) {
+        uint32_t pos = atomicAdd(&h[bucket >> lo_bits], 1u);
+        pairs[pos] = make_uint2(bucket, (neg << 31) | (uint32_t)((uint64_t)w * n + i));
+    });
+}
+// grid (chunks, 256 groups): chunk ch of group g covers an equal share of [off1[g], off1[g+1])
+__device__ __forceinline__ void pre_chunk(const uint32_t* off1, uint32_t& lo, uint32_t& hi) {
+    const uint32_t g0 = off1[blockIdx.y], g1 = off1[blockIdx.y + 1];
+    const uint32_t per = (g1 - g0 + gridDim.x - 1) / gridDim.x;
+    lo = g0 + blockIdx.x * per;
+    hi = lo + per;
+    if (lo > g1) lo = g1;
+    if (hi > g1) hi = g1;
+}
+static __global__ void __launch_bounds__(1024) k_pre_hist2(const uint2* __restrict__ pairs, const uint32_t* __restrict__ off1, int lo_bits,
+                                                           uint32_t* __restrict__ counts) {
+    extern __shared__ uint32_t h[];
+    const uint32_t LB = 1u << lo_bits;
+    for (uint32_t b = threadIdx.x; b < LB; b += blockDim.x) h[b] = 0;
+    __syncthreads();
+    uint32_t lo, hi;
+    pre_chunk(off1, lo, hi);
+    for (uint32_t p = lo + threadIdx.x; p < hi; p += blockDim.x) atomicAdd(&h[pairs[p].x & (LB - 1)], 1u);
+    __syncthreads();
+    uint32_t* cg = counts + ((uint32_t)blockIdx.y << lo_bits);
+    for (uint32_t b = threadIdx.x; b < LB; b += blockDim.x) { uint32_t v = h[b]; if (v) atomicAdd(&cg[b], v); }
+}
+static __global__ void __launch_bounds__(1024) k_pre_scatter2(const uint2* __restrict__ pairs, const uint32_t* __restrict__ off1, int lo_bits,
+                                                              uint32_t* __restrict__ cursor, uint32_t* __restrict__ sorted) {
+    extern __shared__ uint32_t h[];
+    const uint32_t LB = 1u << lo_bits;
+    for (uint32_t b = threadIdx.x; b < LB; b += blockDim.x) h[b] = 0;
+    __syncthreads();
+    uint32_t lo, hi;
+    pre_chunk(off1, lo, hi);
+    for (uint32_t p = lo + threadIdx.x; p < hi; p += blockDim.x) atomicAdd(&h[pairs[p].x & (LB - 1)], 1u);
+    __syncthreads();
+    uint32_t* cg = cursor + ((uint32_t)blockIdx.y << lo_bits);
+    for (uint32_t b = threadIdx.x; b < LB; b += blockDim.x) { uint32_t v = h[b]; if (v) h[b] = atomicAdd(&cg[b], v); }
+    __syncthreads();
+    for (uint32_t p = lo + threadIdx.x; p < hi; p += blockDim.x) {
+        uint2 e = pairs[p];
+        sorted[atomicAdd(&h[e.x & (LB - 1)], 1u)] = e.y;
+    }
+}
+
+// table[j * n + i] = 2^(c j) * bases[i], j = 1 .. W-1 (row 0 = the bases themselves, already in place)
+template <class C>
+__global__ void __launch_bounds__(128) k_precompute(typename C::Aff* __restrict__ table, uint64_t n, int c, int W) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    typename C::Aff p = table[i];
+    for (int j = 1; j < W; j++) {
+        typename C::Xyzz a = C::from_aff(p);
+        for (int k = 0; k < c; k++) a = C::dbl(a);
+        p = C::to_aff(a);
+        table[(uint64_t)j * n + i] = p;
     }
 }
 
@@ -451,13 +613,15 @@ k_bucket_reduce(const typename C::Xyzz* __restrict__ buckets, uint32_t B, int m,
     if (threadIdx.x == 0) store_xyzz<C>(partial + (uint64_t)w * gridDim.x + blockIdx.x, sm[0]);
 }
 
-// grid W, 32 threads: sum the rb partials of a window
+// grid W, 32 threads: sum the rb partials of a window (rb > 32 in precomputed mode: strided first)
 template <class C>
 __global__ void __launch_bounds__(32) k_window_sum(const typename C::Xyzz* __restrict__ partial, int rb, typename C::Xyzz* __restrict__ wsum) {
     typedef typename C::Xyzz Xyzz;
     __shared__ Xyzz sm[32];
     const int w = blockIdx.x;
-    sm[threadIdx.x] = (int)threadIdx.x < rb ? load_xyzz<C>(partial + (uint64_t)w * rb + threadIdx.x) : C::inf();
+    Xyzz mine = C::inf();
+    for (int i = threadIdx.x; i < rb; i += 32) C::add(mine, load_xyzz<C>(partial + (uint64_t)w * rb + i));
+    sm[threadIdx.x] = mine;
     __syncwarp();
     for (int stride = 16; stride >= 1; stride >>= 1) {
         if ((int)threadIdx.x < stride) { Xyzz a = sm[threadIdx.x]; C::add(a, sm[threadIdx.x + stride]); sm[threadIdx.x] = a; }
@@ -473,15 +637,18 @@ struct MsmStats { int c = 0, W = 0; uint32_t acc_threads = 0; cudaEvent_t acc_be
 template <class C, int ACC_THREADS, int ACC_MINB, bool SMEM_ACC = false>
 void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const typename C::Aff* bases_d,
                  uint64_t n, int force_c, int waves, cudaStream_t st, MsmPlan& plan_out, MsmStats* stats,
-                 cudaStream_t tail = nullptr) {
+                 cudaStream_t tail = nullptr, int pre_c = 0, MsmWorkspace* sort_from = nullptr) {
+    // pre_c != 0: bases_d is the table [255/pre_c + 1][n] of precomputed multiples (k_precompute)
+    // sort_from: another MSM over the SAME scalars, map and n (bs1 / bs2 of a proof) whose sorted entries and bucket
+    // offsets are reused when the plans agree -- its stream must already have the sort enqueued
     typedef typename C::Xyzz Xyzz;
     constexpr bool IS_G2 = sizeof(typename C::E) > sizeof(Fp::T);   // the base field is Fp2
-    MsmPlan pl = msm_plan(n, force_c, IS_G2);
+    MsmPlan pl = pre_c ? msm_plan_pre(pre_c) : msm_plan(n, force_c, IS_G2);
     plan_out = pl;
-    if (stats) { stats->c = pl.c; stats->W = pl.W; stats->acc_threads = 0; }
+    if (stats) { stats->c = pl.c; stats->W = pl.Wd; stats->acc_threads = 0; }
     if (n == 0) return;   // callers treat an empty MSM as infinity (icicle.go:330-333)
-    if ((uint64_t)n * pl.W >= 0xfffffff0ull || n >= 0x7fffffffull) throw std::runtime_error("MSM too large for 32-bit entry indices");
-    const uint32_t total_max = (uint32_t)(n * pl.W);
+    if ((uint64_t)n * pl.Wd >= 0x7ffffff0ull || n >= 0x7fffffffull) throw std::runtime_error("MSM too large for 32-bit entry indices");
+    const uint32_t total_max = (uint32_t)(n * pl.Wd);
 
     int dev = 0, sms = 0;
     G16_CUDA(cudaGetDevice(&dev));
@@ -496,7 +663,8 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
     uint32_t cap = (total_max + 3) / 4;
     if (nthreads > cap) nthreads = cap < 1 ? 1 : cap;
 
-    ws.digits.reserve((size_t)n * pl.W * sizeof(uint16_t) + 64);
+    if (!pl.pre) ws.digits.reserve((size_t)n * pl.W * sizeof(uint16_t) + 64);
+    else { ws.pairs.reserve((size_t)total_max * sizeof(uint2) + 64); ws.level1.reserve(3 * 260 * sizeof(uint32_t)); }
     ws.sorted.reserve((size_t)total_max * sizeof(uint32_t) + 64);
     ws.counts.reserve((size_t)pl.NB * 4);
     ws.offsets.reserve((size_t)(pl.NB + 1) * 4);
@@ -510,12 +678,47 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
     ws.wsum.reserve((size_t)pl.W * sizeof(Xyzz));
     ws.host_wsum.reserve((size_t)pl.W * sizeof(Xyzz));
 
-    uint16_t* digits = ws.digits.as<uint16_t>();
     uint32_t* sorted = ws.sorted.as<uint32_t>();
     uint32_t* counts = ws.counts.as<uint32_t>();
     uint32_t* offsets = ws.offsets.as<uint32_t>();
     uint32_t* cursor = ws.cursor.as<uint32_t>();
     Xyzz* buckets = ws.buckets.as<Xyzz>();
+    const uint32_t scan_blocks = (pl.NB + SCAN_BLOCK - 1) / SCAN_BLOCK;
+    if (sort_from && sort_from->sort_done && sort_from->sort_n == n && sort_from->sort_c == pl.c && sort_from->sort_pre == pl.pre) {
+        G16_CUDA(cudaStreamWaitEvent(st, sort_from->sort_done, 0));
+        sorted = sort_from->sorted.as<uint32_t>();
+        offsets = sort_from->offsets.as<uint32_t>();
+    } else if (pl.pre) {
+        const int lo_bits = pl.c - 1 - MSM_PRE_HI_BITS;
+        uint32_t* counts1 = ws.level1.as<uint32_t>();
+        uint32_t* off1 = counts1 + 260;
+        uint32_t* cursor1 = off1 + 260;
+        uint2* pairs = ws.pairs.as<uint2>();
+        const unsigned sblocks = (unsigned)((n + 1023) / 1024);
+        G16_CUDA(cudaMemsetAsync(counts1, 0, 256 * 4, st));
+        G16_CUDA(cudaMemsetAsync(counts, 0, (size_t)pl.NB * 4, st));
+        k_pre_hist1<<<sblocks, 1024, 0, st>>>(scalars_d, map_d, n, pl.c, pl.Wd, lo_bits, counts1);
+        G16_LAUNCH_CHECK();
+        k_pre_scan1<<<1, 256, 0, st>>>(counts1, off1, cursor1);
+        G16_LAUNCH_CHECK();
+        k_pre_scatter1<<<sblocks, 1024, 0, st>>>(scalars_d, map_d, n, pl.c, pl.Wd, lo_bits, cursor1, pairs);
+        G16_LAUNCH_CHECK();
+        // level 2: enough chunks per group to fill the machine a few times, at least ~8K entries each
+        uint32_t chunks2 = (uint32_t)((sms * 4 + 255) / 256);
+        uint64_t per_group = ((uint64_t)total_max + 255) / 256;
+        while (chunks2 > 1 && per_group / chunks2 < 8192) chunks2--;
+        dim3 g2grid(chunks2, 256);
+        const size_t sm2 = (size_t)4 << lo_bits;
+        k_pre_hist2<<<g2grid, 1024, sm2, st>>>(pairs, off1, lo_bits, counts);
+        G16_LAUNCH_CHECK();
+        k_scan_local<<<scan_blocks, 1024, 0, st>>>(counts, offsets, ws.scan_tmp.as<uint32_t>(), pl.NB);
+        G16_LAUNCH_CHECK();
+        k_scan_add<<<scan_blocks, 1024, 0, st>>>(offsets, cursor, ws.scan_tmp.as<uint32_t>(), pl.NB);
+        G16_LAUNCH_CHECK();
+        k_pre_scatter2<<<g2grid, 1024, sm2, st>>>(pairs, off1, lo_bits, cursor, sorted);
+        G16_LAUNCH_CHECK();
+    } else {
+    uint16_t* digits = ws.digits.as<uint16_t>();
 
     k_digits<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(scalars_d, map_d, n, digits, pl.c, pl.W);
     G16_LAUNCH_CHECK();
@@ -534,14 +737,19 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
     dim3 hgrid(chunks, pl.W);
     k_hist<<<hgrid, 1024, hsmem, st>>>(digits, n, counts, pl.c, per_block);
     G16_LAUNCH_CHECK();
-    const uint32_t scan_blocks = (pl.NB + SCAN_BLOCK - 1) / SCAN_BLOCK;
     k_scan_local<<<scan_blocks, 1024, 0, st>>>(counts, offsets, ws.scan_tmp.as<uint32_t>(), pl.NB);
     G16_LAUNCH_CHECK();
     k_scan_add<<<scan_blocks, 1024, 0, st>>>(offsets, cursor, ws.scan_tmp.as<uint32_t>(), pl.NB);
     G16_LAUNCH_CHECK();
     k_scatter<<<hgrid, 1024, hsmem, st>>>(digits, n, cursor, sorted, pl.c, per_block);
     G16_LAUNCH_CHECK();
+    }
 
+    if (sorted == ws.sorted.as<uint32_t>()) {
+        if (!ws.sort_done) G16_CUDA(cudaEventCreateWithFlags(&ws.sort_done, cudaEventDisableTiming));
+        ws.sort_n = n; ws.sort_c = pl.c; ws.sort_pre = pl.pre;
+        G16_CUDA(cudaEventRecord(ws.sort_done, st));
+    }
     if (stats && stats->acc_begin) G16_CUDA(cudaEventRecord(stats->acc_begin, st));
     acc_kernel<<<(nthreads + ACC_THREADS - 1) / ACC_THREADS, ACC_THREADS, acc_smem, st>>>(
         bases_d, sorted, offsets, pl.NB, nthreads, buckets, ws.head.as<Xyzz>(), ws.tail.as<Xyzz>());

@@ -5,11 +5,17 @@
 
 namespace g16 {
 
+// pre_c != 0: bases_d is a table of precomputed multiples [255/pre_c + 1][n] made by msm_g1_precompute
 void msm_g1_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const G1::Aff* bases_d, uint64_t n,
-                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail = nullptr);
+                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail = nullptr,
+                    int pre_c = 0, MsmWorkspace* sort_from = nullptr);
 G1::Aff msm_g1_finish(const MsmWorkspace& ws, const MsmPlan& plan);
 void msm_g2_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const G2::Aff* bases_d, uint64_t n,
-                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail = nullptr);
+                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail = nullptr,
+                    int pre_c = 0, MsmWorkspace* sort_from = nullptr);
+// fill rows 1 .. 255/c of table_d (row j = 2^(c j) * row 0); row 0 holds the n bases
+void msm_g1_precompute(G1::Aff* table_d, uint64_t n, int c, cudaStream_t st);
+void msm_g2_precompute(G2::Aff* table_d, uint64_t n, int c, cudaStream_t st);
 G2::Aff msm_g2_finish(const MsmWorkspace& ws, const MsmPlan& plan);
 
 // out[i] = [scalars[i]] * G (generator), affine Montgomery.  Setup-side tooling: the device analogue of

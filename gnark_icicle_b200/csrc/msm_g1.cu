@@ -6,18 +6,23 @@
 namespace g16 {
 
 void msm_g1_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const G1::Aff* bases_d, uint64_t n,
-                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail) {
+                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail, int pre_c, MsmWorkspace* sort_from) {
     static const int variant = [] { const char* e = getenv("G16_ACC_VARIANT_G1"); return e ? atoi(e) : 0; }();
 #if G16_CURVE == 377
     // 12-limb Fp: the accumulator alone is 48 registers; 128 x 3 (<= 168 registers) is the default
-    if (variant == 1) msm_enqueue<G1, 256, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail);
-    else if (variant == 2) msm_enqueue<G1, 128, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail);
-    else msm_enqueue<G1, 128, 3>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail);
+    if (variant == 1) msm_enqueue<G1, 256, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+    else if (variant == 2) msm_enqueue<G1, 128, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+    else msm_enqueue<G1, 128, 3>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
 #else
     // 256-thread CTAs, 2 per SM (<= 128 registers): measured 1 % faster than 128 x 4; 128 x 5 spills (profiles/README.md)
-    if (variant == 1) msm_enqueue<G1, 128, 4>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail);
-    else msm_enqueue<G1, 256, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail);
+    if (variant == 1) msm_enqueue<G1, 128, 4>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+    else msm_enqueue<G1, 256, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
 #endif
+}
+void msm_g1_precompute(G1::Aff* table_d, uint64_t n, int c, cudaStream_t st) {
+    if (!n) return;
+    k_precompute<G1><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(table_d, n, c, 255 / c + 1);
+    G16_LAUNCH_CHECK();
 }
 G1::Aff msm_g1_finish(const MsmWorkspace& ws, const MsmPlan& plan) { return msm_finish<G1>(ws, plan); }
 

@@ -6,7 +6,7 @@
 namespace g16 {
 
 void msm_g2_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const G2::Aff* bases_d, uint64_t n,
-                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail) {
+                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail, int pre_c, MsmWorkspace* sort_from) {
     static const int variant = [] { const char* e = getenv("G16_ACC_VARIANT_G2"); return e ? atoi(e) : 0; }();
     // 128 x 2.  Measured (profiles/README.md): the G2 kernel is issue-bound -- every integer instruction, IADD3 included,
     // takes the same two-cycle slot as an IMAD -- so more CTAs/SM do not help (3-4 CTAs/SM: +15..50 %).  Parking the
@@ -17,8 +17,13 @@ void msm_g2_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* ma
 #else
     const bool smem_acc = variant == 1;
 #endif
-    if (smem_acc) msm_enqueue<G2, 128, 2, true>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail);
-    else msm_enqueue<G2, 128, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail);
+    if (smem_acc) msm_enqueue<G2, 128, 2, true>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+    else msm_enqueue<G2, 128, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+}
+void msm_g2_precompute(G2::Aff* table_d, uint64_t n, int c, cudaStream_t st) {
+    if (!n) return;
+    k_precompute<G2><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(table_d, n, c, 255 / c + 1);
+    G16_LAUNCH_CHECK();
 }
 G2::Aff msm_g2_finish(const MsmWorkspace& ws, const MsmPlan& plan) { return msm_finish<G2>(ws, plan); }
 

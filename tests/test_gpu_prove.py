@@ -118,3 +118,42 @@ def test_full_size_prove_2p20_trapdoor(ctx):
     h = ocpu.compute_h(case.a, case.b, case.c, case.n)
     assert_limbs_equal(pts, case.expected_points(h), "2^20 prove points vs trapdoor identity")
     case.pk.free_device()
+
+
+# ---------------------------------------------------------------- precomputed-multiples mode (shared bucket set)
+@pytest.mark.parametrize("kind", ["random", "bits", "equal", "sharded"])
+def test_precomputed_tables_give_the_same_points_as_the_window_path(ctx, kind):
+    """g16_pk_upload keeps 2^(c j) multiples of every base (n >= 2^14) and the prove MSMs then use ONE bucket set with
+    a two-level sort; "msm_precompute" = 0 after the upload runs the per-window path on the same key.  Both must give
+    identical points (and both are checked against the trapdoor in the other tests)."""
+    nc = 1 << 15
+    case = ChainCase(nc, seed=41, g1_mul=ctx.g1_fixed_base_mul, g2_mul=ctx.g2_fixed_base_mul)
+    W = case.W.copy()
+    if kind == "bits":          # witness-like: most wires are 0 / 1, a few r-1
+        W[4::2] = 0
+        W[5::4] = ocpu.fr_arr([1])[0]
+        W[7::64] = ocpu.fr_arr([R - 1])[0]
+    elif kind == "equal":       # every wire the same value: all entries of a window land in one bucket
+        W[:] = W[9]
+    sol = g16.R1CSSolution(W=W, A=case.a, B=case.b, C=case.c)
+    pk = case.pk
+    shards = 3 if kind == "sharded" else 1
+    try:
+        got, want = [], []
+        for si in range(shards):
+            pk.free_device()
+            pk.setup_device_pointers(g16.NewProverConfig(g16.WithDevice(0, si, shards)))
+            c = pk.device[0]
+            p1, st1 = g16.prove_msms(pk, sol)
+            c.set("msm_precompute", 0)
+            p0, st0 = g16.prove_msms(pk, sol)
+            if shards == 1:
+                assert st1["msm_windows"][0] < st0["msm_windows"][0], (st1["msm_windows"], st0["msm_windows"])
+            got.append(p1)
+            want.append(p0)
+        assert np.array_equal(g16.combine_shards(got), g16.combine_shards(want))
+        if kind == "random":
+            h = ocpu.compute_h(case.a, case.b, case.c, case.n)
+            assert_limbs_equal(got[0], case.expected_points(h), "precomputed mode vs trapdoor")
+    finally:
+        pk.free_device()
