@@ -48,6 +48,8 @@ struct g16_ctx {
     std::map<int, NttDomain> domains;
     std::map<uint64_t, PkDev> pks;
     std::map<uint64_t, R1csDev> r1cs;
+    struct Bases { DevBuf table; uint64_t n = 0; int pre_c = 0; bool g2 = false; };
+    std::map<uint64_t, Bases> bases;
     uint64_t next_pk = 1;
     MsmWorkspace ws[5];
     DevBuf stage[4];             // host-pointer variants: staged inputs
@@ -156,6 +158,7 @@ void g16_ctx_destroy(g16_ctx* ctx) {
     cudaDeviceSynchronize();
     for (auto& kv : ctx->pks) kv.second.release();
     for (auto& kv : ctx->r1cs) kv.second.release();
+    for (auto& kv : ctx->bases) kv.second.table.release();
     for (auto& kv : ctx->domains) kv.second.release();
     for (auto& w : ctx->ws) w.release();
     for (auto& s : ctx->stage) s.release();
@@ -380,6 +383,67 @@ extern "C" int g16_prove_bn254(g16_ctx* ctx, uint64_t pk_handle, const void* W, 
             G16_CUDA(cudaEventElapsedTime(&stats->ms_h2d, ctx->ev[26], ctx->ev[27]));
             G16_CUDA(cudaEventElapsedTime(&stats->ms_total, ctx->ev[26], ctx->ev[14]));
             stats->h2d_bytes = 3 * cb + (uint64_t)n_wires * 32;
+        }
+    });
+}
+
+// =================================================================== resident bases
+extern "C" int g16_bases_upload(g16_ctx* ctx, const void* bases, uint64_t n, int g2, int from_device, uint64_t* handle) {
+    return guarded(ctx, [&] {
+        if (!handle || (n && !bases)) throw std::runtime_error("null argument");
+        g16_ctx::Bases b;
+        b.n = n; b.g2 = g2 != 0;
+        cudaStream_t st = ctx->stream;
+        const void* src = bases;
+        if (from_device && n) {   // upload_bases copies host -> device; for a device source copy into row 0 afterwards
+            int pre_c = 0;
+            const size_t row = (size_t)n * (g2 ? G2SZ : G1SZ);
+            if (ctx->msm_precompute && n >= PRECOMPUTE_MIN_POINTS) {
+                const int c = msm_pre_choose_c(n, g2 != 0);
+                size_t free_b = 0, total_b = 0;
+                G16_CUDA(cudaMemGetInfo(&free_b, &total_b));
+                if (row * (size_t)(255 / c + 1) <= free_b / 2) pre_c = c;
+            }
+            b.table.reserve(pre_c ? row * (size_t)(255 / pre_c + 1) : row);
+            G16_CUDA(cudaMemcpyAsync(b.table.p, src, row, cudaMemcpyDeviceToDevice, st));
+            if (pre_c) { if (g2) msm_g2_precompute(b.table.as<G2::Aff>(), n, pre_c, st); else msm_g1_precompute(b.table.as<G1::Aff>(), n, pre_c, st); }
+            b.pre_c = pre_c;
+        } else if (g2) {
+            upload_bases<G2>(ctx, b.table, src, n, b.pre_c, st);
+        } else {
+            upload_bases<G1>(ctx, b.table, src, n, b.pre_c, st);
+        }
+        G16_CUDA(cudaStreamSynchronize(st));
+        uint64_t h = ctx->next_pk++;
+        ctx->bases[h] = b;
+        *handle = h;
+    });
+}
+extern "C" int g16_bases_free(g16_ctx* ctx, uint64_t handle) {
+    return guarded(ctx, [&] {
+        auto it = ctx->bases.find(handle);
+        if (it == ctx->bases.end()) throw std::runtime_error("unknown bases handle");
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+        it->second.table.release();
+        ctx->bases.erase(it);
+    });
+}
+extern "C" int g16_msm_resident_dev(g16_ctx* ctx, uint64_t handle, const void* scalars_d, void* out) {
+    return guarded(ctx, [&] {
+        auto it = ctx->bases.find(handle);
+        if (it == ctx->bases.end()) throw std::runtime_error("unknown bases handle");
+        if (!out || (it->second.n && !scalars_d)) throw std::runtime_error("null argument");
+        const g16_ctx::Bases& b = it->second;
+        const int pre_c = (ctx->msm_c == 0 && ctx->msm_precompute) ? b.pre_c : 0;
+        MsmPlan pl;
+        if (b.g2) {
+            if (b.n) { msm_g2_enqueue(ctx->ws[4], (const Fr::T*)scalars_d, nullptr, b.table.as<G2::Aff>(), b.n, ctx->msm_c, ctx->msm_waves, ctx->stream, pl, nullptr, nullptr, pre_c);
+                       G16_CUDA(cudaStreamSynchronize(ctx->stream)); }
+            copy_out(out, b.n ? msm_g2_finish(ctx->ws[4], pl) : G2::aff_inf());
+        } else {
+            if (b.n) { msm_g1_enqueue(ctx->ws[0], (const Fr::T*)scalars_d, nullptr, b.table.as<G1::Aff>(), b.n, ctx->msm_c, ctx->msm_waves, ctx->stream, pl, nullptr, nullptr, pre_c);
+                       G16_CUDA(cudaStreamSynchronize(ctx->stream)); }
+            copy_out(out, b.n ? msm_g1_finish(ctx->ws[0], pl) : G1::aff_inf());
         }
     });
 }

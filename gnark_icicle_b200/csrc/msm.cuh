@@ -531,7 +531,7 @@ k_accumulate(const typename C::Aff* __restrict__ bases, const uint32_t* __restri
 // Buckets whose entries span several accumulate slices are stitched here.  Up to FIXUP_SERIAL pieces: one thread
 // adds them; longer ones (skewed scalars, the short top window, DummySetup-like inputs) go to a work list that
 // k_fixup_heavy reduces with a whole CTA per bucket.
-constexpr uint32_t FIXUP_SERIAL = 8;
+constexpr uint32_t FIXUP_SERIAL = 24;
 
 template <class C>
 __global__ void k_fixup(const uint32_t* __restrict__ offsets, uint32_t nb, uint32_t nthreads,
@@ -660,7 +660,9 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
     G16_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, acc_kernel, ACC_THREADS, acc_smem));
     if (occ < 1) occ = 1;
     uint32_t nthreads = (uint32_t)sms * occ * ACC_THREADS * (waves > 0 ? waves : 2);
-    uint32_t cap = (total_max + 3) / 4;
+    // at least 16 entries per thread: shorter slices only multiply the pieces k_fixup has to stitch (a bucket of the
+    // shared set holds ~32 entries at 2^16 points, and every bucket cut into > 8 pieces goes through k_fixup_heavy)
+    uint32_t cap = (total_max + 15) / 16;
     if (nthreads > cap) nthreads = cap < 1 ? 1 : cap;
 
     if (!pl.pre) ws.digits.reserve((size_t)n * pl.W * sizeof(uint16_t) + 64);

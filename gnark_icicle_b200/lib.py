@@ -73,6 +73,7 @@ SYMBOLS = [
     "g16_ctx_create", "g16_ctx_destroy", "g16_last_error", "g16_ctx_set", "g16_kernel_launch_count",
     "g16_pk_upload", "g16_pk_free", "g16_prove_bn254", "g16_prove_bn254_dev", "g16_assemble_proof_bn254",
     "g16_r1cs_upload", "g16_r1cs_free", "g16_r1cs_eval_dev", "g16_prove_bn254_wires",
+    "g16_bases_upload", "g16_bases_free", "g16_msm_resident_dev",
     "g16_msm_g1", "g16_msm_g1_dev", "g16_msm_g2", "g16_msm_g2_dev", "g16_ntt", "g16_ntt_dev",
     "g16_compute_h", "g16_compute_h_dev", "g16_fr_mul_vec",
     "g16_dist_ntt_stages_dev", "g16_dist_permute_dev", "g16_dist_pointwise_h_dev", "g16_prove_msms_dev",
@@ -280,6 +281,26 @@ class Context:
         self._check(self._lib.g16_prove_bn254_dev(self._h, u64(pk_handle), _ptr(W_ptr), _ptr(a_ptr), _ptr(b_ptr), _ptr(c_ptr),
                                                   _ptr(out), ctypes.byref(st)), "g16_prove_bn254_dev")
         return out, st.as_dict()
+
+    # ---- resident bases (precomputed multiples when they fit)
+    def bases_upload(self, bases, g2=False):
+        b = _arr(bases, self.g2w if g2 else self.g1w)
+        h = u64(0)
+        self._check(self._lib.g16_bases_upload(self._h, _ptr(b), u64(len(b)), int(g2), 0, ctypes.byref(h)), "g16_bases_upload")
+        return h.value
+
+    def bases_upload_dev(self, bases_ptr, n, g2=False):
+        h = u64(0)
+        self._check(self._lib.g16_bases_upload(self._h, _ptr(bases_ptr), u64(n), int(g2), 1, ctypes.byref(h)), "g16_bases_upload")
+        return h.value
+
+    def bases_free(self, handle):
+        self._check(self._lib.g16_bases_free(self._h, u64(handle)), "g16_bases_free")
+
+    def msm_resident_dev(self, handle, scalars_ptr, g2=False):
+        out = np.zeros(self.g2w if g2 else self.g1w, dtype=np.uint64)
+        self._check(self._lib.g16_msm_resident_dev(self._h, u64(handle), _ptr(scalars_ptr), _ptr(out)), "g16_msm_resident_dev")
+        return out
 
     # ---- constraint matrices on the device
     def r1cs_upload(self, n_constraints, n_wires, coeffs, matrices):

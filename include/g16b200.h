@@ -136,6 +136,12 @@ int g16_assemble_proof_bn254(const void* pk_points, const void* r, const void* s
 /* replaces iciclegnark.MsmOnDevice (icicle.go:302,315,332,355) / curve.G1Jac.MultiExp (prove.go:204-247) */
 int g16_msm_g1(g16_ctx* ctx, const void* scalars, const void* bases, uint64_t n, void* out_affine);
 int g16_msm_g1_dev(g16_ctx* ctx, const void* scalars_d, const void* bases_d, uint64_t n, void* out_affine);
+/* Resident bases (the Groth16 case: bases are key material, fixed across proofs; the analogue of icicle's
+ * precompute_bases + MSMConfig.precompute_factor): upload once, optionally with the table of 2^(c j) multiples, then
+ * run MSMs against the handle with device-resident scalars.  g2 != 0: G2 bases / result. */
+int g16_bases_upload(g16_ctx* ctx, const void* bases, uint64_t n, int g2, int from_device, uint64_t* bases_handle);
+int g16_bases_free(g16_ctx* ctx, uint64_t bases_handle);
+int g16_msm_resident_dev(g16_ctx* ctx, uint64_t bases_handle, const void* scalars_d, void* out_affine);
 /* replaces iciclegnark.MsmG2OnDevice (icicle.go:382) / curve.G2Jac.MultiExp (prove.go:293) */
 int g16_msm_g2(g16_ctx* ctx, const void* scalars, const void* bases, uint64_t n, void* out_affine);
 int g16_msm_g2_dev(g16_ctx* ctx, const void* scalars_d, const void* bases_d, uint64_t n, void* out_affine);

@@ -167,3 +167,32 @@ def test_msm_g2_2p20_trapdoor(ctx):
     pts = ctx.g2_fixed_base_mul(k)
     s = fr_rand(1201, n)
     assert_limbs_equal(ctx.msm_g2(s, pts), trapdoor_g2(s, k), "msm_g2 2^20")
+
+
+# ---------------------------------------------------------------- resident bases with precomputed multiples
+@pytest.mark.parametrize("n,g2", [(1 << 16, False), (50000, False), (1 << 14, True), (1000, False), (0, False)])
+def test_msm_resident_bases(ctx, n, g2):
+    """g16_bases_upload keeps the bases (and, from 2^14 points, the table of 2^(c j) multiples) on the device;
+    g16_msm_resident_dev must give the same point as the plain MSM and as the trapdoor identity."""
+    import torch
+    k = fr_rand(77 + n % 13, n)
+    s = fr_rand(78 + n % 13, n)
+    if n:
+        s[:3] = fr_from_ints([0, 1, R - 1])
+    bases = (ctx.g2_fixed_base_mul(k) if g2 else ctx.g1_fixed_base_mul(k)) if n else np.zeros((0, 16 if g2 else 8), dtype=np.uint64)
+    if n > 10:
+        bases[7] = 0                       # an infinity base is legal
+        k = k.copy(); k[7] = 0
+    h = ctx.bases_upload(bases, g2=g2)
+    try:
+        sd = torch.from_numpy(np.ascontiguousarray(s).view(np.int64)).cuda() if n else torch.zeros((1, 4), dtype=torch.int64, device="cuda")
+        torch.cuda.synchronize()
+        got = ctx.msm_resident_dev(h, sd.data_ptr(), g2=g2)
+        plain = (ctx.msm_g2 if g2 else ctx.msm_g1)(s, bases)
+        assert_limbs_equal(got, plain, "resident vs plain MSM")
+        if n:
+            assert_limbs_equal(got, (trapdoor_g2 if g2 else trapdoor_g1)(s, k), "resident MSM vs trapdoor")
+        else:
+            assert not got.any()
+    finally:
+        ctx.bases_free(h)
