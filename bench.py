@@ -395,11 +395,12 @@ def run_ours(args):
     g1_bytes = sum(st["msm_n"][i] * st["msm_windows"][i] for i in range(4)) * (8 * ctx.g1w + 4)
     roof["hbm"] = {"bound": "hbm", "achieved": g1_bytes / (g1_ms * 1e-3) / 1e9, "peak": pk_["hbm_gbs"], "unit": "GB/s",
                    "frac": g1_bytes / (g1_ms * 1e-3) / 1e9 / pk_["hbm_gbs"], "peak_source": src,
-                   "algorithmic_bytes_per_launch_2p22": (1 << 22) * 16 * 68,
+                   "algorithmic_bytes_per_launch_2p22": (1 << 22) * 13 * 68,
                    "note": "the accumulate kernel is bound by the integer multiplier, not HBM: it moves <10 % of the copy bandwidth"}
     if args.log_n == 22 and args.curve == "bn254":
-        roof["traffic"] = 7.06e9
-        roof["traffic_source"] = "profiles/r01b_accumulate_2p22_ncu_raw.csv: 6.95 GB read + 0.11 GB written per 2^22-point launch (12.04 ms)"
+        roof["traffic"] = 4.07e9
+        roof["traffic_source"] = ("profiles/r01c_accumulate_2p22_ncu_raw.csv: 3.96 GB read + 0.11 GB written per 2^22-point launch "
+                                  "(9.6 ms, 54.5 M entries x 68 B = 3.71 GB algorithmic); before the 64-byte L2 fill hint: 7.45 GB")
     ntt_bytes = 7 * 64 * n
     if st["ms_compute_h"] > 0:
       roof["compute_h"] = {"bound": "hbm", "achieved": ntt_bytes / (st["ms_compute_h"] * 1e-3) / 1e9, "peak": pk_["hbm_gbs"],

@@ -135,6 +135,7 @@ int g16_ctx_create(g16_ctx** out, int curve_id, const int* device_ids, int n_dev
         if (count < 1) throw std::runtime_error("no CUDA device: libg16b200 has no CPU fallback");
         c->device = (device_ids && n_devices == 1) ? device_ids[0] : 0;
         G16_CUDA(cudaSetDevice(c->device));
+        if (const char* e = getenv("G16_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(e));   // experiment knob
         G16_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
         for (auto& a : c->aux) G16_CUDA(cudaStreamCreateWithFlags(&a, cudaStreamNonBlocking));
         int prio_lo = 0, prio_hi = 0;

@@ -379,7 +379,12 @@ __device__ __forceinline__ typename C::Aff load_aff(const typename C::Aff* p) {
     const uint4* src = reinterpret_cast<const uint4*>(p);
     uint4* dst = reinterpret_cast<uint4*>(&r);
 #pragma unroll
-    for (int i = 0; i < Q; i++) dst[i] = __ldg(src + i);
+    for (int i = 0; i < Q; i++) {
+        // read-only path with a 64-byte L2 fill hint: the gathers are random, so the default 128-byte line fill of a
+        // 64-byte G1 point doubles the DRAM traffic (ncu: 135 B per entry before, profiles/README.md)
+        asm volatile("ld.global.nc.L2::64B.v4.u32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(dst[i].x), "=r"(dst[i].y), "=r"(dst[i].z), "=r"(dst[i].w) : "l"(src + i));
+    }
     return r;
 }
 template <class C>
