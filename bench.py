@@ -402,7 +402,7 @@ def run_ours(args):
         roof["traffic_source"] = ("profiles/r01c_accumulate_2p22_ncu_raw.csv: 3.96 GB read + 0.11 GB written per 2^22-point launch "
                                   "(9.6 ms, 54.5 M entries x 68 B = 3.71 GB algorithmic); before the 64-byte L2 fill hint: 7.45 GB")
     ntt_bytes = 7 * 64 * n
-    if st["ms_compute_h"] > 0:
+    if world == 1 and st["ms_compute_h"] > 0:
       roof["compute_h"] = {"bound": "hbm", "achieved": ntt_bytes / (st["ms_compute_h"] * 1e-3) / 1e9, "peak": pk_["hbm_gbs"],
                          "unit": "GB/s", "frac": ntt_bytes / (st["ms_compute_h"] * 1e-3) / 1e9 / pk_["hbm_gbs"],
                          "peak_source": src, "note": "7 transforms x 64n B algorithmic; the butterflies are IMAD-bound at 254 bits"}
