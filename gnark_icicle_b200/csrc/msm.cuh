@@ -27,7 +27,7 @@
 namespace g16 {
 
 struct MsmWorkspace {
-    DevBuf digits, sorted, counts, offsets, cursor, buckets, head, tail, partial, wsum, scan_tmp, heavy, pairs, level1;
+    DevBuf digits, sorted, counts, offsets, cursor, buckets, head, tail, partial, wsum, scan_tmp, heavy, pairs, level1, fold;
     PinnedBuf host_wsum;
     cudaEvent_t acc_done = nullptr, tail_done = nullptr, sort_done = nullptr;
     uint64_t sort_n = 0; int sort_c = 0; bool sort_pre = false;   // what `sorted` / `offsets` currently describe
@@ -37,7 +37,7 @@ struct MsmWorkspace {
         if (sort_done) cudaEventDestroy(sort_done);
         acc_done = tail_done = sort_done = nullptr;
         digits.release(); sorted.release(); counts.release(); offsets.release(); cursor.release();
-        buckets.release(); head.release(); tail.release(); partial.release(); wsum.release(); host_wsum.release(); scan_tmp.release(); heavy.release(); pairs.release(); level1.release();
+        buckets.release(); head.release(); tail.release(); partial.release(); wsum.release(); host_wsum.release(); scan_tmp.release(); heavy.release(); pairs.release(); level1.release(); fold.release();
     }
 };
 
@@ -45,12 +45,16 @@ struct MsmPlan {
     int c, W;          // window bits; number of bucket SETS (= windows; 1 with precomputed multiples)
     uint32_t B;        // buckets per set = 2^(c-1)
     uint32_t NB;       // W * B
-    int red_m, red_rb; // bucket-reduce: buckets per thread, CTAs per set
+    int red_m, red_rb; // bucket-reduce level 2 (over the level-1 sums): sums per thread, CTAs per set
+    int fold_m, fold_rb; // bucket-reduce level 1: buckets per thread (power of two), CTAs per set
     int Wd;            // digits (bucket entries) per scalar: = W, or the window count when W == 1 (precomputed mode)
     bool pre;          // bases are a table [Wd][n] of 2^(c j) P_i: every window feeds the same bucket set
 };
 
 constexpr int MSM_RED_THREADS = 64;
+
+struct MsmPlan;
+inline void msm_plan_reduce(MsmPlan& p);
 
 inline MsmPlan msm_plan(uint64_t n, int force_c, bool g2) {
     MsmPlan p;
@@ -66,10 +70,7 @@ inline MsmPlan msm_plan(uint64_t n, int force_c, bool g2) {
     p.W = 255 / p.c + 1;
     p.B = 1u << (p.c - 1);
     p.NB = p.W * p.B;
-    uint32_t m = p.B / (MSM_RED_THREADS * 32);
-    if (m < 1) m = 1;
-    p.red_m = (int)m;
-    p.red_rb = (int)(p.B / (MSM_RED_THREADS * m));
+    msm_plan_reduce(p);
     p.Wd = p.W;
     p.pre = false;
     return p;
@@ -96,10 +97,22 @@ inline MsmPlan msm_plan_pre(int c) {
     p.Wd = 255 / c + 1;
     p.B = 1u << (c - 1);
     p.NB = p.B;
-    p.red_m = 16;
-    p.red_rb = (int)(p.B / (MSM_RED_THREADS * 16));
+    msm_plan_reduce(p);
     p.pre = true;
     return p;
+}
+// Two-level reduction of a bucket set: level 1 folds fold_m consecutive buckets per thread (no scalar multiplication),
+// level 2 is the weighted sum of the B / fold_m level-1 sums (k_bucket_reduce).  B >= 128 (c >= 8).
+inline void msm_plan_reduce(MsmPlan& p) {
+    uint32_t fm = p.B / MSM_RED_THREADS;
+    if (fm > 16) fm = 16;
+    p.fold_m = (int)fm;
+    p.fold_rb = (int)(p.B / (MSM_RED_THREADS * fm));
+    const uint32_t nt = p.B / fm;                        // level-1 sums per set, a multiple of 64
+    uint32_t m = nt / (MSM_RED_THREADS * 32);
+    if (m < 1) m = 1;
+    p.red_m = (int)m;
+    p.red_rb = (int)(nt / (MSM_RED_THREADS * m));
 }
 
 // ------------------------------------------------------------------ digits
@@ -588,6 +601,36 @@ k_fixup_heavy(const uint32_t* __restrict__ offsets, uint32_t nb, uint32_t nthrea
 }
 
 // ------------------------------------------------------------------ bucket reduction
+// The weighted sum  sum_k (k+1) B_k  of a bucket set in two levels.  With k = t*m + j (thread t, j < m):
+//   (k+1) = (t+1)*m - (m-1-j)   =>   total = m * sum_t (t+1) S_t  -  sum_t T_t,
+//   S_t = sum_j B_{tm+j},  T_t = sum_j (m-1-j) B_{tm+j}  -- both from one forward running sum, no scalar multiplication.
+// Level 1 (k_bucket_fold): S_t -> fold[w][t], T_t tree-summed per CTA -> partialT.  Level 2: k_bucket_reduce on the
+// S_t as a bucket set of B/m entries.  The host finishes with log2(m) doublings and one subtraction per set.
+// grid (fold_rb, W)
+template <class C>
+__global__ void __launch_bounds__(MSM_RED_THREADS)
+k_bucket_fold(const typename C::Xyzz* __restrict__ buckets, uint32_t B, int m, typename C::Xyzz* __restrict__ fold,
+              typename C::Xyzz* __restrict__ partialT) {
+    typedef typename C::Xyzz Xyzz;
+    __shared__ Xyzz sm[MSM_RED_THREADS];
+    const int w = blockIdx.y;
+    const uint32_t t = blockIdx.x * MSM_RED_THREADS + threadIdx.x;
+    const Xyzz* bw = buckets + (uint64_t)w * B + (uint64_t)t * m;
+    Xyzz run = C::inf(), ws = C::inf();
+    for (int j = 0; j < m; j++) {
+        C::add(ws, run);
+        C::add(run, load_xyzz<C>(bw + j));
+    }
+    store_xyzz<C>(fold + (uint64_t)w * (B / m) + t, run);
+    sm[threadIdx.x] = ws;
+    __syncthreads();
+    for (int stride = MSM_RED_THREADS / 2; stride >= 1; stride >>= 1) {
+        if ((int)threadIdx.x < stride) { Xyzz a = sm[threadIdx.x]; C::add(a, sm[threadIdx.x + stride]); sm[threadIdx.x] = a; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) store_xyzz<C>(partialT + (uint64_t)w * gridDim.x + blockIdx.x, sm[0]);
+}
+
 // grid (red_rb, W); thread handles m consecutive buckets; CTA result -> partial[w * red_rb + blockIdx.x]
 template <class C>
 __global__ void __launch_bounds__(MSM_RED_THREADS)
@@ -604,9 +647,12 @@ k_bucket_reduce(const typename C::Xyzz* __restrict__ buckets, uint32_t B, int m,
         C::add(ws, run);
     }
     // + b0 * run  (weights are b+1; the running sums above cover (b - b0 + 1))
-    if (b0) {
-        uint32_t kk[1] = {b0};
-        Xyzz t = C::mul(run, kk, 1);
+    if (b0) {   // double-and-add from the top set bit of b0
+        Xyzz t = run;
+        for (int i = 30 - __clz(b0); i >= 0; i--) {
+            t = C::dbl(t);
+            if ((b0 >> i) & 1) C::add(t, run);
+        }
         C::add(ws, t);
     }
     sm[threadIdx.x] = ws;
@@ -681,9 +727,10 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
     ws.buckets.reserve((size_t)pl.NB * sizeof(Xyzz));
     ws.head.reserve((size_t)nthreads * sizeof(Xyzz));
     ws.tail.reserve((size_t)nthreads * sizeof(Xyzz));
-    ws.partial.reserve((size_t)pl.W * pl.red_rb * sizeof(Xyzz));
-    ws.wsum.reserve((size_t)pl.W * sizeof(Xyzz));
-    ws.host_wsum.reserve((size_t)pl.W * sizeof(Xyzz));
+    ws.fold.reserve((size_t)pl.W * (pl.B / pl.fold_m) * sizeof(Xyzz));
+    ws.partial.reserve((size_t)pl.W * (pl.red_rb + pl.fold_rb) * sizeof(Xyzz));
+    ws.wsum.reserve((size_t)2 * pl.W * sizeof(Xyzz));
+    ws.host_wsum.reserve((size_t)2 * pl.W * sizeof(Xyzz));
 
     uint32_t* sorted = ws.sorted.as<uint32_t>();
     uint32_t* counts = ws.counts.as<uint32_t>();
@@ -782,12 +829,21 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
         k_fixup_heavy<C, HT><<<sms * 2, HT, hs, st>>>(offsets, pl.NB, nthreads, buckets, ws.head.as<Xyzz>(), ws.tail.as<Xyzz>(), heavy);
         G16_LAUNCH_CHECK();
     }
-    dim3 rgrid(pl.red_rb, pl.W);
-    k_bucket_reduce<C><<<rgrid, MSM_RED_THREADS, 0, st>>>(buckets, pl.B, pl.red_m, ws.partial.as<Xyzz>());
-    G16_LAUNCH_CHECK();
-    k_window_sum<C><<<pl.W, 32, 0, st>>>(ws.partial.as<Xyzz>(), pl.red_rb, ws.wsum.as<Xyzz>());
-    G16_LAUNCH_CHECK();
-    G16_CUDA(cudaMemcpyAsync(ws.host_wsum.p, ws.wsum.p, (size_t)pl.W * sizeof(Xyzz), cudaMemcpyDeviceToHost, st));
+    {
+        Xyzz* partialU = ws.partial.as<Xyzz>();
+        Xyzz* partialT = partialU + (size_t)pl.W * pl.red_rb;
+        Xyzz* wsum = ws.wsum.as<Xyzz>();                 // [0, W): U_w = sum_t (t+1) S_t, [W, 2W): T_w
+        dim3 fgrid(pl.fold_rb, pl.W), rgrid(pl.red_rb, pl.W);
+        k_bucket_fold<C><<<fgrid, MSM_RED_THREADS, 0, st>>>(buckets, pl.B, pl.fold_m, ws.fold.as<Xyzz>(), partialT);
+        G16_LAUNCH_CHECK();
+        k_bucket_reduce<C><<<rgrid, MSM_RED_THREADS, 0, st>>>(ws.fold.as<Xyzz>(), pl.B / pl.fold_m, pl.red_m, partialU);
+        G16_LAUNCH_CHECK();
+        k_window_sum<C><<<pl.W, 32, 0, st>>>(partialU, pl.red_rb, wsum);
+        G16_LAUNCH_CHECK();
+        k_window_sum<C><<<pl.W, 32, 0, st>>>(partialT, pl.fold_rb, wsum + pl.W);
+        G16_LAUNCH_CHECK();
+    }
+    G16_CUDA(cudaMemcpyAsync(ws.host_wsum.p, ws.wsum.p, (size_t)2 * pl.W * sizeof(Xyzz), cudaMemcpyDeviceToHost, st));
     if (st != main_st) {   // the MSM's own stream completes when its tail does
         G16_CUDA(cudaEventRecord(ws.tail_done, st));
         G16_CUDA(cudaStreamWaitEvent(main_st, ws.tail_done, 0));
@@ -803,7 +859,10 @@ typename C::Aff msm_finish(const MsmWorkspace& ws, const MsmPlan& pl) {
     Xyzz acc = C::inf();
     for (int w = pl.W - 1; w >= 0; w--) {
         for (int i = 0; i < pl.c; i++) acc = C::dbl(acc);
-        C::add(acc, wsum[w]);
+        Xyzz u = wsum[w];                                  // set total = fold_m * U_w - T_w
+        for (int m = pl.fold_m; m > 1; m >>= 1) u = C::dbl(u);
+        C::add(u, C::neg(wsum[pl.W + w]));
+        C::add(acc, u);
     }
     return C::to_aff(acc);
 }
