@@ -50,6 +50,8 @@ struct g16_ctx {
     std::map<uint64_t, R1csDev> r1cs;
     struct Bases { DevBuf table; uint64_t n = 0; int pre_c = 0; bool g2 = false; };
     std::map<uint64_t, Bases> bases;
+    struct CommitKey { Bases basis, basis_exp_sigma; };   // pedersen.ProvingKey (setup.go:57)
+    std::map<uint64_t, CommitKey> commit_keys;
     uint64_t next_pk = 1;
     MsmWorkspace ws[5];
     DevBuf stage[4];             // host-pointer variants: staged inputs
@@ -160,6 +162,7 @@ void g16_ctx_destroy(g16_ctx* ctx) {
     for (auto& kv : ctx->pks) kv.second.release();
     for (auto& kv : ctx->r1cs) kv.second.release();
     for (auto& kv : ctx->bases) kv.second.table.release();
+    for (auto& kv : ctx->commit_keys) { kv.second.basis.table.release(); kv.second.basis_exp_sigma.table.release(); }
     for (auto& kv : ctx->domains) kv.second.release();
     for (auto& w : ctx->ws) w.release();
     for (auto& s : ctx->stage) s.release();
@@ -445,6 +448,89 @@ extern "C" int g16_msm_resident_dev(g16_ctx* ctx, uint64_t handle, const void* s
             if (b.n) { msm_g1_enqueue(ctx->ws[0], (const Fr::T*)scalars_d, nullptr, b.table.as<G1::Aff>(), b.n, ctx->msm_c, ctx->msm_waves, ctx->stream, pl, nullptr, nullptr, pre_c);
                        G16_CUDA(cudaStreamSynchronize(ctx->stream)); }
             copy_out(out, b.n ? msm_g1_finish(ctx->ws[0], pl) : G1::aff_inf());
+        }
+    });
+}
+
+extern "C" int g16_msm_resident(g16_ctx* ctx, uint64_t handle, const void* scalars, void* out) {
+    // host-scalar form of g16_msm_resident_dev: one staged H2D copy, then the same path
+    if (!ctx) return 1;
+    uint64_t n = 0;
+    int rc = guarded(ctx, [&] {
+        auto it = ctx->bases.find(handle);
+        if (it == ctx->bases.end()) throw std::runtime_error("unknown bases handle");
+        n = it->second.n;
+        if (n && !scalars) throw std::runtime_error("null argument");
+        upload(ctx->stage[3], scalars, (size_t)n * 32, ctx->stream);
+    });
+    return rc ? rc : g16_msm_resident_dev(ctx, handle, ctx->stage[3].p, out);
+}
+
+// =================================================================== BSB22 commitment keys
+// pedersen.ProvingKey{Basis, BasisExpSigma} (setup.go:57,295-305) resident on the device.  g16_commit is what the
+// bsb22 hint (prove.go:94: CommitmentKeys[i].Commit) and the proof of knowledge (prove.go:124: ProveKnowledge)
+// become: both are MSMs of the same committed values, so one call uploads the values once and returns both points.
+extern "C" int g16_commitment_key_upload(g16_ctx* ctx, const void* basis, const void* basis_exp_sigma, uint64_t n,
+                                         uint64_t* key_handle) {
+    return guarded(ctx, [&] {
+        if (!key_handle || (n && (!basis || !basis_exp_sigma))) throw std::runtime_error("null argument");
+        g16_ctx::CommitKey k;
+        cudaStream_t st = ctx->stream;
+        k.basis.n = k.basis_exp_sigma.n = n;
+        try {
+            upload_bases<G1>(ctx, k.basis.table, basis, n, k.basis.pre_c, st);
+            upload_bases<G1>(ctx, k.basis_exp_sigma.table, basis_exp_sigma, n, k.basis_exp_sigma.pre_c, st);
+            G16_CUDA(cudaStreamSynchronize(st));
+        } catch (...) {
+            k.basis.table.release(); k.basis_exp_sigma.table.release();
+            throw;
+        }
+        uint64_t h = ctx->next_pk++;
+        ctx->commit_keys[h] = k;
+        *key_handle = h;
+    });
+}
+extern "C" int g16_commitment_key_free(g16_ctx* ctx, uint64_t key_handle) {
+    return guarded(ctx, [&] {
+        auto it = ctx->commit_keys.find(key_handle);
+        if (it == ctx->commit_keys.end()) throw std::runtime_error("unknown commitment-key handle");
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+        it->second.basis.table.release();
+        it->second.basis_exp_sigma.table.release();
+        ctx->commit_keys.erase(it);
+    });
+}
+extern "C" int g16_commit(g16_ctx* ctx, uint64_t key_handle, const void* values, uint64_t n_values,
+                          void* commitment_out, void* pok_out) {
+    return guarded(ctx, [&] {
+        auto it = ctx->commit_keys.find(key_handle);
+        if (it == ctx->commit_keys.end()) throw std::runtime_error("unknown commitment-key handle");
+        const g16_ctx::CommitKey& k = it->second;
+        // pedersen.Commit / ProveKnowledge: "must have as many values as basis elements"
+        if (n_values != k.basis.n) throw std::runtime_error("must have as many values as basis elements");
+        if (n_values && !values) throw std::runtime_error("null argument");
+        if (!commitment_out && !pok_out) throw std::runtime_error("no output requested");
+        void* outs[2] = {commitment_out, pok_out};
+        if (!n_values) {   // MultiExp over nothing: the point at infinity
+            for (void* o : outs) if (o) copy_out(o, G1::aff_inf());
+            return;
+        }
+        upload(ctx->stage[3], values, (size_t)n_values * 32, ctx->stream);
+        G16_CUDA(cudaEventRecord(ctx->ev[15], ctx->stream));
+        const g16_ctx::Bases* bs[2] = {&k.basis, &k.basis_exp_sigma};
+        cudaStream_t sts[2] = {ctx->stream, ctx->aux[0]};
+        MsmPlan pl[2];
+        for (int j = 0; j < 2; j++) {   // the two MSMs side by side: own workspace and stream each
+            if (!outs[j]) continue;
+            if (j) G16_CUDA(cudaStreamWaitEvent(sts[j], ctx->ev[15], 0));
+            const int pre_c = (ctx->msm_c == 0 && ctx->msm_precompute) ? bs[j]->pre_c : 0;
+            msm_g1_enqueue(ctx->ws[j], ctx->stage[3].as<Fr::T>(), nullptr, bs[j]->table.as<G1::Aff>(), n_values, ctx->msm_c,
+                           ctx->msm_waves, sts[j], pl[j], nullptr, nullptr, pre_c);
+        }
+        for (int j = 0; j < 2; j++) {
+            if (!outs[j]) continue;
+            G16_CUDA(cudaStreamSynchronize(sts[j]));
+            copy_out(outs[j], msm_g1_finish(ctx->ws[j], pl[j]));
         }
     });
 }

@@ -12,8 +12,8 @@ meaning follow the reference:
   backend.WithIcicleAcceleration()           backend/backend.go:142-147   -> WithIcicleAcceleration
 
 Differences that are deliberate: r, s can be injected (the reference hard-codes SetRandom at
-icicle.go:283-288, which makes byte-exact comparison impossible); BSB22 commitments are not supported
- and raise.
+icicle.go:283-288, which makes byte-exact comparison impossible); the BSB22 commitment MSMs (prove.go:94,124,
+which the reference leaves on the CPU) run on the device against resident commitment keys (bsb22.py).
 """
 import secrets
 from dataclasses import dataclass, field as _field
@@ -21,6 +21,7 @@ from dataclasses import dataclass, field as _field
 import numpy as np
 
 from . import lib as _lib
+from . import bsb22 as _bsb22
 
 HasIcicle = True
 _FR_MOD = {"bn254": 21888242871839275222246405745257275088548364400416034343698204186575808495617,
@@ -104,13 +105,19 @@ class ConstraintSystem:
 
 @dataclass
 class Proof:
-    """prove.go:44-49 (no commitments): raw gnark memory images."""
+    """prove.go:44-49: raw gnark memory images."""
     Ar: np.ndarray    # (8,)  G1Affine   ((12,) for BLS12-377)
     Bs: np.ndarray    # (16,) G2Affine   ((24,))
     Krs: np.ndarray   # (8,)  G1Affine
+    Commitments: list = _field(default_factory=list)    # []G1Affine, one per BSB22 commitment
+    CommitmentPok: np.ndarray = None                    # G1Affine, the folded proof of knowledge
 
     def raw(self):
-        return np.concatenate([self.Ar, self.Bs, self.Krs]).tobytes()
+        """Ar || Bs || Krs || Commitments... || CommitmentPok (the last two only when there are commitments)."""
+        parts = [self.Ar, self.Bs, self.Krs] + list(self.Commitments)
+        if self.Commitments:
+            parts.append(self.CommitmentPok)
+        return np.concatenate(parts).tobytes()
 
 
 @dataclass
@@ -131,9 +138,11 @@ class ProvingKey:
     infinity_b: np.ndarray
     nb_wires: int
     nb_public: int
-    commitment_keys: list = _field(default_factory=list)
+    commitment_keys: list = _field(default_factory=list)   # []bsb22.CommitmentKey (pedersen.ProvingKey, setup.go:57)
     device: object = None     # deviceInfo (provingkey.go:10-23): (Context, handle)
     curve: str = "bn254"      # "bls12_377": 12/24-limb points, the g16_bls12_377_* entry points (config 5)
+    k_index: np.ndarray = None           # wire feeding each K base; None = W[nb_wires - len(g1_k):] (no commitments)
+    commitment_device: object = None     # (Context, [commitment-key handles])
 
     def setup_device_pointers(self, cfg=None):
         """icicle.go:31-130: one-time upload; lazily on first Prove (icicle.go:145-150)."""
@@ -142,7 +151,7 @@ class ProvingKey:
         cfg = cfg or ProverConfig()
         ctx = _lib.Context(cfg.device, curve=self.curve)
         handle = ctx.pk_upload(self.domain_n, self.g1_a, self.g1_b, self.g1_k, self.g1_z, self.g2_b,
-                               self.infinity_a, self.infinity_b, self.nb_wires,
+                               self.infinity_a, self.infinity_b, self.nb_wires, k_index=self.k_index,
                                shard_index=cfg.shard_index, shard_count=cfg.shard_count)
         self.device = (ctx, handle)
 
@@ -153,6 +162,10 @@ class ProvingKey:
     def free_device(self):
         if self.device is not None:
             ctx, handle = self.device
+            if self.commitment_device is not None:
+                for h in self.commitment_device[1]:
+                    ctx.commitment_key_free(h)
+                self.commitment_device = None
             ctx.pk_free(handle)
             ctx.close()
             self.device = None
@@ -183,6 +196,10 @@ def Prove(r1cs, pk, full_witness, *opts):
     ``r1cs`` must offer ``solve(full_witness) -> R1CSSolution`` (constraint/bn254/system.go:65; the solver
     is host code outside the accelerated path) -- or pass ``r1cs=None`` and an R1CSSolution as the witness, or a
     ``ConstraintSystem`` and the solved wire vector (a, b, c are then computed on the device).
+    A constraint system with BSB22 commitments additionally carries ``commitment_info`` (a list of
+    bsb22.Groth16Commitment, = r1cs.CommitmentInfo) and ``nb_public``, and its ``solve(full_witness, bsb22_hint)``
+    calls ``bsb22_hint(i, hashed_values, committed_values) -> int`` where gnark's solver would call the overridden
+    Bsb22CommitmentComputePlaceholder hint (prove.go:81-109).
     Without WithIcicleAcceleration() the reference falls back to the CPU prover (icicle.go:141-143); this
     package has no CPU prover, so that is an error here.
     """
@@ -190,8 +207,9 @@ def Prove(r1cs, pk, full_witness, *opts):
     if cfg.accelerator != "icicle":
         raise _lib.G16Error("accelerator option missing: pass WithIcicleAcceleration() "
                             "(the CPU prover lives in gnark, not in this package)")
-    if pk.commitment_keys:
-        raise NotImplementedError("BSB22 commitments are outside this round's scope (SURVEY.md 8(f) N3)")
+    info = list(getattr(r1cs, "commitment_info", None) or [])
+    if info or pk.commitment_keys:
+        return _prove_with_commitments(r1cs, pk, full_witness, info, cfg)
     if isinstance(r1cs, ConstraintSystem):
         # the wire vector is the whole witness-side input: the device evaluates the constraint matrices
         points, stats = prove_msms_wires(pk, r1cs, full_witness, cfg)
@@ -203,6 +221,41 @@ def Prove(r1cs, pk, full_witness, *opts):
     proof = assemble(pk, points, r, s)
     proof.stats = stats
     return proof
+
+
+def _prove_with_commitments(r1cs, pk, full_witness, info, cfg):
+    """Prove for a circuit that uses api.Commit: prove.go:74-139 around the usual device section."""
+    if r1cs is None or isinstance(r1cs, ConstraintSystem) or not hasattr(r1cs, "solve"):
+        raise _lib.G16Error("a constraint system with commitments must be solved inside Prove: the bsb22 hint "
+                            "computes the commitments (prove.go:81-109); pass an r1cs with solve(witness, bsb22_hint)")
+    if pk.k_index is None:
+        # wires that reach the K MSM (prove.go:241-246); fixed per circuit, so it becomes part of the resident key
+        if pk.device is not None:
+            raise _lib.G16Error("proving key was uploaded before its commitment info was known; free_device() first")
+        pk.k_index = _bsb22.k_wire_indices(r1cs.nb_public, pk.nb_wires, info)
+        if len(pk.k_index) != len(pk.g1_k):
+            raise _lib.G16Error(f"commitment info leaves {len(pk.k_index)} private wires, pk.G1.K has {len(pk.g1_k)}")
+    pk.setup_device_pointers(cfg)
+    ctx, handle = pk.device
+    session = _bsb22.Session(pk, info, ctx)
+    sol = r1cs.solve(full_witness, session.hint)
+    points, stats = ctx.prove(handle, sol.W, sol.A, sol.B, sol.C)
+    commitment_values = [_fr_from_limbs(sol.W[c.commitment_index], pk.curve) for c in info]
+    commitments, pok = session.finish(commitment_values)
+    r = cfg.r if cfg.r is not None else _random_fr(pk.curve)
+    s = cfg.s if cfg.s is not None else _random_fr(pk.curve)
+    proof = assemble(pk, points, r, s)
+    proof.Commitments, proof.CommitmentPok = commitments, pok
+    proof.stats = stats
+    return proof
+
+
+def _fr_from_limbs(limbs, curve):
+    m = _FR_MOD[curve]
+    v = 0
+    for i, w in enumerate(np.asarray(limbs, dtype=np.uint64).reshape(-1)):
+        v |= int(w) << (64 * i)
+    return v * pow(1 << 256, -1, m) % m
 
 
 def assemble(pk, msm_points, r, s):

@@ -73,7 +73,8 @@ SYMBOLS = [
     "g16_ctx_create", "g16_ctx_destroy", "g16_last_error", "g16_ctx_set", "g16_kernel_launch_count",
     "g16_pk_upload", "g16_pk_free", "g16_prove_bn254", "g16_prove_bn254_dev", "g16_assemble_proof_bn254",
     "g16_r1cs_upload", "g16_r1cs_free", "g16_r1cs_eval_dev", "g16_prove_bn254_wires",
-    "g16_bases_upload", "g16_bases_free", "g16_msm_resident_dev",
+    "g16_bases_upload", "g16_bases_free", "g16_msm_resident_dev", "g16_msm_resident",
+    "g16_commitment_key_upload", "g16_commitment_key_free", "g16_commit",
     "g16_msm_g1", "g16_msm_g1_dev", "g16_msm_g2", "g16_msm_g2_dev", "g16_ntt", "g16_ntt_dev",
     "g16_compute_h", "g16_compute_h_dev", "g16_fr_mul_vec",
     "g16_dist_ntt_stages_dev", "g16_dist_permute_dev", "g16_dist_pointwise_h_dev", "g16_prove_msms_dev",
@@ -301,6 +302,35 @@ class Context:
         out = np.zeros(self.g2w if g2 else self.g1w, dtype=np.uint64)
         self._check(self._lib.g16_msm_resident_dev(self._h, u64(handle), _ptr(scalars_ptr), _ptr(out)), "g16_msm_resident_dev")
         return out
+
+    def msm_resident(self, handle, scalars, g2=False):
+        s = _arr(scalars, 4) if len(scalars) else np.zeros((0, 4), dtype=np.uint64)
+        out = np.zeros(self.g2w if g2 else self.g1w, dtype=np.uint64)
+        self._check(self._lib.g16_msm_resident(self._h, u64(handle), _ptr(s), _ptr(out)), "g16_msm_resident")
+        return out
+
+    # ---- BSB22 commitment keys
+    def commitment_key_upload(self, basis, basis_exp_sigma):
+        empty = np.zeros((0, self.g1w), dtype=np.uint64)
+        b = _arr(basis, self.g1w) if len(basis) else empty
+        e = _arr(basis_exp_sigma, self.g1w) if len(basis_exp_sigma) else empty
+        if len(b) != len(e):
+            raise G16Error("commitment key: Basis and BasisExpSigma differ in length")
+        h = u64(0)
+        self._check(self._lib.g16_commitment_key_upload(self._h, _ptr(b), _ptr(e), u64(len(b)), ctypes.byref(h)),
+                    "g16_commitment_key_upload")
+        return h.value
+
+    def commitment_key_free(self, handle):
+        self._check(self._lib.g16_commitment_key_free(self._h, u64(handle)), "g16_commitment_key_free")
+
+    def commit(self, handle, values, want_pok=True):
+        """(commitment, pok) = (sum v_j Basis_j, sum v_j BasisExpSigma_j); pok is None unless want_pok."""
+        v = _arr(values, 4) if len(values) else np.zeros((0, 4), dtype=np.uint64)
+        cm = np.zeros(self.g1w, dtype=np.uint64)
+        pok = np.zeros(self.g1w, dtype=np.uint64) if want_pok else None
+        self._check(self._lib.g16_commit(self._h, u64(handle), _ptr(v), u64(len(v)), _ptr(cm), _ptr(pok)), "g16_commit")
+        return cm, pok
 
     # ---- constraint matrices on the device (SURVEY.md 8(f) N1)
     def r1cs_upload(self, n_constraints, n_wires, coeffs, matrices):

@@ -142,6 +142,20 @@ int g16_msm_g1_dev(g16_ctx* ctx, const void* scalars_d, const void* bases_d, uin
 int g16_bases_upload(g16_ctx* ctx, const void* bases, uint64_t n, int g2, int from_device, uint64_t* bases_handle);
 int g16_bases_free(g16_ctx* ctx, uint64_t bases_handle);
 int g16_msm_resident_dev(g16_ctx* ctx, uint64_t bases_handle, const void* scalars_d, void* out_affine);
+int g16_msm_resident(g16_ctx* ctx, uint64_t bases_handle, const void* scalars, void* out_affine);   /* host scalars */
+/* BSB22 commitment keys: pedersen.ProvingKey{Basis, BasisExpSigma} (setup.go:57,295-305; dump
+ * layout marshal.go:447-452) resident on the device, n G1 affine points each ((0,0) = infinity is legal).
+ * g16_commit replaces pk.CommitmentKeys[i].Commit(values) inside the bsb22 solver hint (prove.go:94; icicle.go keeps
+ * the CPU call) and pk.CommitmentKeys[i].ProveKnowledge(values) (prove.go:124): commitment_out = sum values_j Basis_j,
+ * pok_out = sum values_j BasisExpSigma_j, both Montgomery affine; either may be NULL.  values: n_values Fr,
+ * Montgomery, host memory; n_values must equal the key's length ("must have as many values as basis elements").
+ * An empty key yields the point at infinity.  Hashing the commitment to the wire value and folding the proofs of
+ * knowledge (prove.go:97-108,125-135) are O(#commitments) host work and stay with the caller. */
+int g16_commitment_key_upload(g16_ctx* ctx, const void* basis, const void* basis_exp_sigma, uint64_t n,
+                              uint64_t* key_handle);
+int g16_commitment_key_free(g16_ctx* ctx, uint64_t key_handle);
+int g16_commit(g16_ctx* ctx, uint64_t key_handle, const void* values, uint64_t n_values, void* commitment_out,
+               void* pok_out);
 /* replaces iciclegnark.MsmG2OnDevice (icicle.go:382) / curve.G2Jac.MultiExp (prove.go:293) */
 int g16_msm_g2(g16_ctx* ctx, const void* scalars, const void* bases, uint64_t n, void* out_affine);
 int g16_msm_g2_dev(g16_ctx* ctx, const void* scalars_d, const void* bases_d, uint64_t n, void* out_affine);

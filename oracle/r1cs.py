@@ -16,6 +16,7 @@ class R1CS:
         self.nb_secret = nb_secret
         self.nb_internal = 0
         self.constraints = []
+        self.commitment_info = []      # constraint.Groth16Commitments (oracle.commitment.Groth16Commitment)
 
     @property
     def nb_wires(self):
@@ -110,3 +111,69 @@ def mimc_chain_witness(cs, x0, k):
         (cf, o), = O
         w[o] = dot(L) * dot(Rr) % R
     return w
+
+
+def committed_chain(nb_constraints, rng, nb_commitments=1, nb_private_committed=5):
+    """MiMC-shaped chain with BSB22 commitments (the shape api.Commit gives a circuit: constraint/commitment.go:9-14,
+    backend/groth16/bn254/commitment_test.go:33-49,129-149).  Wires: 0=ONE 1=OUT 2=P (public) 3=X0 4=K (secret).
+    The chain runs in nb_commitments + 1 phases; after phase j a commitment wire cm_j (an internal wire no
+    constraint defines -- the bsb22 hint does) is created and added to the round key of the later phases.
+    Commitment 0 commits to P (public), X0, K and up to nb_private_committed internal wires of phase 0;
+    commitment j > 0 commits to P (public), cm_{j-1} (a commitment wire, exercising the index translation
+    of GetPublicAndCommitmentCommitted) and internal wires of phase j.  The last commitment of an odd count > 2
+    commits to nothing privately (empty basis).  Returns the R1CS."""
+    from .commitment import Groth16Commitment
+    cs = R1CS(nb_public=3, nb_secret=2)
+    phases = nb_commitments + 1
+    per_phase = max(1, (nb_constraints - 1) // (3 * phases))
+    x = [(1, 3)]
+    key = [(1, 4)]
+    prev_cm = None
+    for ph in range(phases):
+        internals = []
+        for _ in range(per_phase):
+            if cs.nb_constraints + 3 > nb_constraints - 1:
+                break
+            ci = rng.field(R)
+            t = x + key + [(ci, 0)]
+            u = cs.new_internal()
+            cs.add(t, t, [(1, u)])
+            v = cs.new_internal()
+            cs.add([(1, u)], [(1, u)], [(1, v)])
+            nx = cs.new_internal()
+            cs.add([(1, v)], t, [(1, nx)])
+            internals += [u, v, nx]
+            x = [(1, nx)]
+        if ph < nb_commitments:
+            if ph == 0:
+                pub, priv = [2], [3, 4] + internals[:nb_private_committed]
+                nb_pub_committed = 1
+            else:
+                pub, priv = [2, prev_cm], internals[1:1 + nb_private_committed]
+                nb_pub_committed = 1
+                if nb_commitments > 2 and ph == nb_commitments - 1 and nb_commitments % 2 == 1:
+                    priv = []
+            cm = cs.new_internal()
+            cs.commitment_info.append(Groth16Commitment(pub, sorted(priv), cm, nb_pub_committed))
+            key = key + [(1, cm)]
+            prev_cm = cm
+    while cs.nb_constraints < nb_constraints - 1:
+        nx = cs.new_internal()
+        cs.add(x + key[1:], x, [(1, nx)])
+        x = [(1, nx)]
+    cs.add(x + key, [(1, 0)], [(1, 1)])
+    return cs
+
+
+def committed_chain_assignment(cs, pk, p, x0, k, solve):
+    """input wires [ONE, OUT, P, X0, K]: OUT is what the chain evaluates to, found by solving everything but the
+    final assertion once (no commitment hashes OUT, so there is no circularity)."""
+    probe = [1, 0, p % R, x0 % R, k % R]
+    saved = cs.constraints
+    cs.constraints = saved[:-1]
+    try:
+        w, _, _ = solve(cs, pk, probe)
+    finally:
+        cs.constraints = saved
+    out = sum(cf * w[j] for cf, j in saved[-1][0]) % R
+    return [1, out, p % R, x0 % R, k % R]
