@@ -4,6 +4,7 @@
   lib.py       ctypes binding of libg16b200.so (stand-in for the cgo layer)
   groth16.py   mirror of package icicle_bn254 (Prove, ProvingKey, WithIcicleAcceleration)
   bsb22.py     BSB22 commitments on that path (hint override, commitment keys on the device, folded PoK)
+  dump.py      ProvingKey.WriteDump / ReadDump and the direct file -> device key load
 
 The directory ``gnark-icicle_b200`` at the repo root is a link to this package (a hyphen is not importable).
 """
@@ -11,7 +12,8 @@ from . import lib, bsb22
 from .groth16 import (HasIcicle, Prove, ProvingKey, Proof, R1CSSolution, WithIcicleAcceleration, WithRandomness,
                       WithDevice, NewProverConfig, prove_msms, assemble, combine_shards, ConstraintSystem,
                       prove_msms_wires)
+from . import dump
 
-__all__ = ["lib", "bsb22", "HasIcicle", "Prove", "ProvingKey", "Proof", "R1CSSolution", "WithIcicleAcceleration",
+__all__ = ["lib", "bsb22", "dump", "HasIcicle", "Prove", "ProvingKey", "Proof", "R1CSSolution", "WithIcicleAcceleration",
            "WithRandomness", "WithDevice", "NewProverConfig", "prove_msms", "assemble", "combine_shards",
            "ConstraintSystem", "prove_msms_wires"]

@@ -6,6 +6,7 @@
 #include <chrono>
 #include <cstdlib>
 #include <memory>
+#include <unistd.h>
 
 #include "curve_select.h"
 #include "../../include/g16b200.h"
@@ -55,6 +56,7 @@ struct g16_ctx {
     uint64_t next_pk = 1;
     MsmWorkspace ws[5];
     DevBuf stage[4];             // host-pointer variants: staged inputs
+    PinnedBuf file_stage[2];     // g16_pk_upload_from_file: double-buffered pread -> H2D
     DevBuf fb_table_g1, fb_table_g2;
     int msm_c = 0, msm_waves = 4;
     int msm_precompute = 1;      // keep 2^(c j) multiples of every key base resident (one shared bucket set, larger windows)
@@ -101,8 +103,46 @@ void upload(DevBuf& dst, const void* src, size_t bytes, cudaStream_t st) {
 // large enough to pay for it, also holds the 2^(c j) multiples used by the shared-bucket MSM (msm.cuh, precomputed
 // mode).  pre_c = window bits of the table, 0 = bases only.
 constexpr uint64_t PRECOMPUTE_MIN_POINTS = 1 << 14;
+// Where key material comes from: host memory, or a byte range of a file (a ProvingKey.WriteDump image, whose point
+// slices are raw memory = the device format; marshal.go:386-456).
+struct Src {
+    const char* host = nullptr;
+    int fd = -1;
+    uint64_t off = 0;
+    Src at(uint64_t bytes) const { Src s = *this; if (host) s.host += bytes; s.off += bytes; return s; }
+};
+Src host_src(const void* p) { Src s; s.host = (const char*)p; return s; }
+
+// file -> HBM without an intermediate pageable copy: pread into two pinned staging buffers, the H2D copy of one
+// chunk in flight while the next is being read
+constexpr size_t FILE_CHUNK = (size_t)32 << 20;
+void copy_in(g16_ctx* ctx, void* dst, const Src& src, size_t bytes, cudaStream_t st) {
+    if (!bytes) return;
+    if (src.fd < 0) { G16_CUDA(cudaMemcpyAsync(dst, src.host, bytes, cudaMemcpyHostToDevice, st)); return; }
+    cudaEvent_t* done = &ctx->ev[28];   // ev[28], ev[29]: staging buffer free again
+    for (int b = 0; b < 2; b++) ctx->file_stage[b].reserve(FILE_CHUNK);
+    size_t pos = 0;
+    for (int it = 0; pos < bytes; it++) {
+        const int b = it & 1;
+        const size_t len = bytes - pos < FILE_CHUNK ? bytes - pos : FILE_CHUNK;
+        if (it >= 2) G16_CUDA(cudaEventSynchronize(done[b]));
+        char* buf = ctx->file_stage[b].as<char>();
+        size_t got = 0;
+        while (got < len) {
+            ssize_t r = pread(src.fd, buf + got, len - got, (off_t)(src.off + pos + got));
+            if (r < 0) throw std::runtime_error("pread failed while loading the key dump");
+            if (r == 0) throw std::runtime_error("key dump is shorter than its slice headers say");
+            got += (size_t)r;
+        }
+        G16_CUDA(cudaMemcpyAsync((char*)dst + pos, buf, len, cudaMemcpyHostToDevice, st));
+        G16_CUDA(cudaEventRecord(done[b], st));
+        pos += len;
+    }
+    G16_CUDA(cudaStreamSynchronize(st));   // the staging buffers are reused by the next array
+}
+
 template <class C>
-void upload_bases(g16_ctx* ctx, DevBuf& dst, const void* src, uint64_t n, int& pre_c, cudaStream_t st) {
+void upload_bases(g16_ctx* ctx, DevBuf& dst, const Src& src, uint64_t n, int& pre_c, cudaStream_t st) {
     constexpr bool IS_G2 = sizeof(typename C::E) > sizeof(Fp::T);
     const size_t row = (size_t)n * sizeof(typename C::Aff);
     pre_c = 0;
@@ -114,11 +154,15 @@ void upload_bases(g16_ctx* ctx, DevBuf& dst, const void* src, uint64_t n, int& p
         if (total <= free_b / 2) pre_c = c;
     }
     dst.reserve(pre_c ? row * (size_t)(255 / pre_c + 1) : (row ? row : 16));
-    if (row) G16_CUDA(cudaMemcpyAsync(dst.p, src, row, cudaMemcpyHostToDevice, st));
+    copy_in(ctx, dst.p, src, row, st);
     if (pre_c) {
         if constexpr (IS_G2) msm_g2_precompute(dst.as<G2::Aff>(), n, pre_c, st);
         else msm_g1_precompute(dst.as<G1::Aff>(), n, pre_c, st);
     }
+}
+template <class C>
+void upload_bases(g16_ctx* ctx, DevBuf& dst, const void* src, uint64_t n, int& pre_c, cudaStream_t st) {
+    upload_bases<C>(ctx, dst, host_src(src), n, pre_c, st);
 }
 
 }  // namespace
@@ -166,6 +210,7 @@ void g16_ctx_destroy(g16_ctx* ctx) {
     for (auto& kv : ctx->domains) kv.second.release();
     for (auto& w : ctx->ws) w.release();
     for (auto& s : ctx->stage) s.release();
+    for (auto& s : ctx->file_stage) s.release();
     ctx->fb_table_g1.release(); ctx->fb_table_g2.release();
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
     for (auto& a : ctx->aux) if (a) cudaStreamDestroy(a);
@@ -193,7 +238,9 @@ void* g16_ctx_stream(g16_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; 
 }  // extern "C"
 
 // =================================================================== proving key
-extern "C" int g16_pk_upload(g16_ctx* ctx, const g16_pk_desc* d, uint64_t* pk_handle) {
+namespace {
+// src: G1.A, G1.B, G1.K, G1.Z, G2.B
+int pk_upload_impl(g16_ctx* ctx, const g16_pk_desc* d, const Src* src, uint64_t* pk_handle) {
     return guarded(ctx, [&] {
         if (!d || !pk_handle) throw std::runtime_error("null argument");
         if (!is_pow2(d->domain_n)) throw std::runtime_error("domain_n must be a power of two");
@@ -226,16 +273,16 @@ extern "C" int g16_pk_upload(g16_ctx* ctx, const g16_pk_desc* d, uint64_t* pk_ha
         uint64_t lo, hi;
         slice(d->n_a, si, sc, lo, hi);
         pk.n_a = hi - lo;
-        upload_bases<G1>(ctx, pk.g1_a, (const char*)d->g1_a + lo * G1SZ, pk.n_a, pk.pre_c[G16_OUT_AR], st);
+        upload_bases<G1>(ctx, pk.g1_a, src[0].at(lo * G1SZ), pk.n_a, pk.pre_c[G16_OUT_AR], st);
         upload(pk.map_a, ma.data() + lo, pk.n_a * 4, st);
         slice(d->n_b, si, sc, lo, hi);
         pk.n_b = pk.n_b2 = hi - lo;
-        upload_bases<G1>(ctx, pk.g1_b, (const char*)d->g1_b + lo * G1SZ, pk.n_b, pk.pre_c[G16_OUT_BS1], st);
-        upload_bases<G2>(ctx, pk.g2_b, (const char*)d->g2_b + lo * G2SZ, pk.n_b, pk.pre_c[G16_OUT_BS2], st);
+        upload_bases<G1>(ctx, pk.g1_b, src[1].at(lo * G1SZ), pk.n_b, pk.pre_c[G16_OUT_BS1], st);
+        upload_bases<G2>(ctx, pk.g2_b, src[4].at(lo * G2SZ), pk.n_b, pk.pre_c[G16_OUT_BS2], st);
         upload(pk.map_b, mb.data() + lo, pk.n_b * 4, st);
         slice(d->n_k, si, sc, lo, hi);
         pk.n_k = hi - lo;
-        upload_bases<G1>(ctx, pk.g1_k, (const char*)d->g1_k + lo * G1SZ, pk.n_k, pk.pre_c[G16_OUT_KRS_K], st);
+        upload_bases<G1>(ctx, pk.g1_k, src[2].at(lo * G1SZ), pk.n_k, pk.pre_c[G16_OUT_KRS_K], st);
         upload(pk.map_k, mk.data() + lo, pk.n_k * 4, st);
         uint64_t nz = d->n_z < d->domain_n ? d->n_z : d->domain_n - 1;   // h[:n-1] (prove.go:235-237)
         // Z follows the block distribution of h over the domain (so a distributed computeH leaves each rank's
@@ -245,7 +292,7 @@ extern "C" int g16_pk_upload(g16_ctx* ctx, const g16_pk_desc* d, uint64_t* pk_ha
         if (hi > nz) hi = nz;
         pk.n_z = hi - lo;
         pk.z_off = lo;
-        upload_bases<G1>(ctx, pk.g1_z, (const char*)d->g1_z + lo * G1SZ, pk.n_z, pk.pre_c[G16_OUT_KRS_HZ], st);
+        upload_bases<G1>(ctx, pk.g1_z, src[3].at(lo * G1SZ), pk.n_z, pk.pre_c[G16_OUT_KRS_HZ], st);
 
         // twiddles of the domain (replaces icicle.go:44-75)
         NttDomain& dom = ctx->domain(pk.logn);
@@ -257,6 +304,25 @@ extern "C" int g16_pk_upload(g16_ctx* ctx, const g16_pk_desc* d, uint64_t* pk_ha
         ctx->pks[h] = pk;
         *pk_handle = h;
     });
+}
+}  // namespace
+
+extern "C" int g16_pk_upload(g16_ctx* ctx, const g16_pk_desc* d, uint64_t* pk_handle) {
+    if (!ctx) return 1;
+    if (!d) { ctx->err = "null argument"; return 2; }
+    const Src src[5] = {host_src(d->g1_a), host_src(d->g1_b), host_src(d->g1_k), host_src(d->g1_z), host_src(d->g2_b)};
+    return pk_upload_impl(ctx, d, src, pk_handle);
+}
+
+// the point slices of a ProvingKey.WriteDump image (marshal.go:386-456) are raw memory, i.e.
+// already the device format; they go file -> pinned staging -> HBM (sharded: only this shard's byte ranges are read).
+extern "C" int g16_pk_upload_from_file(g16_ctx* ctx, const g16_pk_file_desc* f, uint64_t* pk_handle) {
+    if (!ctx) return 1;
+    if (!f || f->fd < 0) { ctx->err = "null argument / bad file descriptor"; return 2; }
+    Src src[5];
+    const uint64_t off[5] = {f->off_g1_a, f->off_g1_b, f->off_g1_k, f->off_g1_z, f->off_g2_b};
+    for (int i = 0; i < 5; i++) { src[i].fd = f->fd; src[i].off = off[i]; }
+    return pk_upload_impl(ctx, &f->key, src, pk_handle);
 }
 
 extern "C" int g16_pk_free(g16_ctx* ctx, uint64_t pk_handle) {

@@ -60,6 +60,14 @@ class PkDesc(ctypes.Structure):
     ]
 
 
+class PkFileDesc(ctypes.Structure):
+    _fields_ = [
+        ("key", PkDesc), ("fd", ctypes.c_int),
+        ("off_g1_a", ctypes.c_uint64), ("off_g1_b", ctypes.c_uint64), ("off_g1_k", ctypes.c_uint64),
+        ("off_g1_z", ctypes.c_uint64), ("off_g2_b", ctypes.c_uint64),
+    ]
+
+
 class R1csDesc(ctypes.Structure):
     _fields_ = [
         ("n_constraints", ctypes.c_uint64), ("n_wires", ctypes.c_uint64),
@@ -71,7 +79,7 @@ class R1csDesc(ctypes.Structure):
 # every symbol include/g16b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "g16_ctx_create", "g16_ctx_destroy", "g16_last_error", "g16_ctx_set", "g16_kernel_launch_count",
-    "g16_pk_upload", "g16_pk_free", "g16_prove_bn254", "g16_prove_bn254_dev", "g16_assemble_proof_bn254",
+    "g16_pk_upload", "g16_pk_upload_from_file", "g16_pk_free", "g16_prove_bn254", "g16_prove_bn254_dev", "g16_assemble_proof_bn254",
     "g16_r1cs_upload", "g16_r1cs_free", "g16_r1cs_eval_dev", "g16_prove_bn254_wires",
     "g16_bases_upload", "g16_bases_free", "g16_msm_resident_dev", "g16_msm_resident",
     "g16_commitment_key_upload", "g16_commitment_key_free", "g16_commit",
@@ -262,6 +270,21 @@ class Context:
                    _ptr(g2_b), len(g2_b), _ptr(ia), _ptr(ib), n_wires, _ptr(ki), shard_index, shard_count)
         h = u64(0)
         self._check(self._lib.g16_pk_upload(self._h, ctypes.byref(d), ctypes.byref(h)), "g16_pk_upload")
+        return h.value
+
+    def pk_upload_from_file(self, fd, domain_n, spans, infinity_a, infinity_b, n_wires, k_index=None,
+                            shard_index=0, shard_count=1):
+        """spans: {"g1_a": (byte offset, count), "g1_b", "g1_k", "g1_z", "g2_b"} inside the open file `fd`
+        (a ProvingKey.WriteDump image); the points never pass through host arrays of the caller."""
+        ia = np.ascontiguousarray(infinity_a, dtype=np.uint8)
+        ib = np.ascontiguousarray(infinity_b, dtype=np.uint8)
+        ki = None if k_index is None else np.ascontiguousarray(k_index, dtype=np.uint32)
+        null = ctypes.c_void_p(0)
+        key = PkDesc(domain_n, null, spans["g1_a"][1], null, spans["g1_b"][1], null, spans["g1_k"][1], null, spans["g1_z"][1],
+                     null, spans["g2_b"][1], _ptr(ia), _ptr(ib), n_wires, _ptr(ki), shard_index, shard_count)
+        d = PkFileDesc(key, fd, spans["g1_a"][0], spans["g1_b"][0], spans["g1_k"][0], spans["g1_z"][0], spans["g2_b"][0])
+        h = u64(0)
+        self._check(self._lib.g16_pk_upload_from_file(self._h, ctypes.byref(d), ctypes.byref(h)), "g16_pk_upload_from_file")
         return h.value
 
     def pk_free(self, handle):

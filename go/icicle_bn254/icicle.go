@@ -22,8 +22,12 @@ import (
 	"github.com/consensys/gnark/backend"
 	groth16_bn254 "github.com/consensys/gnark/backend/groth16/bn254"
 	"github.com/consensys/gnark/backend/witness"
+	"github.com/consensys/gnark-crypto/ecc"
+	"github.com/consensys/gnark-crypto/ecc/bn254/fr/hash_to_field"
 	"github.com/consensys/gnark/constraint"
 	cs "github.com/consensys/gnark/constraint/bn254"
+	"github.com/consensys/gnark/constraint/solver"
+	fcs "github.com/consensys/gnark/frontend/cs"
 	"github.com/consensys/gnark/logger"
 )
 
@@ -56,9 +60,33 @@ func ptrOf[T any](s []T) unsafe.Pointer {
 // setupDevicePointers uploads the key once.  gnark-crypto elements are already the memory image the library
 // expects (little-endian Montgomery limbs), so slices are handed over as they are -- no conversion, no
 // stripping of infinity points.
-func (pk *ProvingKey) setupDevicePointers() error {
+//
+// commitmentInfo decides which wires reach the K MSM (prove.go:241-246): W[nbPublic:] without the privately committed
+// wires and the commitment wires.  The reference filters the wire vector on the host for every proof (filterHeap);
+// here the surviving wire indices become part of the resident key (k_index) and the device gathers.
+func (pk *ProvingKey) setupDevicePointers(nbPublic int, commitmentInfo constraint.Groth16Commitments) error {
 	if pk.deviceInfo != nil {
 		return nil
+	}
+	var kIndex []uint32
+	if len(commitmentInfo) != 0 {
+		nbWires := len(pk.InfinityA)
+		removed := make([]bool, nbWires)
+		for _, c := range commitmentInfo {
+			for _, w := range c.PrivateCommitted {
+				removed[w] = true
+			}
+			removed[c.CommitmentIndex] = true
+		}
+		kIndex = make([]uint32, 0, len(pk.G1.K))
+		for w := nbPublic; w < nbWires; w++ {
+			if !removed[w] {
+				kIndex = append(kIndex, uint32(w))
+			}
+		}
+		if len(kIndex) != len(pk.G1.K) {
+			return fmt.Errorf("commitment info leaves %d private wires, pk.G1.K has %d", len(kIndex), len(pk.G1.K))
+		}
 	}
 	var ctx ctxHandle
 	dev := C.int(0)
@@ -68,7 +96,7 @@ func (pk *ProvingKey) setupDevicePointers() error {
 	infA, infB := boolBytes(pk.InfinityA), boolBytes(pk.InfinityB)
 	var pin runtime.Pinner
 	defer pin.Unpin()
-	for _, p := range []unsafe.Pointer{ptrOf(pk.G1.A), ptrOf(pk.G1.B), ptrOf(pk.G1.K), ptrOf(pk.G1.Z), ptrOf(pk.G2.B), ptrOf(infA), ptrOf(infB)} {
+	for _, p := range []unsafe.Pointer{ptrOf(pk.G1.A), ptrOf(pk.G1.B), ptrOf(pk.G1.K), ptrOf(pk.G1.Z), ptrOf(pk.G2.B), ptrOf(infA), ptrOf(infB), ptrOf(kIndex)} {
 		if p != nil {
 			pin.Pin(p)
 		}
@@ -82,6 +110,7 @@ func (pk *ProvingKey) setupDevicePointers() error {
 	d.g2_b, d.n_b2 = ptrOf(pk.G2.B), C.uint64_t(len(pk.G2.B))
 	d.infinity_a, d.infinity_b = (*C.uint8_t)(ptrOf(infA)), (*C.uint8_t)(ptrOf(infB))
 	d.n_wires = C.uint64_t(len(pk.InfinityA))
+	d.k_index = (*C.uint32_t)(ptrOf(kIndex))
 	d.shard_count = 1
 	var h C.uint64_t
 	if rc := C.g16_pk_upload(ctx, &d, &h); rc != 0 {
@@ -90,6 +119,19 @@ func (pk *ProvingKey) setupDevicePointers() error {
 		return err
 	}
 	pk.deviceInfo = &deviceInfo{ctx: ctx, handle: uint64(h)}
+	return pk.uploadCommitmentKeys()
+}
+
+// BSB22 commitment keys (pedersen.ProvingKey{Basis, BasisExpSigma}) stay resident next to the key.
+func (pk *ProvingKey) uploadCommitmentKeys() error {
+	for i := range pk.CommitmentKeys {
+		ck := &pk.CommitmentKeys[i]
+		var kh C.uint64_t
+		if rc := C.g16_commitment_key_upload(pk.ctx, ptrOf(ck.Basis), ptrOf(ck.BasisExpSigma), C.uint64_t(len(ck.Basis)), &kh); rc != 0 {
+			return lastError(pk.ctx, "g16_commitment_key_upload")
+		}
+		pk.commitKeys = append(pk.commitKeys, uint64(kh))
+	}
 	return nil
 }
 
@@ -104,19 +146,73 @@ func Prove(r1cs *cs.R1CS, pk *ProvingKey, fullWitness witness.Witness, opts ...b
 		return groth16_bn254.Prove(r1cs, &pk.ProvingKey, fullWitness, opts...)
 	}
 	log := logger.Logger().With().Str("curve", r1cs.CurveID().String()).Str("acceleration", "g16b200").Int("nbConstraints", r1cs.GetNbConstraints()).Str("backend", "groth16").Logger()
-	if len(r1cs.CommitmentInfo.(constraint.Groth16Commitments)) != 0 {
-		// BSB22 commitments are handled by the CPU prover until the commitment MSMs move behind the ABI.
-		return groth16_bn254.Prove(r1cs, &pk.ProvingKey, fullWitness, opts...)
+	if opt.HashToFieldFn == nil {
+		opt.HashToFieldFn = hash_to_field.New([]byte(constraint.CommitmentDst))
 	}
-	if err := pk.setupDevicePointers(); err != nil {
+	commitmentInfo := r1cs.CommitmentInfo.(constraint.Groth16Commitments)
+	if err := pk.setupDevicePointers(r1cs.GetNbPublicVariables(), commitmentInfo); err != nil {
 		return nil, err
 	}
-	_solution, err := r1cs.Solve(fullWitness, opt.SolverOpts...)
+	proof := &groth16_bn254.Proof{Commitments: make([]curve.G1Affine, len(commitmentInfo))}
+	poks := make([]curve.G1Affine, len(commitmentInfo))
+
+	// the bsb22 hint (prove.go:81-109) with Commit moved to the device; the proof of knowledge (prove.go:120-127) is the
+	// same values against BasisExpSigma, so g16_commit returns it from the same upload
+	solverOpts := opt.SolverOpts[:len(opt.SolverOpts):len(opt.SolverOpts)]
+	bsb22ID := solver.GetHintID(fcs.Bsb22CommitmentComputePlaceholder)
+	solverOpts = append(solverOpts, solver.OverrideHint(bsb22ID, func(_ *big.Int, in []*big.Int, out []*big.Int) error {
+		i := int(in[0].Int64())
+		in = in[1:]
+		hashed := in[:len(commitmentInfo[i].PublicAndCommitmentCommitted)]
+		committed := in[len(hashed):]
+		values := make([]fr.Element, len(committed))
+		for j, inJ := range committed {
+			values[j].SetBigInt(inJ)
+		}
+		var pin runtime.Pinner
+		if len(values) != 0 {
+			pin.Pin(&values[0])
+		}
+		rc := C.g16_commit(pk.ctx, C.uint64_t(pk.commitKeys[i]), ptrOf(values), C.uint64_t(len(values)),
+			unsafe.Pointer(&proof.Commitments[i]), unsafe.Pointer(&poks[i]))
+		pin.Unpin()
+		if rc != 0 {
+			return lastError(pk.ctx, "g16_commit")
+		}
+		opt.HashToFieldFn.Write(constraint.SerializeCommitment(proof.Commitments[i].Marshal(), hashed, (fr.Bits-1)/8+1))
+		hashBts := opt.HashToFieldFn.Sum(nil)
+		opt.HashToFieldFn.Reset()
+		nbBuf := fr.Bytes
+		if opt.HashToFieldFn.Size() < fr.Bytes {
+			nbBuf = opt.HashToFieldFn.Size()
+		}
+		var res fr.Element
+		res.SetBytes(hashBts[:nbBuf])
+		res.BigInt(out[0])
+		return nil
+	}))
+
+	_solution, err := r1cs.Solve(fullWitness, solverOpts...)
 	if err != nil {
 		return nil, err
 	}
 	solution := _solution.(*cs.R1CSSolution)
 	start := time.Now()
+
+	// fold the proofs of knowledge (prove.go:125-135)
+	if len(commitmentInfo) != 0 {
+		commitmentsSerialized := make([]byte, fr.Bytes*len(commitmentInfo))
+		for i := range commitmentInfo {
+			copy(commitmentsSerialized[fr.Bytes*i:], solution.W[commitmentInfo[i].CommitmentIndex].Marshal())
+		}
+		challenge, err := fr.Hash(commitmentsSerialized, []byte("G16-BSB22"), 1)
+		if err != nil {
+			return nil, err
+		}
+		if _, err = proof.CommitmentPok.Fold(poks, challenge[0], ecc.MultiExpConfig{NbTasks: 1}); err != nil {
+			return nil, err
+		}
+	}
 
 	var out [C.G16_PROVE_OUT_BYTES]byte
 	var stats C.g16_stats
@@ -153,7 +249,6 @@ func Prove(r1cs *cs.R1CS, pk *ProvingKey, fullWitness witness.Witness, opts ...b
 	_s.BigInt(&s)
 	deltas := curve.BatchScalarMultiplicationG1(&pk.G1.Delta, []fr.Element{_r, _s, _kr})
 
-	proof := &groth16_bn254.Proof{}
 	var ar, bs1, krs, p1 curve.G1Jac
 	ar.FromAffine(&arMsm)
 	ar.AddMixed(&pk.G1.Alpha)

@@ -9,8 +9,9 @@ import (
 // uploaded key (bases in Montgomery affine form, index maps, domain twiddles).  It is never serialised, so a key
 // read back with ReadFrom re-uploads lazily on its next Prove.
 type deviceInfo struct {
-	ctx    ctxHandle
-	handle uint64
+	ctx        ctxHandle
+	handle     uint64
+	commitKeys []uint64 // one resident pedersen.ProvingKey per BSB22 commitment
 }
 
 // ProvingKey embeds the native key so that every (un)marshalling method of groth16.ProvingKey is inherited.

@@ -90,6 +90,18 @@ typedef struct {
     uint32_t shard_count;          /*   array (point-range sharding across GPUs); 0/1 = whole key */
 } g16_pk_desc;
 int g16_pk_upload(g16_ctx* ctx, const g16_pk_desc* desc, uint64_t* pk_handle);
+/* SURVEY.md 8(f) N2 -- load the key straight from a ProvingKey.WriteDump image (marshal.go:386-456).  The dump's
+ * point slices (unsafe.WriteSlice: u64 length, then the raw memory of the []G1Affine / []G2Affine) are already the
+ * device format, so they never need to become Go slices: the caller decodes the small header with gnark's own
+ * decoder (domain, alpha/beta/delta, InfinityA/B -- marshal.go:476-509), notes the byte offset of each slice's
+ * first element, and the library streams file -> pinned staging -> HBM (two 32 MiB buffers, pread overlapped with
+ * the H2D copy), reading only this shard's ranges.  `key` is a g16_pk_desc whose five base pointers are ignored. */
+typedef struct {
+    g16_pk_desc key;               /* counts, domain_n, infinity_a/b, n_wires, k_index, shard_*; g1_a..g2_b unused */
+    int fd;                        /* open file, readable with pread(2) */
+    uint64_t off_g1_a, off_g1_b, off_g1_k, off_g1_z, off_g2_b;   /* byte offset of element 0 of each slice */
+} g16_pk_file_desc;
+int g16_pk_upload_from_file(g16_ctx* ctx, const g16_pk_file_desc* desc, uint64_t* pk_handle);
 int g16_pk_free(g16_ctx* ctx, uint64_t pk_handle);
 
 /* ---- the proof hot path ---------------------------------------------------------------------------- */
