@@ -176,16 +176,25 @@ int g16_ctx_create(g16_ctx** out, int curve_id, const int* device_ids, int n_dev
     if (n_devices > 1) return 4;
     std::unique_ptr<g16_ctx> c(new g16_ctx());
     try {
+        // A prove uses 10 streams (main, 4 MSM streams, 5 tail streams); with the default 8 hardware queues two of them
+        // share one and the later MSM starts only when the earlier one has finished.  Takes effect only if CUDA has not
+        // been initialised in this process yet (hosts that initialise CUDA first should export it themselves).
+        setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
         int count = 0;
         G16_CUDA(cudaGetDeviceCount(&count));
         if (count < 1) throw std::runtime_error("no CUDA device: libg16b200 has no CPU fallback");
         c->device = (device_ids && n_devices == 1) ? device_ids[0] : 0;
         G16_CUDA(cudaSetDevice(c->device));
         if (const char* e = getenv("G16_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(e));   // experiment knob
-        G16_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-        for (auto& a : c->aux) G16_CUDA(cudaStreamCreateWithFlags(&a, cudaStreamNonBlocking));
         int prio_lo = 0, prio_hi = 0;
         G16_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+        // the main stream carries computeH and then the H.Z MSM.  Measured (G16_TIMELINE=1): at high priority h is ready
+        // after 6.8 ms instead of ~50, but the proof takes the same 69 ms -- the GPU is busy throughout and some MSM
+        // has to finish last -- and the host-buffer entry point gets slower (75.9 vs 72.0 ms); default = normal priority
+        int prio_main = prio_lo;
+        if (const char* e = getenv("G16_MAIN_PRIO")) prio_main = atoi(e);
+        G16_CUDA(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_main));
+        for (auto& a : c->aux) G16_CUDA(cudaStreamCreateWithFlags(&a, cudaStreamNonBlocking));
         for (auto& t : c->tails) G16_CUDA(cudaStreamCreateWithPriority(&t, cudaStreamNonBlocking, prio_hi));
         for (auto& e : c->ev) G16_CUDA(cudaEventCreate(&e));
         if (const char* e = getenv("G16_STREAMS")) c->streams = atoi(e);
@@ -405,6 +414,15 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
         stats->d2h_bytes = 0;
         for (int i = 0; i < 5; i++) stats->d2h_bytes += (uint64_t)2 * plan[i].W * (i == 4 ? sizeof(G2::Xyzz) : sizeof(G1::Xyzz));
         stats->kernel_launches = (uint32_t)(launch_counter().load() - launches0);
+    }
+    static const bool timeline = getenv("G16_TIMELINE") != nullptr;   // diagnostic: event offsets from the start of the prove
+    if (timeline) {
+        auto at = [&](cudaEvent_t e) { float ms = 0; cudaEventElapsedTime(&ms, ev[0], e); return ms; };
+        const char* names[5] = {"ar", "bs1", "krs_k", "krs_hz", "bs2"};
+        fprintf(stderr, "[g16 timeline] computeH %.2f-%.2f  end %.2f\n", at(ev[12]), at(ev[13]), at(ev[14]));
+        for (int i = 0; i < 5; i++)
+            if (ns[i]) fprintf(stderr, "[g16 timeline] %-7s msm %.2f-%.2f  accumulate %.2f-%.2f\n", names[i], at(ev[1 + i]), at(ev[6 + i]),
+                               at(ev[16 + 2 * i]), at(ev[17 + 2 * i]));
     }
 }
 

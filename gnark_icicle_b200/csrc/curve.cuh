@@ -110,5 +110,16 @@ struct Curve {
 
 typedef Curve<FpC> G1;
 typedef Curve<Fp2> G2;
+// The same groups over the lazily reduced fields (coordinates in [0, 2p), field.cuh LazyFieldCall): used inside the
+// bucket-accumulation loop only; Aff / Xyzz have the same memory layout as G1 / G2.
+typedef Curve<FpL> G1L;
+typedef Curve<Fp2L> G2L;
+// MODE 0: every base-field multiplication is a call.  MODE 1: G1 inlines them (the loop body then has to stay a single
+// group addition to fit the instruction cache), G2 calls at the Fp2 level.
+template <class C, int MODE> struct LazyCurve;
+template <> struct LazyCurve<G1, 0> { typedef G1L type; };
+template <> struct LazyCurve<G2, 0> { typedef G2L type; };
+template <> struct LazyCurve<G1, 1> { typedef Curve<FpLI> type; };
+template <> struct LazyCurve<G2, 1> { typedef Curve<Fp2LC> type; };
 
 }  // namespace g16

@@ -142,6 +142,7 @@ struct Field {
 #pragma unroll
         for (int i = 0; i < N; i++) o |= a.l[i] ^ b.l[i]; return o == 0; }
 
+    G16_HD static T canon(const T& a) { return a; }   // values of this field are always in [0, p); see LazyFieldCall
     // r = a - p if a >= p (a < 2p)
     G16_HD static T reduce_once(const T& a) {
         T s;
@@ -242,6 +243,25 @@ struct Field {
     }
 #endif
 
+#ifdef __CUDA_ARCH__
+    // Montgomery product without the final conditional subtraction: for inputs in [0, 2p) the result is in [0, 2p)
+    // because 4p < R for every modulus here (a*b/R < p, plus at most p from the reduction)
+    G16_D static T mul_raw(const T& a, const T& b) {
+        uint32_t even[N], odd[N];
+#pragma unroll
+        for (int i = 0; i < N; i += 2) {
+            mad_redc(even, odd, a.l, b.l[i], i == 0);
+            mad_redc(odd, even, a.l, b.l[i + 1], false);
+        }
+        T r;
+        r.l[0] = ptx::add_cc(even[0], odd[1]);
+#pragma unroll
+        for (int i = 1; i < N - 1; i++) r.l[i] = ptx::addc_cc(even[i], odd[i + 1]);
+        r.l[N - 1] = ptx::addc(even[N - 1], 0);
+        return r;
+    }
+#endif
+
     // Montgomery product a*b*R^-1 mod p, inputs and output in [0, p)
     G16_HD static T mul(const T& a, const T& b) {
 #ifdef __CUDA_ARCH__
@@ -323,6 +343,74 @@ struct FieldCall : Field<P> {
     G16_HD static T sqr(const T& a) { return mul(a, a); }
 };
 
+// Lazy reduction for the hot loops (bucket accumulation): values live in [0, 2p) instead of [0, p), which drops the
+// conditional subtraction at the end of every multiplication (17 of its 183 instructions on 8 limbs).  Valid because
+// 4p < R for all four moduli (BN254 p, r: 254 bits of 256; BLS12-377 p: 377 of 384, r: 253 of 256): a Montgomery
+// product of two values below 2p is below 2p, a sum is below 4p < R and is brought back with one conditional
+// subtraction of 2p.  Zero has two representations (0 and p).  canon() returns to [0, p) where values leave the loop.
+template <class P>
+struct LazyField : Field<P> {
+    typedef Field<P> B;
+    typedef typename B::T T;
+    static constexpr int N = P::N;
+    G16_HD static constexpr uint32_t mod2(int i) { return (P::mod(i) << 1) | (i ? P::mod(i - 1) >> 31 : 0u); }
+#ifdef __CUDA_ARCH__
+    G16_D static T mul(const T& a, const T& b) { return B::mul_raw(a, b); }
+    G16_D static T sqr(const T& a) { return mul(a, a); }
+    // a < 4p -> [0, 2p)
+    G16_D static T reduce2(const T& a) {
+        T s;
+        s.l[0] = ptx::sub_cc(a.l[0], mod2(0));
+#pragma unroll
+        for (int i = 1; i < N; i++) s.l[i] = ptx::subc_cc(a.l[i], mod2(i));
+        uint32_t borrow = ptx::subc(0, 0);
+        T r;
+#pragma unroll
+        for (int i = 0; i < N; i++) r.l[i] = borrow ? a.l[i] : s.l[i];
+        return r;
+    }
+    G16_D static T add(const T& a, const T& b) {
+        T r;
+        r.l[0] = ptx::add_cc(a.l[0], b.l[0]);
+#pragma unroll
+        for (int i = 1; i < N - 1; i++) r.l[i] = ptx::addc_cc(a.l[i], b.l[i]);
+        r.l[N - 1] = ptx::addc(a.l[N - 1], b.l[N - 1]);   // a + b < 4p < R
+        return reduce2(r);
+    }
+    G16_D static T dbl(const T& a) { return add(a, a); }
+    G16_D static T sub(const T& a, const T& b) {
+        T r;
+        r.l[0] = ptx::sub_cc(a.l[0], b.l[0]);
+#pragma unroll
+        for (int i = 1; i < N; i++) r.l[i] = ptx::subc_cc(a.l[i], b.l[i]);
+        uint32_t borrow = ptx::subc(0, 0);
+        r.l[0] = ptx::add_cc(r.l[0], borrow & mod2(0));
+#pragma unroll
+        for (int i = 1; i < N - 1; i++) r.l[i] = ptx::addc_cc(r.l[i], borrow & mod2(i));
+        r.l[N - 1] = ptx::addc(r.l[N - 1], borrow & mod2(N - 1));
+        return r;
+    }
+    G16_D static bool is_zero(const T& a) {
+        uint32_t z = 0, m = 0;
+#pragma unroll
+        for (int i = 0; i < N; i++) { z |= a.l[i]; m |= a.l[i] ^ P::mod(i); }
+        return z == 0 || m == 0;
+    }
+    G16_D static bool eq(const T& a, const T& b) { return is_zero(sub(a, b)); }
+    G16_D static T neg(const T& a) { return B::is_zero(a) ? a : sub(B::zero(), a); }   // 2p - a for a in (0, 2p)
+    G16_D static T canon(const T& a) { return B::reduce_once(a); }
+#endif
+};
+// the same with the multiplication as a real call (see FieldCall)
+template <class P>
+struct LazyFieldCall : LazyField<P> {
+    typedef typename Field<P>::T T;
+#ifdef __CUDA_ARCH__
+    __device__ __noinline__ static T mul(T a, T b) { return Field<P>::mul_raw(a, b); }
+    G16_D static T sqr(const T& a) { return mul(a, a); }
+#endif
+};
+
 #if G16_CURVE == 377
 typedef FpBLS377 FpParams;
 typedef FrBLS377 FrParams;
@@ -335,6 +423,8 @@ constexpr int FP2_NONRESIDUE = 1;    // Fp2 = Fp[u]/(u^2+1)  (gnark-crypto bn254
 typedef Field<FpParams> Fp;
 typedef Field<FrParams> Fr;
 typedef FieldCall<FpParams> FpC;
+typedef LazyFieldCall<FpParams> FpL;
+typedef LazyField<FrParams> FrL;
 
 // ---------------------------------------------------------------- Fp2 = Fp[u]/(u^2 + NR)  (gnark E2{A0,A1})
 template <class F, int NR>
@@ -348,6 +438,7 @@ struct Ext2 {
     G16_HD static T sub(const T& a, const T& b) { T r; r.a0 = F::sub(a.a0, b.a0); r.a1 = F::sub(a.a1, b.a1); return r; }
     G16_HD static T dbl(const T& a) { return add(a, a); }
     G16_HD static T neg(const T& a) { T r; r.a0 = F::neg(a.a0); r.a1 = F::neg(a.a1); return r; }
+    G16_HD static T canon(const T& a) { T r; r.a0 = F::canon(a.a0); r.a1 = F::canon(a.a1); return r; }
     // NR * a for the small non-residues in use (1 and 5)
     G16_HD static typename F::T mul_nr(const typename F::T& a) {
         static_assert(NR == 1 || NR == 5, "unsupported non-residue");
@@ -380,5 +471,18 @@ struct Ext2 {
     }
 };
 typedef Ext2<FpC, FP2_NONRESIDUE> Fp2;
+typedef Ext2<FpL, FP2_NONRESIDUE> Fp2L;     // same memory layout as Fp2, coordinates in [0, 2p)
+// Fp2 with the call boundary one level up: mul / sqr are real calls whose 3 / 2 base-field multiplications are inlined
+// (a third of the argument shuffling of three separate calls)
+template <class F, int NR>
+struct Ext2Call : Ext2<F, NR> {
+    typedef typename Ext2<F, NR>::T T;
+#ifdef __CUDA_ARCH__
+    __device__ __noinline__ static T mul(T a, T b) { return Ext2<F, NR>::mul(a, b); }
+    __device__ __noinline__ static T sqr(T a) { return Ext2<F, NR>::sqr(a); }
+#endif
+};
+typedef LazyField<FpParams> FpLI;                      // lazily reduced, multiplication inlined
+typedef Ext2Call<FpLI, FP2_NONRESIDUE> Fp2LC;
 
 }  // namespace g16

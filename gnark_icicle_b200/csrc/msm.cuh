@@ -429,17 +429,26 @@ __host__ __device__ __forceinline__ uint32_t msm_slice(uint32_t total, uint32_t 
 // The running bucket sum of an accumulate thread, in registers (G1) or word-interleaved in shared memory (G2: the
 // XYZZ accumulator alone is 64 / 96 registers; parking it in shared memory -- word w of component k of thread t at
 // [(k*EW + w) * THREADS + t], conflict-free -- frees enough registers for one more CTA per SM).
-template <class C>
+// Both run the additions of the loop in the lazily reduced field (values in [0, 2p): no conditional subtraction after
+// a multiplication) and bring the sum back to [0, p) when it leaves the thread.
+template <class C, int MODE>
 struct RegAcc {
-    typename C::Xyzz a;
-    __device__ __forceinline__ void reset() { a = C::inf(); }
-    __device__ __forceinline__ void add(const typename C::Aff& p) { C::madd(a, p); }
-    __device__ __forceinline__ void store(typename C::Xyzz* dst) const { store_xyzz<C>(dst, a); }
+    typedef typename LazyCurve<C, MODE>::type CL;
+    typename CL::Xyzz a;
+    __device__ __forceinline__ void reset() { a = CL::inf(); }
+    __device__ __forceinline__ void add(const typename C::Aff& p) { CL::madd(a, reinterpret_cast<const typename CL::Aff&>(p)); }
+    __device__ __forceinline__ void store(typename C::Xyzz* dst) const {
+        typedef typename CL::BaseField BF;
+        typename CL::Xyzz v;
+        v.x = BF::canon(a.x); v.y = BF::canon(a.y); v.zz = BF::canon(a.zz); v.zzz = BF::canon(a.zzz);
+        store_xyzz<C>(dst, reinterpret_cast<const typename C::Xyzz&>(v));
+    }
 };
-template <class C, int THREADS>
+template <class C, int THREADS, int MODE>
 struct SmemAcc {
-    typedef typename C::E E;
-    typedef typename C::BaseField BF;
+    typedef typename LazyCurve<C, MODE>::type CL;
+    typedef typename CL::E E;
+    typedef typename CL::BaseField BF;
     static constexpr int EW = sizeof(E) / 4;
     static constexpr size_t BYTES = (size_t)4 * EW * THREADS * 4;
     uint32_t* s;     // shared base + threadIdx.x
@@ -457,13 +466,14 @@ struct SmemAcc {
     }
     __device__ __forceinline__ void reset() { is_inf = true; }
     // madd-2008-s with every accumulator coordinate loaded right before its use and stored as soon as it is final
-    __device__ __forceinline__ void add(const typename C::Aff& p) {
-        if (C::is_inf(p)) return;
+    __device__ __forceinline__ void add(const typename C::Aff& p0) {
+        const typename CL::Aff& p = reinterpret_cast<const typename CL::Aff&>(p0);
+        if (CL::is_inf(p)) return;
         if (is_inf) { st(0, p.x); st(1, p.y); st(2, BF::one()); st(3, BF::one()); is_inf = false; return; }
         E pp = BF::sub(BF::mul(p.x, ld(2)), ld(0));
         E r = BF::sub(BF::mul(p.y, ld(3)), ld(1));
         if (BF::is_zero(pp)) {
-            if (BF::is_zero(r)) { typename C::Xyzz d = C::dbl_aff(p); st(0, d.x); st(1, d.y); st(2, d.zz); st(3, d.zzz); }
+            if (BF::is_zero(r)) { typename CL::Xyzz d = CL::dbl_aff(p); st(0, d.x); st(1, d.y); st(2, d.zz); st(3, d.zzz); }
             else is_inf = true;
             return;
         }
@@ -477,14 +487,14 @@ struct SmemAcc {
         st(1, BF::sub(BF::mul(r, BF::sub(q, x3)), BF::mul(ld(1), p3)));
     }
     __device__ __forceinline__ void store(typename C::Xyzz* dst) const {
-        typename C::Xyzz v;
-        if (is_inf) v = C::inf();
-        else { v.x = ld(0); v.y = ld(1); v.zz = ld(2); v.zzz = ld(3); }
-        store_xyzz<C>(dst, v);
+        typename CL::Xyzz v;
+        if (is_inf) v = CL::inf();
+        else { v.x = BF::canon(ld(0)); v.y = BF::canon(ld(1)); v.zz = BF::canon(ld(2)); v.zzz = BF::canon(ld(3)); }
+        store_xyzz<C>(dst, reinterpret_cast<const typename C::Xyzz&>(v));
     }
 };
 
-template <class C, int THREADS, int MINB, bool SMEM_ACC>
+template <class C, int THREADS, int MINB, bool SMEM_ACC, int MODE>
 __global__ void __launch_bounds__(THREADS, MINB)
 k_accumulate(const typename C::Aff* __restrict__ bases, const uint32_t* __restrict__ sorted,
              const uint32_t* __restrict__ offsets, uint32_t nb, uint32_t nthreads,
@@ -510,14 +520,15 @@ k_accumulate(const typename C::Aff* __restrict__ bases, const uint32_t* __restri
     uint32_t b_start = offsets[gb], b_end = offsets[gb + 1];
     uint32_t seg_start = my_start;
     extern __shared__ uint32_t acc_smem[];
-    typename std::conditional<SMEM_ACC, SmemAcc<C, THREADS>, RegAcc<C>>::type acc;
+    typename std::conditional<SMEM_ACC, SmemAcc<C, THREADS, MODE>, RegAcc<C, MODE>>::type acc;
     if constexpr (SMEM_ACC) acc.s = acc_smem + threadIdx.x;
     acc.reset();
 
     for (uint32_t p = my_start; p < my_end; p += 4) {
         uint4 idx4 = *reinterpret_cast<const uint4*>(sorted + p);   // padded allocation: reading past `total` is safe
         uint32_t idx[4] = {idx4.x, idx4.y, idx4.z, idx4.w};
-#pragma unroll
+        // G1 with inlined multiplications: one group addition is ~32 KB of code, so the loop must not be unrolled
+#pragma unroll(MODE == 1 && !SMEM_ACC && sizeof(typename C::E) == sizeof(Fp::T) ? 1 : 4)
         for (int k = 0; k < 4; k++) {
             uint32_t pos = p + k;
             if (pos >= my_end) break;
@@ -685,7 +696,7 @@ __global__ void __launch_bounds__(32) k_window_sum(const typename C::Xyzz* __res
 struct MsmStats { int c = 0, W = 0; uint32_t acc_threads = 0; cudaEvent_t acc_begin = nullptr, acc_end = nullptr; };
 
 // Enqueues the whole MSM on `st`; window sums land in ws.host_wsum (pinned) after the stream drains.
-template <class C, int ACC_THREADS, int ACC_MINB, bool SMEM_ACC = false>
+template <class C, int ACC_THREADS, int ACC_MINB, bool SMEM_ACC = false, int MODE = 0>
 void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const typename C::Aff* bases_d,
                  uint64_t n, int force_c, int waves, cudaStream_t st, MsmPlan& plan_out, MsmStats* stats,
                  cudaStream_t tail = nullptr, int pre_c = 0, MsmWorkspace* sort_from = nullptr) {
@@ -705,8 +716,8 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
     G16_CUDA(cudaGetDevice(&dev));
     G16_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     int occ = 0;
-    auto acc_kernel = k_accumulate<C, ACC_THREADS, ACC_MINB, SMEM_ACC>;
-    const size_t acc_smem = SMEM_ACC ? SmemAcc<C, ACC_THREADS>::BYTES : 0;
+    auto acc_kernel = k_accumulate<C, ACC_THREADS, ACC_MINB, SMEM_ACC, MODE>;
+    const size_t acc_smem = SMEM_ACC ? SmemAcc<C, ACC_THREADS, MODE>::BYTES : 0;
     if (acc_smem > 48 * 1024) G16_CUDA(cudaFuncSetAttribute(acc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)acc_smem));
     G16_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, acc_kernel, ACC_THREADS, acc_smem));
     if (occ < 1) occ = 1;

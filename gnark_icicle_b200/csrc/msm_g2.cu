@@ -11,13 +11,16 @@ void msm_g2_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* ma
     // 128 x 2.  Measured (profiles/README.md): the G2 kernel is issue-bound -- every integer instruction, IADD3 included,
     // takes the same two-cycle slot as an IMAD -- so more CTAs/SM do not help (3-4 CTAs/SM: +15..50 %).  Parking the
     // accumulator in shared memory (SmemAcc) costs 15 % on BN254 (extra LDS/STS issue slots) but removes enough spills
-    // on the 12-limb BLS12-377 field to win 5 % there.
+    // on the 12-limb BLS12-377 field to win 5 % there.  Variants 3 / 4 call at the Fp2 level (three base-field
+    // multiplications inlined per call): 252 / 222 registers and 10 % slower than the per-Fp calls (23.4 vs 21.3 ms).
 #if G16_CURVE == 377
     const bool smem_acc = variant != 1;
 #else
     const bool smem_acc = variant == 1;
 #endif
-    if (smem_acc) msm_enqueue<G2, 128, 2, true>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+    if (variant == 3) msm_enqueue<G2, 128, 2, false, 1>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+    else if (variant == 4) msm_enqueue<G2, 128, 2, true, 1>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+    else if (smem_acc) msm_enqueue<G2, 128, 2, true>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
     else msm_enqueue<G2, 128, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
 }
 void msm_g2_precompute(G2::Aff* table_d, uint64_t n, int c, cudaStream_t st) {

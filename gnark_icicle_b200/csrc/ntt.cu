@@ -172,14 +172,15 @@ __global__ void __launch_bounds__(NTT_THREADS) k_ntt_pass(PassArgs a) {
             uint64_t q = qbase + c;
             uint64_t j = ((uint64_t)(r0 & mmask) << s) | (q & smask);
             Fr::T t = ldg_fr(tws + ((j << a.g) | a.rank));
+            // butterflies in the lazily reduced field (values in [0, 2r) while the tile is in shared memory)
             Fr::T u = ld_planes(lo, hi, e0), v = ld_planes(lo, hi, e1);
             if (DIF) {
-                st_planes(lo, hi, e0, Fr::add(u, v));
-                st_planes(lo, hi, e1, Fr::mul(Fr::sub(u, v), t));
+                st_planes(lo, hi, e0, FrL::add(u, v));
+                st_planes(lo, hi, e1, FrL::mul(FrL::sub(u, v), t));
             } else {
-                v = Fr::mul(v, t);
-                st_planes(lo, hi, e0, Fr::add(u, v));
-                st_planes(lo, hi, e1, Fr::sub(u, v));
+                v = FrL::mul(v, t);
+                st_planes(lo, hi, e0, FrL::add(u, v));
+                st_planes(lo, hi, e1, FrL::sub(u, v));
             }
         }
         __syncthreads();
@@ -190,8 +191,9 @@ __global__ void __launch_bounds__(NTT_THREADS) k_ntt_pass(PassArgs a) {
         uint64_t q = qbase + c;
         uint64_t gi = ((q >> s) << (s + k)) | ((uint64_t)r << s) | (q & smask);
         uint4* dst = reinterpret_cast<uint4*>(data + gi);
-        dst[0] = lo[e];
-        dst[1] = hi[e];
+        Fr::T v = FrL::canon(ld_planes(lo, hi, e));     // back to [0, r): global memory only ever holds canonical values
+        dst[0] = make_uint4(v.l[0], v.l[1], v.l[2], v.l[3]);
+        dst[1] = make_uint4(v.l[4], v.l[5], v.l[6], v.l[7]);
     }
 }
 

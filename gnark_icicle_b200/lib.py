@@ -12,6 +12,10 @@ import os
 
 import numpy as np
 
+# a prove runs on 10 CUDA streams; the default 8 hardware queues would make two of them share one (see g16_ctx_create).
+# Must be in the environment before the process initialises CUDA (torch does so lazily, after this import).
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libg16b200.so")
 
