@@ -274,9 +274,20 @@ def run_ours(args):
     dev = torch.device(f"cuda:{local}")
     torch.cuda.set_device(dev)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"       # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL prints its version banner on stdout when the communicator comes up (NCCL_DEBUG=VERSION from the box's
+        # environment or nccl.conf); rank 0 must print ONE JSON line there, so stdout points at stderr until then
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            warm = torch.zeros(1, device=dev)
+            dist.all_reduce(warm)
+            torch.cuda.synchronize(dev)
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
     ctx = lib.Context(local, curve=args.curve)
     fp_eq = IMAD_EQ_PER_FP_MUL if args.curve == "bn254" else IMAD_EQ_PER_FP_MUL_12
     ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
@@ -398,9 +409,9 @@ def run_ours(args):
                    "algorithmic_bytes_per_launch_2p22": (1 << 22) * 13 * 68,
                    "note": "the accumulate kernel is bound by the integer multiplier, not HBM: it moves <10 % of the copy bandwidth"}
     if args.log_n == 22 and args.curve == "bn254":
-        roof["traffic"] = 4.07e9
-        roof["traffic_source"] = ("profiles/r01c_accumulate_2p22_ncu_raw.csv: 3.96 GB read + 0.11 GB written per 2^22-point launch "
-                                  "(9.6 ms, 54.5 M entries x 68 B = 3.71 GB algorithmic); before the 64-byte L2 fill hint: 7.45 GB")
+        roof["traffic"] = 4.10e9
+        roof["traffic_source"] = ("profiles/r01d_accumulate_ntt_2p22_ncu_raw.csv: 3.97 GB read + 0.13 GB written per 2^22-point launch "
+                                  "(8.6 ms, 54.5 M entries x 68 B = 3.71 GB algorithmic); before the 64-byte L2 fill hint: 7.45 GB")
     ntt_bytes = 7 * 64 * n
     if world == 1 and st["ms_compute_h"] > 0:
       roof["compute_h"] = {"bound": "hbm", "achieved": ntt_bytes / (st["ms_compute_h"] * 1e-3) / 1e9, "peak": pk_["hbm_gbs"],

@@ -18,7 +18,10 @@ void msm_g2_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* ma
 #else
     const bool smem_acc = variant == 1;
 #endif
-    if (variant == 3) msm_enqueue<G2, 128, 2, false, 1>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+    if (variant == 5) msm_enqueue<G2, 64, 1>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+    else if (variant == 6) msm_enqueue<G2, 32, 1>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+    else if (variant == 7) msm_enqueue<G2, 96, 1>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+    else if (variant == 3) msm_enqueue<G2, 128, 2, false, 1>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
     else if (variant == 4) msm_enqueue<G2, 128, 2, true, 1>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
     else if (smem_acc) msm_enqueue<G2, 128, 2, true>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
     else msm_enqueue<G2, 128, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
