@@ -1,6 +1,7 @@
 """BSB22 commitments on the accelerated proving path.
 
-Host side of backend/groth16/bn254/prove.go:81-139 (the icicle prover repeats it verbatim at icicle.go:152-203):
+Host side of backend/groth16/bn254/prove.go:81-139 (the icicle prover repeats the hint at icicle.go:152-190 but is
+stale after it -- no proof of knowledge, SURVEY.md F5 -- so the CPU prover is the model):
 the bsb22 solver-hint override that commits to the privately committed wires, hashes the commitment to the value
 of the commitment wire, and -- after the solve -- the per-key proofs of knowledge folded with the "G16-BSB22"
 challenge.  The two MSMs per commitment (pedersen Commit / ProveKnowledge over Basis / BasisExpSigma) run on the
