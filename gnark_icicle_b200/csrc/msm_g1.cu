@@ -12,6 +12,8 @@ void msm_g1_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* ma
     // 12-limb Fp: the accumulator alone is 48 registers; 128 x 3 (<= 168 registers) is the default
     if (variant == 1) msm_enqueue<G1, 256, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
     else if (variant == 2) msm_enqueue<G1, 128, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+    else if (variant == 3) msm_enqueue<G1, 128, 3, false, 1>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+    else if (variant == 4) msm_enqueue<G1, 128, 2, false, 1>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
     else msm_enqueue<G1, 128, 3>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
 #else
     // 256-thread CTAs, 2 per SM, the field multiplications of the group addition inlined and the loop not unrolled: the
