@@ -330,7 +330,8 @@ def run_ours(args):
         abc_master = torch.stack([sd[k][rank::world] for k in ("a", "b", "c")]).contiguous()
         abc_work = torch.empty_like(abc_master)
         abc_pin = abc_master.cpu().pin_memory()
-        W_stage = torch.empty_like(sd["W"])
+        W_stage = torch.zeros_like(sd["W"])
+        w_lo, w_hi = ctx.pk_wire_range(handle)           # the wires this rank's shard of the A, B, K bases reads
         del wa, wb, wc
 
         def msms(W_t):
@@ -344,10 +345,11 @@ def run_ours(args):
             return msms(sd["W"])
 
         def step_e2e():
-            W_stage.copy_(sh["W"], non_blocking=True)      # full W + this rank's 1/world of a, b, c from pinned host memory
+            # this rank's 1/world of a, b, c and the wire range its key shard reads, from pinned host memory
             abc_work.copy_(abc_pin, non_blocking=True)
+            W_stage[w_lo:w_hi].copy_(sh["W"][w_lo:w_hi], non_blocking=True)
             pts, st = msms(W_stage)
-            st["h2d_bytes"] = W_stage.numel() * 8 + abc_pin.numel() * 8
+            st["h2d_bytes"] = (w_hi - w_lo) * W_stage.shape[1] * 8 + abc_pin.numel() * 8
             return pts, st
 
     l0 = lib.kernel_launch_count(args.curve)

@@ -30,6 +30,7 @@ struct PkDev {
     uint64_t n_a = 0, n_b = 0, n_k = 0, n_z = 0, n_b2 = 0;
     int pre_c[5] = {0, 0, 0, 0, 0}; // window bits of the precomputed-multiples table per MSM (G16_OUT_* order); 0 = none
     uint64_t z_off = 0;           // first h index of this shard's Z slice
+    uint64_t w_lo = 0, w_hi = 0;  // wires [w_lo, w_hi) are the only ones this shard's A / B / K maps read
     void release() {
         g1_a.release(); g1_b.release(); g1_k.release(); g1_z.release(); g2_b.release();
         map_a.release(); map_b.release(); map_k.release();
@@ -280,16 +281,24 @@ int pk_upload_impl(g16_ctx* ctx, const g16_pk_desc* d, const Src* src, uint64_t*
         }
 
         uint64_t lo, hi;
+        pk.w_lo = d->n_wires; pk.w_hi = 0;
+        auto touch = [&](const std::vector<uint32_t>& m, uint64_t a, uint64_t b) {   // maps are not assumed monotone (k_index)
+            for (uint64_t i = a; i < b; i++) { if (m[i] < pk.w_lo) pk.w_lo = m[i]; if ((uint64_t)m[i] + 1 > pk.w_hi) pk.w_hi = (uint64_t)m[i] + 1; }
+        };
         slice(d->n_a, si, sc, lo, hi);
+        touch(ma, lo, hi);
         pk.n_a = hi - lo;
         upload_bases<G1>(ctx, pk.g1_a, src[0].at(lo * G1SZ), pk.n_a, pk.pre_c[G16_OUT_AR], st);
         upload(pk.map_a, ma.data() + lo, pk.n_a * 4, st);
         slice(d->n_b, si, sc, lo, hi);
+        touch(mb, lo, hi);
         pk.n_b = pk.n_b2 = hi - lo;
         upload_bases<G1>(ctx, pk.g1_b, src[1].at(lo * G1SZ), pk.n_b, pk.pre_c[G16_OUT_BS1], st);
         upload_bases<G2>(ctx, pk.g2_b, src[4].at(lo * G2SZ), pk.n_b, pk.pre_c[G16_OUT_BS2], st);
         upload(pk.map_b, mb.data() + lo, pk.n_b * 4, st);
         slice(d->n_k, si, sc, lo, hi);
+        touch(mk, lo, hi);
+        if (pk.w_hi <= pk.w_lo) pk.w_lo = pk.w_hi = 0;
         pk.n_k = hi - lo;
         upload_bases<G1>(ctx, pk.g1_k, src[2].at(lo * G1SZ), pk.n_k, pk.pre_c[G16_OUT_KRS_K], st);
         upload(pk.map_k, mk.data() + lo, pk.n_k * 4, st);
@@ -332,6 +341,15 @@ extern "C" int g16_pk_upload_from_file(g16_ctx* ctx, const g16_pk_file_desc* f, 
     const uint64_t off[5] = {f->off_g1_a, f->off_g1_b, f->off_g1_k, f->off_g1_z, f->off_g2_b};
     for (int i = 0; i < 5; i++) { src[i].fd = f->fd; src[i].off = off[i]; }
     return pk_upload_impl(ctx, &f->key, src, pk_handle);
+}
+
+extern "C" int g16_pk_wire_range(g16_ctx* ctx, uint64_t pk_handle, uint64_t* lo, uint64_t* hi) {
+    return guarded(ctx, [&] {
+        auto it = ctx->pks.find(pk_handle);
+        if (it == ctx->pks.end()) throw std::runtime_error("unknown proving-key handle");
+        if (!lo || !hi) throw std::runtime_error("null argument");
+        *lo = it->second.w_lo; *hi = it->second.w_hi;
+    });
 }
 
 extern "C" int g16_pk_free(g16_ctx* ctx, uint64_t pk_handle) {
@@ -455,8 +473,10 @@ extern "C" int g16_prove_bn254(g16_ctx* ctx, uint64_t pk_handle, const void* W, 
         const size_t nb = (size_t)pk.domain_n * 32, cb = (size_t)n_constraints * 32;
         G16_CUDA(cudaEventRecord(ctx->ev[26], st));
         // W first: the four MSMs over W start on their own streams while a, b, c are still in flight
+        // a sharded key reads only the wires [w_lo, w_hi) of W: nothing else crosses PCIe
         ctx->stage[3].reserve((size_t)n_wires * 32);
-        G16_CUDA(cudaMemcpyAsync(ctx->stage[3].p, W, (size_t)n_wires * 32, cudaMemcpyHostToDevice, st));
+        const size_t w_bytes = (size_t)(pk.w_hi - pk.w_lo) * 32;
+        if (w_bytes) G16_CUDA(cudaMemcpyAsync((char*)ctx->stage[3].p + (size_t)pk.w_lo * 32, (const char*)W + (size_t)pk.w_lo * 32, w_bytes, cudaMemcpyHostToDevice, st));
         G16_CUDA(cudaEventRecord(ctx->ev[15], st));
         const void* src[3] = {a, b, c};
         for (int i = 0; i < 3; i++) {      // pad to the domain size (icicle.go:463-467)
@@ -470,7 +490,7 @@ extern "C" int g16_prove_bn254(g16_ctx* ctx, uint64_t pk_handle, const void* W, 
         if (stats) {
             G16_CUDA(cudaEventElapsedTime(&stats->ms_h2d, ctx->ev[26], ctx->ev[27]));
             G16_CUDA(cudaEventElapsedTime(&stats->ms_total, ctx->ev[26], ctx->ev[14]));
-            stats->h2d_bytes = 3 * cb + (uint64_t)n_wires * 32;
+            stats->h2d_bytes = 3 * cb + (uint64_t)w_bytes;
         }
     });
 }
@@ -694,8 +714,10 @@ extern "C" int g16_prove_bn254_wires(g16_ctx* ctx, uint64_t pk_handle, uint64_t 
         cudaStream_t st = ctx->stream;
         const size_t nb = (size_t)pk.domain_n * 32;
         G16_CUDA(cudaEventRecord(ctx->ev[26], st));
+        // a sharded key reads only the wires [w_lo, w_hi) of W: nothing else crosses PCIe
         ctx->stage[3].reserve((size_t)n_wires * 32);
-        G16_CUDA(cudaMemcpyAsync(ctx->stage[3].p, W, (size_t)n_wires * 32, cudaMemcpyHostToDevice, st));
+        const size_t w_bytes = (size_t)(pk.w_hi - pk.w_lo) * 32;
+        if (w_bytes) G16_CUDA(cudaMemcpyAsync((char*)ctx->stage[3].p + (size_t)pk.w_lo * 32, (const char*)W + (size_t)pk.w_lo * 32, w_bytes, cudaMemcpyHostToDevice, st));
         G16_CUDA(cudaEventRecord(ctx->ev[15], st));
         G16_CUDA(cudaEventRecord(ctx->ev[27], st));
         for (int i = 0; i < 3; i++) ctx->stage[i].reserve(nb);

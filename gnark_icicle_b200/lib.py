@@ -83,7 +83,7 @@ class R1csDesc(ctypes.Structure):
 # every symbol include/g16b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "g16_ctx_create", "g16_ctx_destroy", "g16_last_error", "g16_ctx_set", "g16_kernel_launch_count",
-    "g16_pk_upload", "g16_pk_upload_from_file", "g16_pk_free", "g16_prove_bn254", "g16_prove_bn254_dev", "g16_assemble_proof_bn254",
+    "g16_pk_upload", "g16_pk_upload_from_file", "g16_pk_free", "g16_pk_wire_range", "g16_prove_bn254", "g16_prove_bn254_dev", "g16_assemble_proof_bn254",
     "g16_r1cs_upload", "g16_r1cs_free", "g16_r1cs_eval_dev", "g16_prove_bn254_wires",
     "g16_bases_upload", "g16_bases_free", "g16_msm_resident_dev", "g16_msm_resident",
     "g16_commitment_key_upload", "g16_commitment_key_free", "g16_commit",
@@ -290,6 +290,12 @@ class Context:
         h = u64(0)
         self._check(self._lib.g16_pk_upload_from_file(self._h, ctypes.byref(d), ctypes.byref(h)), "g16_pk_upload_from_file")
         return h.value
+
+    def pk_wire_range(self, handle):
+        """[lo, hi): the wires of W this context's shard of the key reads."""
+        lo, hi = u64(0), u64(0)
+        self._check(self._lib.g16_pk_wire_range(self._h, u64(handle), ctypes.byref(lo), ctypes.byref(hi)), "g16_pk_wire_range")
+        return lo.value, hi.value
 
     def pk_free(self, handle):
         self._check(self._lib.g16_pk_free(self._h, u64(handle)), "g16_pk_free")

@@ -103,6 +103,10 @@ typedef struct {
 } g16_pk_file_desc;
 int g16_pk_upload_from_file(g16_ctx* ctx, const g16_pk_file_desc* desc, uint64_t* pk_handle);
 int g16_pk_free(g16_ctx* ctx, uint64_t pk_handle);
+/* The wires [*lo, *hi) of the witness vector are the only ones this context's shard of the A, B and K bases reads (the
+ * whole vector for an unsharded key).  g16_prove_bn254 copies just that range; callers that keep W on the device
+ * (g16_prove_bn254_dev, g16_prove_msms_dev) need to fill only that range. */
+int g16_pk_wire_range(g16_ctx* ctx, uint64_t pk_handle, uint64_t* lo, uint64_t* hi);
 
 /* ---- the proof hot path ---------------------------------------------------------------------------- */
 /* Replaces the device section of icicle_bn254.Prove (icicle.go:204-410): computeH + the five MSMs.

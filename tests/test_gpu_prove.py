@@ -97,14 +97,27 @@ def test_sharded_prove_combines_to_the_same_points():
     case = ChainCase(3000, seed=5)
     sol = g16.R1CSSolution(W=case.W, A=case.a, B=case.b, C=case.c)
     whole, _ = g16.prove_msms(case.pk, sol)
+    ctx0, h0 = case.pk.device
+    assert ctx0.pk_wire_range(h0) == (0, case.nw)        # unsharded: the A map starts at wire 0, K ends at the last wire
     case.pk.free_device()
-    blocks = []
+    blocks, ranges = [], []
     for i in range(3):
         cfg = g16.NewProverConfig(g16.WithDevice(0, i, 3))
-        blk, _ = g16.prove_msms(case.pk, sol, cfg)
+        # the host-buffer entry point uploads only the wires this shard reads: poison everything else
+        blk, st = g16.prove_msms(case.pk, sol, cfg)
+        ctx_i, h_i = case.pk.device
+        lo, hi = ctx_i.pk_wire_range(h_i)
+        ranges.append((lo, hi))
+        assert st["h2d_bytes"] == (hi - lo) * 32 + 3 * len(case.a) * 32
+        Wp = case.W.copy()
+        Wp[:lo] = 0xDEADBEEF
+        Wp[hi:] = 0xDEADBEEF
+        blk2, _ = g16.prove_msms(case.pk, g16.R1CSSolution(W=Wp, A=case.a, B=case.b, C=case.c), cfg)
+        assert np.array_equal(blk, blk2), "wires outside the shard's range must not be read"
         blocks.append(blk)
         case.pk.free_device()
     assert_limbs_equal(g16.combine_shards(blocks), whole, "sharded vs whole")
+    assert ranges[0][0] == 0 and ranges[-1][1] == case.nw and all(hi - lo < case.nw * 0.4 for lo, hi in ranges)
 
 
 def test_full_size_prove_2p20_trapdoor(ctx):
