@@ -243,3 +243,40 @@ def test_prove_2p13_trapdoor(ctx377):
         assert np.array_equal(g16.combine_shards(blocks, curve=CURVE), points)
     finally:
         pk.free_device()
+
+
+# ---------------------------------------------------------------- BSB22 commitment keys, resident bases (8(f) N3)
+@pytest.mark.parametrize("n", [0, 1, 40, 900])
+def test_commit_matches_oracle(ctx377, n):
+    """g16_bls12_377_commit: commitment = sum v_j Basis_j, pok = sum v_j BasisExpSigma_j (12-limb Fp build)."""
+    rng = Xoshiro(SEED_BASE + 75 + n)
+    logs = fr_rand(rng, n)
+    sigma = rng.field(R) or 1
+    vals = fr_rand(rng, n)
+    if n > 2:
+        vals[0] = 0
+        logs[1] = 0                                  # an infinity base is legal
+    empty = np.zeros((0, 12), dtype=np.uint64)      # bases from the fixed-base kernel (itself checked against the oracle)
+    basis = ctx377.g1_fixed_base_mul(fr_arr(logs)) if n else empty
+    basis_sigma = ctx377.g1_fixed_base_mul(fr_arr([k * sigma % R for k in logs])) if n else empty
+    h = ctx377.commitment_key_upload(basis, basis_sigma)
+    cm, pok = ctx377.commit(h, fr_arr(vals) if n else np.zeros((0, 4), np.uint64))
+    e = dot(vals, logs)
+    assert g1_pts(cm)[0] == (C.g1_mul(C.G1_GEN, e) if e else None)
+    assert g1_pts(pok)[0] == (C.g1_mul(C.G1_GEN, e * sigma % R) if e else None)
+    if n:
+        with pytest.raises(lib.G16Error, match="as many values as basis elements"):
+            ctx377.commit(h, fr_arr(vals[:-1]) if n > 1 else np.zeros((0, 4), np.uint64))
+    ctx377.commitment_key_free(h)
+
+
+def test_msm_resident_host_scalars_g1_g2(ctx377):
+    rng = Xoshiro(SEED_BASE + 76)
+    logs, vals = fr_rand(rng, 600), fr_rand(rng, 600)
+    e = dot(vals, logs)
+    h1 = ctx377.bases_upload(ctx377.g1_fixed_base_mul(fr_arr(logs)))
+    assert g1_pts(ctx377.msm_resident(h1, fr_arr(vals)))[0] == C.g1_mul(C.G1_GEN, e)
+    ctx377.bases_free(h1)
+    h2 = ctx377.bases_upload(ctx377.g2_fixed_base_mul(fr_arr(logs)), g2=True)
+    assert g2_pts(ctx377.msm_resident(h2, fr_arr(vals), g2=True))[0] == C.g2_mul(C.G2_GEN, e)
+    ctx377.bases_free(h2)
