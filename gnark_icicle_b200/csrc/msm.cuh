@@ -314,67 +314,20 @@ static __global__ void __launch_bounds__(256) k_pre_scan1(const uint32_t* __rest
     off1[threadIdx.x] = s[threadIdx.x];
     cursor1[threadIdx.x] = s[threadIdx.x];
 }
-// The counting pass keeps the rank every atomicAdd returns (position of the entry among this CTA's entries of its group),
-// so the placement pass needs no second round of shared-memory atomics: position = CTA's reserved base + rank.
-constexpr int MSM_PRE_WMAX = 255 / MSM_PRE_CMIN + 1;   // most digits per scalar in precomputed mode (c >= 16)
 static __global__ void __launch_bounds__(1024) k_pre_scatter1(const Fr::T* __restrict__ scalars, const uint32_t* __restrict__ map, uint64_t n,
                                                               int c, int W, int lo_bits, uint32_t* __restrict__ cursor1, uint2* __restrict__ pairs) {
     __shared__ uint32_t h[256];
     if (threadIdx.x < 256) h[threadIdx.x] = 0;
     __syncthreads();
-    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t bucket_of[MSM_PRE_WMAX];   // bucket | sign << 31 per digit, 0xffffffff = zero digit (no entry)
-    uint16_t rank[MSM_PRE_WMAX];        // < 1024 * 16
-#pragma unroll
-    for (int w = 0; w < MSM_PRE_WMAX; w++) bucket_of[w] = 0xffffffffu;
-    if (i < n) {
-        uint64_t src = map ? map[i] : i;
-        const uint4* q = reinterpret_cast<const uint4*>(scalars + src);
-        uint4 a = __ldg(q), b = __ldg(q + 1);
-        Fr::T s;
-        s.l[0] = a.x; s.l[1] = a.y; s.l[2] = a.z; s.l[3] = a.w; s.l[4] = b.x; s.l[5] = b.y; s.l[6] = b.z; s.l[7] = b.w;
-        s = Fr::from_mont(s);
-        uint32_t l[9];
-#pragma unroll
-        for (int k = 0; k < 8; k++) l[k] = s.l[k];
-        l[8] = 0;
-        const uint32_t mask = (1u << c) - 1, half = 1u << (c - 1);
-        uint32_t carry = 0;
-#pragma unroll
-        for (int w = 0; w < MSM_PRE_WMAX; w++) {     // same recoding as for_each_digit, unrolled so that the arrays stay in registers
-            if (w < W) {
-                const int bit = w * c;
-                uint32_t raw = 0;
-                if (bit < 256) {
-                    const int limb = bit >> 5, sh = bit & 31;
-                    uint32_t lo_w = 0, hi_w = 0;
-#pragma unroll
-                    for (int k = 0; k < 8; k++) { if (k == limb) { lo_w = l[k]; hi_w = l[k + 1]; } }
-                    const uint64_t two = (uint64_t)lo_w | ((uint64_t)hi_w << 32);
-                    raw = (uint32_t)(two >> sh) & mask;
-                }
-                raw += carry;
-                int d;
-                if (raw >= half) { carry = 1; d = (int)raw - (int)(half << 1); } else { carry = 0; d = (int)raw; }
-                if (d != 0) {
-                    const uint32_t bucket = (uint32_t)(d < 0 ? -d : d) - 1;
-                    bucket_of[w] = bucket | (d < 0 ? 0x80000000u : 0u);
-                    rank[w] = (uint16_t)atomicAdd(&h[bucket >> lo_bits], 1u);
-                }
-            }
-        }
-    }
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) for_each_digit(scalars, map, i, c, W, [&](int, uint32_t bucket, uint32_t) { atomicAdd(&h[bucket >> lo_bits], 1u); });
     __syncthreads();
     if (threadIdx.x < 256) { uint32_t v = h[threadIdx.x]; if (v) h[threadIdx.x] = atomicAdd(&cursor1[threadIdx.x], v); }
     __syncthreads();
-#pragma unroll
-    for (int w = 0; w < MSM_PRE_WMAX; w++) {
-        const uint32_t e = bucket_of[w];
-        if (e != 0xffffffffu) {
-            const uint32_t bucket = e & 0x7fffffffu;
-            pairs[h[bucket >> lo_bits] + rank[w]] = make_uint2(bucket, (e & 0x80000000u) | (uint32_t)((uint64_t)w * n + i));
-        }
-    }
+    if (i < n) for_each_digit(scalars, map, i, c, W, [&](int w, uint32_t bucket, uint32_t neg) {
+        uint32_t pos = atomicAdd(&h[bucket >> lo_bits], 1u);
+        pairs[pos] = make_uint2(bucket, (neg << 31) | (uint32_t)((uint64_t)w * n + i));
+    });
 }
 // grid (chunks, 256 groups): chunk ch of group g covers an equal share of [off1[g], off1[g+1])
 __device__ __forceinline__ void pre_chunk(const uint32_t* off1, uint32_t& lo, uint32_t& hi) {
