@@ -5,6 +5,7 @@
   groth16.py   mirror of package icicle_bn254 (Prove, ProvingKey, WithIcicleAcceleration)
   bsb22.py     BSB22 commitments on that path (hint override, commitment keys on the device, folded PoK)
   dump.py      ProvingKey.WriteDump / ReadDump and the direct file -> device key load
+  marshal.py   Proof.WriteTo / WriteRawTo / ReadFrom (compressed and raw point encodings, BN254)
 
 The directory ``gnark-icicle_b200`` at the repo root is a link to this package (a hyphen is not importable).
 """
@@ -12,8 +13,8 @@ from . import lib, bsb22
 from .groth16 import (HasIcicle, Prove, ProvingKey, Proof, R1CSSolution, WithIcicleAcceleration, WithRandomness,
                       WithDevice, NewProverConfig, prove_msms, assemble, combine_shards, ConstraintSystem,
                       prove_msms_wires)
-from . import dump
+from . import dump, marshal
 
-__all__ = ["lib", "bsb22", "dump", "HasIcicle", "Prove", "ProvingKey", "Proof", "R1CSSolution", "WithIcicleAcceleration",
+__all__ = ["lib", "bsb22", "dump", "marshal", "HasIcicle", "Prove", "ProvingKey", "Proof", "R1CSSolution", "WithIcicleAcceleration",
            "WithRandomness", "WithDevice", "NewProverConfig", "prove_msms", "assemble", "combine_shards",
            "ConstraintSystem", "prove_msms_wires"]

@@ -119,6 +119,16 @@ class Proof:
             parts.append(self.CommitmentPok)
         return np.concatenate(parts).tobytes()
 
+    def write_to(self):
+        """Proof.WriteTo (marshal.go:30-35): compressed points."""
+        from . import marshal
+        return marshal.proof_write_to(self, raw=False)
+
+    def write_raw_to(self):
+        """Proof.WriteRawTo (marshal.go:37-42)."""
+        from . import marshal
+        return marshal.proof_write_to(self, raw=True)
+
 
 @dataclass
 class ProvingKey:

@@ -1,0 +1,205 @@
+"""Proof.WriteTo / WriteRawTo / ReadFrom (backend/groth16/bn254/marshal.go:30-92) for the proofs this package
+produces (wire formats).  Host-only code on Python ints; BN254.
+
+Order on the wire: Ar, Bs, Krs, Commitments (u32 big-endian count, then the points), CommitmentPok -- compressed
+by WriteTo, uncompressed by WriteRawTo; ReadFrom accepts either (the flag bits say which).  Point encodings are
+gnark-crypto's (ecc/bn254/marshal.go, restated [recollection]; the reference holds no proof fixture): coordinates
+big-endian canonical, E2 as A1 || A0, the two top bits of the first byte are the flag -- 00 uncompressed, 01
+infinity (compressed or not), 10 / 11 compressed with the lexicographically smallest / largest y (y > (p-1)/2;
+for E2 decided by A1 unless it is zero, then by A0).
+"""
+import struct
+
+import numpy as np
+
+from .bsb22 import FP_MOD
+
+_P = FP_MOD["bn254"]
+_RINV = pow(1 << 256, -1, _P)
+_R = (1 << 256) % _P
+_B1 = 3
+_B2 = None   # 3 / (9 + u), filled lazily
+M_MASK, M_UNCOMPRESSED, M_INFINITY, M_SMALLEST, M_LARGEST = 0xC0, 0x00, 0x40, 0x80, 0xC0
+
+
+def _from_limbs(limbs):
+    v = 0
+    for i, w in enumerate(limbs):
+        v |= int(w) << (64 * i)
+    return v * _RINV % _P
+
+
+def _to_limbs(v):
+    m = v * _R % _P
+    return [(m >> (64 * i)) & 0xFFFFFFFFFFFFFFFF for i in range(4)]
+
+
+def _coords(pt, n):
+    pt = np.asarray(pt, dtype=np.uint64).reshape(-1)
+    assert pt.size == 4 * n
+    return None if not pt.any() else [_from_limbs(pt[4 * i:4 * i + 4]) for i in range(n)]
+
+
+def _lex_largest(v):
+    return v > (_P - 1) // 2
+
+
+def _be(v):
+    return v.to_bytes(32, "big")
+
+
+def g1_encode(pt, raw=False):
+    c = _coords(pt, 2)
+    if c is None:
+        return bytes([M_INFINITY]) + bytes(63 if raw else 31)
+    if raw:
+        return _be(c[0]) + _be(c[1])
+    out = bytearray(_be(c[0]))
+    out[0] |= M_LARGEST if _lex_largest(c[1]) else M_SMALLEST
+    return bytes(out)
+
+
+def g2_encode(pt, raw=False):
+    c = _coords(pt, 4)          # X.A0 X.A1 Y.A0 Y.A1
+    if c is None:
+        return bytes([M_INFINITY]) + bytes(127 if raw else 63)
+    if raw:
+        return _be(c[1]) + _be(c[0]) + _be(c[3]) + _be(c[2])
+    out = bytearray(_be(c[1]) + _be(c[0]))
+    largest = _lex_largest(c[3]) if c[3] else _lex_largest(c[2])
+    out[0] |= M_LARGEST if largest else M_SMALLEST
+    return bytes(out)
+
+
+# ---- decompression: square roots in Fp (p = 3 mod 4) and Fp2 = Fp[u]/(u^2+1)
+def _fp_sqrt(a):
+    r = pow(a, (_P + 1) // 4, _P)
+    return r if r * r % _P == a % _P else None
+
+
+def _f2_mul(a, b):
+    return ((a[0] * b[0] - a[1] * b[1]) % _P, (a[0] * b[1] + a[1] * b[0]) % _P)
+
+
+def _f2_sqrt(a):
+    a0, a1 = a
+    if a1 == 0:
+        r = _fp_sqrt(a0)
+        if r is not None:
+            return (r, 0)
+        r = _fp_sqrt(-a0 % _P)
+        return None if r is None else (0, r)
+    s = _fp_sqrt((a0 * a0 + a1 * a1) % _P)          # norm
+    if s is None:
+        return None
+    half = pow(2, -1, _P)
+    x0 = _fp_sqrt((a0 + s) * half % _P)
+    if x0 is None:
+        x0 = _fp_sqrt((a0 - s) * half % _P)
+    if x0 is None or x0 == 0:
+        return None
+    x1 = a1 * pow(2 * x0, -1, _P) % _P
+    return (x0, x1) if _f2_mul((x0, x1), (x0, x1)) == (a0 % _P, a1 % _P) else None
+
+
+def _twist_b():
+    global _B2
+    if _B2 is None:
+        d = pow(9 * 9 + 1, -1, _P)                  # 1 / (9 + u) = (9 - u) / 82
+        _B2 = (3 * 9 * d % _P, -3 * d % _P)
+    return _B2
+
+
+def g1_decode(buf, off=0):
+    """(limb array, bytes consumed)."""
+    flag = buf[off] & M_MASK
+    if flag == M_INFINITY:
+        raise ValueError("g1_decode: use proof_read_from (the length of an encoded infinity depends on the encoding in use)")
+    if flag == M_UNCOMPRESSED:
+        x, y = int.from_bytes(buf[off:off + 32], "big"), int.from_bytes(buf[off + 32:off + 64], "big")
+        n = 64
+    else:
+        x = int.from_bytes(bytes([buf[off] & ~M_MASK & 0xFF]) + buf[off + 1:off + 32], "big")
+        y = _fp_sqrt((x * x * x + _B1) % _P)
+        if y is None:
+            raise ValueError("invalid compressed G1 point")
+        if _lex_largest(y) != (flag == M_LARGEST):
+            y = _P - y
+        n = 32
+    if x >= _P or y >= _P or (y * y - x * x * x - _B1) % _P:
+        raise ValueError("G1 point is not on the curve")
+    return np.array(_to_limbs(x) + _to_limbs(y), dtype=np.uint64), n
+
+
+def g2_decode(buf, off=0):
+    flag = buf[off] & M_MASK
+    if flag == M_INFINITY:
+        raise ValueError("g2_decode: use proof_read_from")
+    if flag == M_UNCOMPRESSED:
+        x1, x0, y1, y0 = (int.from_bytes(buf[off + 32 * i:off + 32 * i + 32], "big") for i in range(4))
+        n = 128
+    else:
+        x1 = int.from_bytes(bytes([buf[off] & ~M_MASK & 0xFF]) + buf[off + 1:off + 32], "big")
+        x0 = int.from_bytes(buf[off + 32:off + 64], "big")
+        x = (x0, x1)
+        b = _twist_b()
+        x3 = _f2_mul(_f2_mul(x, x), x)
+        y = _f2_sqrt(((x3[0] + b[0]) % _P, (x3[1] + b[1]) % _P))
+        if y is None:
+            raise ValueError("invalid compressed G2 point")
+        largest = _lex_largest(y[1]) if y[1] else _lex_largest(y[0])
+        if largest != (flag == M_LARGEST):
+            y = (-y[0] % _P, -y[1] % _P)
+        y0, y1 = y
+        n = 64
+    b = _twist_b()
+    x = (x0, x1)
+    x3 = _f2_mul(_f2_mul(x, x), x)
+    if _f2_mul((y0, y1), (y0, y1)) != ((x3[0] + b[0]) % _P, (x3[1] + b[1]) % _P):
+        raise ValueError("G2 point is not on the curve")
+    return np.array(_to_limbs(x0) + _to_limbs(x1) + _to_limbs(y0) + _to_limbs(y1), dtype=np.uint64), n
+
+
+def proof_write_to(proof, raw=False):
+    """Proof.WriteTo (compressed) / WriteRawTo (raw=True)."""
+    if len(np.asarray(proof.Ar).reshape(-1)) != 8:
+        raise ValueError("proof wire format is implemented for BN254")
+    out = [g1_encode(proof.Ar, raw), g2_encode(proof.Bs, raw), g1_encode(proof.Krs, raw),
+           struct.pack(">I", len(proof.Commitments))]
+    out += [g1_encode(c, raw) for c in proof.Commitments]
+    pok = proof.CommitmentPok if proof.CommitmentPok is not None else np.zeros(8, dtype=np.uint64)
+    out.append(g1_encode(pok, raw))
+    return b"".join(out)
+
+
+def proof_read_from(buf):
+    """Proof.ReadFrom: either encoding; returns (Proof, bytes read)."""
+    from .groth16 import Proof
+    # the encoding is uniform over a proof: Ar is never the point at infinity in a valid proof, so its flag tells
+    raw = (buf[0] & M_MASK) == M_UNCOMPRESSED
+    off = 0
+
+    def g1():
+        nonlocal off
+        if (buf[off] & M_MASK) == M_INFINITY:
+            off += 64 if raw else 32
+            return np.zeros(8, dtype=np.uint64)
+        pt, n = g1_decode(buf, off)
+        off += n
+        return pt
+
+    def g2():
+        nonlocal off
+        if (buf[off] & M_MASK) == M_INFINITY:
+            off += 128 if raw else 64
+            return np.zeros(16, dtype=np.uint64)
+        pt, n = g2_decode(buf, off)
+        off += n
+        return pt
+
+    ar, bs, krs = g1(), g2(), g1()
+    (count,) = struct.unpack(">I", buf[off:off + 4])
+    off += 4
+    commitments = [g1() for _ in range(count)]
+    pok = g1()
+    return Proof(Ar=ar, Bs=bs, Krs=krs, Commitments=commitments, CommitmentPok=pok), off
