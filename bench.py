@@ -336,6 +336,8 @@ def run_ours(args):
 
         def msms(W_t):
             torch.cuda.current_stream().synchronize()
+            # (g16_prove_msms_begin_dev could start the W MSMs here, under the distributed computeH; measured: 41.3 vs 40.4 ms
+            #  at N=2, 13.7 vs 13.8 at N=8 -- the GPUs are busy either way, and h arriving late leaves the H.Z MSM alone at the end)
             h_blk = gdist.compute_h_distributed(ctx, abc_work, n, rank, world)
             pts, st = ctx.prove_msms_dev(handle, W_t.data_ptr(), h_blk.data_ptr())
             return combine(pts), st

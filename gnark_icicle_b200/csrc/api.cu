@@ -55,6 +55,8 @@ struct g16_ctx {
     struct CommitKey { Bases basis, basis_exp_sigma; };   // pedersen.ProvingKey (setup.go:57)
     std::map<uint64_t, CommitKey> commit_keys;
     uint64_t next_pk = 1;
+    MsmPlan pend_plan[5];        // g16_prove_msms_begin_dev .. g16_prove_msms_dev: plans of the MSMs already in flight
+    uint64_t pend_pk = 0;        // 0 = nothing pending
     MsmWorkspace ws[5];
     DevBuf stage[4];             // host-pointer variants: staged inputs
     PinnedBuf file_stage[2];     // g16_pk_upload_from_file: double-buffered pread -> H2D
@@ -368,8 +370,10 @@ namespace {
 template <class Aff>
 void copy_out(void* dst, const Aff& p) { memcpy(dst, &p, sizeof(Aff)); }
 
+// phase 0: the whole device section.  phase 1: enqueue the four MSMs over W and return (they run while the caller
+// produces h, e.g. the distributed computeH with its all-to-alls); phase 2: enqueue the H.Z MSM, wait for all five, finish.
 void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* b_d, Fr::T* c_d, void* out_points,
-                  g16_stats* stats, uint64_t launches0, cudaEvent_t w_ready, bool h_given = false) {
+                  g16_stats* stats, uint64_t launches0, cudaEvent_t w_ready, bool h_given = false, int phase = 0) {
     cudaStream_t st = ctx->stream;
     NttDomain& dom = ctx->domain(pk.logn);
     cudaEvent_t* ev = ctx->ev;
@@ -384,30 +388,40 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
     auto pre = [&](int i) { return (ctx->msm_c == 0 && ctx->msm_precompute) ? pk.pre_c[i] : 0; };
     cudaStream_t sA = overlap ? ctx->aux[0] : st, sB = overlap ? ctx->aux[1] : st, sK = overlap ? ctx->aux[2] : st,
                  s2 = overlap ? ctx->aux[3] : st;
-    G16_CUDA(cudaEventRecord(ev[0], st));
-    if (overlap) {
-        cudaEvent_t ready = w_ready ? w_ready : ev[0];
-        for (int i = 0; i < 4; i++) G16_CUDA(cudaStreamWaitEvent(ctx->aux[i], ready, 0));
+    if (phase != 2) {
+        G16_CUDA(cudaEventRecord(ev[0], st));
+        if (overlap) {
+            cudaEvent_t ready = w_ready ? w_ready : ev[0];
+            for (int i = 0; i < 4; i++) G16_CUDA(cudaStreamWaitEvent(ctx->aux[i], ready, 0));
+        }
+    } else {
+        for (int i = 0; i < 5; i++) plan[i] = ctx->pend_plan[i];
     }
     auto run = [&](int idx, cudaStream_t s, auto&& fn) {
         G16_CUDA(cudaEventRecord(ev[1 + idx], s));
         fn(s);
         G16_CUDA(cudaEventRecord(ev[6 + idx], s));
     };
-    run(G16_OUT_BS2, s2, [&](cudaStream_t s) {
+    if (phase != 2) run(G16_OUT_BS2, s2, [&](cudaStream_t s) {
         msm_g2_enqueue(ctx->ws[G16_OUT_BS2], W_d, pk.map_b.as<uint32_t>(), pk.g2_b.as<G2::Aff>(), pk.n_b2, ctx->msm_c, ctx->msm_waves, s, plan[4], &ms[4], overlap ? ctx->tails[4] : nullptr, pre(G16_OUT_BS2)); });
-    G16_CUDA(cudaEventRecord(ev[12], st));
-    if (!h_given) compute_h_device(dom, a_d, b_d, c_d, st);   // h (bit-reversed) in a_d; h_given: a_d is this shard's block of h
-    G16_CUDA(cudaEventRecord(ev[13], st));
-    run(G16_OUT_AR, sA, [&](cudaStream_t s) {
+    if (phase != 1) {
+        G16_CUDA(cudaEventRecord(ev[12], st));
+        if (!h_given) compute_h_device(dom, a_d, b_d, c_d, st);   // h (bit-reversed) in a_d; h_given: a_d is this shard's block of h
+        G16_CUDA(cudaEventRecord(ev[13], st));
+    }
+    if (phase != 2) run(G16_OUT_AR, sA, [&](cudaStream_t s) {
         msm_g1_enqueue(ctx->ws[G16_OUT_AR], W_d, pk.map_a.as<uint32_t>(), pk.g1_a.as<G1::Aff>(), pk.n_a, ctx->msm_c, ctx->msm_waves, s, plan[0], &ms[0], overlap ? ctx->tails[0] : nullptr, pre(G16_OUT_AR)); });
-    run(G16_OUT_KRS_HZ, st, [&](cudaStream_t s) {
+    if (phase != 1) run(G16_OUT_KRS_HZ, st, [&](cudaStream_t s) {
         msm_g1_enqueue(ctx->ws[G16_OUT_KRS_HZ], a_d + (h_given ? 0 : pk.z_off), nullptr, pk.g1_z.as<G1::Aff>(), pk.n_z, ctx->msm_c, ctx->msm_waves, s, plan[3], &ms[3], overlap ? ctx->tails[3] : nullptr, pre(G16_OUT_KRS_HZ)); });
-    run(G16_OUT_BS1, sB, [&](cudaStream_t s) {
+    if (phase != 2) run(G16_OUT_BS1, sB, [&](cudaStream_t s) {
         msm_g1_enqueue(ctx->ws[G16_OUT_BS1], W_d, pk.map_b.as<uint32_t>(), pk.g1_b.as<G1::Aff>(), pk.n_b, ctx->msm_c, ctx->msm_waves, s, plan[1], &ms[1], overlap ? ctx->tails[1] : nullptr, pre(G16_OUT_BS1),
                        pk.n_b == pk.n_b2 ? &ctx->ws[G16_OUT_BS2] : nullptr); });   // same scalars, same map: reuse the G2 MSM's sort
-    run(G16_OUT_KRS_K, sK, [&](cudaStream_t s) {
+    if (phase != 2) run(G16_OUT_KRS_K, sK, [&](cudaStream_t s) {
         msm_g1_enqueue(ctx->ws[G16_OUT_KRS_K], W_d, pk.map_k.as<uint32_t>(), pk.g1_k.as<G1::Aff>(), pk.n_k, ctx->msm_c, ctx->msm_waves, s, plan[2], &ms[2], overlap ? ctx->tails[2] : nullptr, pre(G16_OUT_KRS_K)); });
+    if (phase == 1) {
+        for (int i = 0; i < 5; i++) ctx->pend_plan[i] = plan[i];
+        return;
+    }
     if (overlap) {
         const int aux_of[4] = {G16_OUT_AR, G16_OUT_BS1, G16_OUT_KRS_K, G16_OUT_BS2};
         for (int i = 0; i < 4; i++) G16_CUDA(cudaStreamWaitEvent(st, ev[6 + aux_of[i]], 0));
@@ -1155,7 +1169,20 @@ int g16_prove_msms_dev(g16_ctx* ctx, uint64_t pk_handle, const void* W_d, const 
         if (!W_d || !h_local_d || !out_points) throw std::runtime_error("null argument");
         uint64_t l0 = launch_counter().load();
         if (stats) memset(stats, 0, sizeof(*stats));
-        prove_device(ctx, it->second, (const Fr::T*)W_d, (Fr::T*)h_local_d, nullptr, nullptr, out_points, stats, l0, nullptr, true);
+        const bool pending = ctx->pend_pk == pk_handle;
+        if (ctx->pend_pk && !pending) throw std::runtime_error("g16_prove_msms_begin_dev is pending for another proving key");
+        ctx->pend_pk = 0;
+        prove_device(ctx, it->second, (const Fr::T*)W_d, (Fr::T*)h_local_d, nullptr, nullptr, out_points, stats, l0, nullptr, true, pending ? 2 : 0);
+    });
+}
+int g16_prove_msms_begin_dev(g16_ctx* ctx, uint64_t pk_handle, const void* W_d) {
+    return guarded(ctx, [&] {
+        auto it = ctx->pks.find(pk_handle);
+        if (it == ctx->pks.end()) throw std::runtime_error("unknown proving-key handle");
+        if (!W_d) throw std::runtime_error("null argument");
+        if (ctx->pend_pk) throw std::runtime_error("g16_prove_msms_begin_dev: a previous begin has not been finished by g16_prove_msms_dev");
+        prove_device(ctx, it->second, (const Fr::T*)W_d, nullptr, nullptr, nullptr, nullptr, nullptr, 0, nullptr, true, 1);
+        ctx->pend_pk = pk_handle;
     });
 }
 

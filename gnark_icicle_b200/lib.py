@@ -89,7 +89,7 @@ SYMBOLS = [
     "g16_commitment_key_upload", "g16_commitment_key_free", "g16_commit",
     "g16_msm_g1", "g16_msm_g1_dev", "g16_msm_g2", "g16_msm_g2_dev", "g16_ntt", "g16_ntt_dev",
     "g16_compute_h", "g16_compute_h_dev", "g16_fr_mul_vec",
-    "g16_dist_ntt_stages_dev", "g16_dist_permute_dev", "g16_dist_pointwise_h_dev", "g16_prove_msms_dev",
+    "g16_dist_ntt_stages_dev", "g16_dist_permute_dev", "g16_dist_pointwise_h_dev", "g16_prove_msms_dev", "g16_prove_msms_begin_dev",
     "g16_g1_fixed_base_mul", "g16_g2_fixed_base_mul", "g16_g1_fixed_base_mul_dev", "g16_g2_fixed_base_mul_dev",
     "g16_g1_add", "g16_g2_add", "g16_g1_scalar_mul", "g16_g2_scalar_mul", "g16_imad_peak", "g16_pipe_rates", "g16_ctx_stream",
 ]
@@ -408,6 +408,10 @@ class Context:
 
     def dist_pointwise_h_dev(self, abc_ptr, n_local, n_global):
         self._check(self._lib.g16_dist_pointwise_h_dev(self._h, _ptr(abc_ptr), u64(n_local), u64(n_global)), "g16_dist_pointwise_h_dev")
+
+    def prove_msms_begin_dev(self, pk_handle, W_ptr):
+        """start the four MSMs over W; they run while the caller computes h; finish with prove_msms_dev."""
+        self._check(self._lib.g16_prove_msms_begin_dev(self._h, u64(pk_handle), _ptr(W_ptr)), "g16_prove_msms_begin_dev")
 
     def prove_msms_dev(self, pk_handle, W_ptr, h_local_ptr):
         out = np.zeros(self.prove_out_words, dtype=np.uint64)

@@ -207,6 +207,10 @@ int g16_dist_pointwise_h_dev(g16_ctx* ctx, void* abc_d, uint64_t n_local, uint64
 /* the five MSMs only; h_local_d = this shard's block of h (domain_n/shard_count elements, bit-reversed order) */
 int g16_prove_msms_dev(g16_ctx* ctx, uint64_t pk_handle, const void* W_d, const void* h_local_d, void* out_points,
                        g16_stats* stats);
+/* Optional first half of g16_prove_msms_dev: enqueues the four MSMs over W (ar, bs1, krs_k, bs2) on their own streams and
+ * returns at once, so that they run while the caller produces h (the distributed computeH and its all-to-alls).  The next
+ * g16_prove_msms_dev on the same key then only adds the H.Z MSM and collects all five.  W_d must stay valid until then. */
+int g16_prove_msms_begin_dev(g16_ctx* ctx, uint64_t pk_handle, const void* W_d);
 
 /* out[i] = a[i] * b[i] in Fr (icicle.go:500 PolyOps building block; minimum parity slice) */
 int g16_fr_mul_vec(g16_ctx* ctx, const void* a, const void* b, uint64_t n, void* out);

@@ -8,7 +8,7 @@ import torch
 from helpers import ChainCase, fr_rand, assert_limbs_equal
 from oracle import cpu as ocpu
 import gnark_icicle_b200 as g16
-from gnark_icicle_b200 import dist as gdist
+from gnark_icicle_b200 import dist as gdist, lib
 
 pytestmark = pytest.mark.gpu
 
@@ -54,6 +54,12 @@ def test_sharded_prove_with_distributed_h(ctx):
         h = ctx.pk_upload(pk.domain_n, pk.g1_a, pk.g1_b, pk.g1_k, pk.g1_z, pk.g2_b, pk.infinity_a, pk.infinity_b, pk.nb_wires,
                           shard_index=r, shard_count=world)
         pts, st = ctx.prove_msms_dev(h, W_d.data_ptr(), blocks[r].data_ptr())
+        # the two-call form (the W MSMs started first, h handed in later) gives the same points
+        ctx.prove_msms_begin_dev(h, W_d.data_ptr())
+        with pytest.raises(lib.G16Error, match="has not been finished"):
+            ctx.prove_msms_begin_dev(h, W_d.data_ptr())
+        pts2, _ = ctx.prove_msms_dev(h, W_d.data_ptr(), blocks[r].data_ptr())
+        assert np.array_equal(pts, pts2)
         outs.append(pts)
         ctx.pk_free(h)
     assert_limbs_equal(g16.combine_shards(outs), whole, "sharded MSMs over distributed h")
