@@ -6,6 +6,7 @@
   bsb22.py     BSB22 commitments on that path (hint override, commitment keys on the device, folded PoK)
   dump.py      ProvingKey.WriteDump / ReadDump and the direct file -> device key load
   marshal.py   Proof.WriteTo / WriteRawTo / ReadFrom (compressed and raw point encodings, BN254)
+  witness.py   witness.Witness binary protocol
 
 The directory ``gnark-icicle_b200`` at the repo root is a link to this package (a hyphen is not importable).
 """
@@ -13,8 +14,8 @@ from . import lib, bsb22
 from .groth16 import (HasIcicle, Prove, ProvingKey, Proof, R1CSSolution, WithIcicleAcceleration, WithRandomness,
                       WithDevice, NewProverConfig, prove_msms, assemble, combine_shards, ConstraintSystem,
                       prove_msms_wires)
-from . import dump, marshal
+from . import dump, marshal, witness
 
-__all__ = ["lib", "bsb22", "dump", "marshal", "HasIcicle", "Prove", "ProvingKey", "Proof", "R1CSSolution", "WithIcicleAcceleration",
+__all__ = ["lib", "bsb22", "dump", "marshal", "witness", "HasIcicle", "Prove", "ProvingKey", "Proof", "R1CSSolution", "WithIcicleAcceleration",
            "WithRandomness", "WithDevice", "NewProverConfig", "prove_msms", "assemble", "combine_shards",
            "ConstraintSystem", "prove_msms_wires"]
