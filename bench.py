@@ -330,6 +330,9 @@ def run_ours(args):
         abc_master = torch.stack([sd[k][rank::world] for k in ("a", "b", "c")]).contiguous()
         abc_work = torch.empty_like(abc_master)
         abc_pin = abc_master.cpu().pin_memory()
+        # G16_DIST_ASYNC=1: stream-ordered distributed computeH (no host waits between its steps).  Measured at N=2:
+        # 40.9 vs 40.5 ms host-synchronised -- the GPU is the bottleneck, not the host -- so the plain form is the default
+        dist_stream = ext if os.environ.get("G16_DIST_ASYNC") else None
         W_stage = torch.zeros_like(sd["W"])
         w_lo, w_hi = ctx.pk_wire_range(handle)           # the wires this rank's shard of the A, B, K bases reads
         del wa, wb, wc
@@ -338,7 +341,7 @@ def run_ours(args):
             torch.cuda.current_stream().synchronize()
             # (g16_prove_msms_begin_dev could start the W MSMs here, under the distributed computeH; measured: 41.3 vs 40.4 ms
             #  at N=2, 13.7 vs 13.8 at N=8 -- the GPUs are busy either way, and h arriving late leaves the H.Z MSM alone at the end)
-            h_blk = gdist.compute_h_distributed(ctx, abc_work, n, rank, world)
+            h_blk = gdist.compute_h_distributed(ctx, abc_work, n, rank, world, stream=dist_stream)
             pts, st = ctx.prove_msms_dev(handle, W_t.data_ptr(), h_blk.data_ptr())
             return combine(pts), st
 
@@ -354,6 +357,20 @@ def run_ours(args):
             st["h2d_bytes"] = (w_hi - w_lo) * W_stage.shape[1] * 8 + abc_pin.numel() * 8
             return pts, st
 
+    if world > 1:
+        # one-time check of the multi-rank path: this rank's block of the distributed h == the same block of h computed
+        # by this GPU alone from the full a, b, c
+        abc_work.copy_(abc_master)
+        torch.cuda.synchronize()
+        h_blk = gdist.compute_h_distributed(ctx, abc_work, n, rank, world, stream=dist_stream)
+        torch.cuda.synchronize()
+        full = [sd[k].clone() for k in ("a", "b", "c")]
+        torch.cuda.synchronize()                     # the clones were made on torch's stream, computeH runs on the library's
+        ctx.compute_h_dev(full[0].data_ptr(), full[1].data_ptr(), full[2].data_ptr(), n)
+        torch.cuda.synchronize()
+        if not torch.equal(h_blk, full[0][rank * n_local:(rank + 1) * n_local]):
+            raise SystemExit(f"bench.py: rank {rank}: distributed computeH differs from the single-GPU h")
+        del full
     l0 = lib.kernel_launch_count(args.curve)
     with ClockSampler(local) as clk:
         ms_dev, (pts_dev, st) = timed(torch, ext, step_dev, args.steps, args.warmup, world, dist)

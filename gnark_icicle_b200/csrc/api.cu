@@ -62,6 +62,7 @@ struct g16_ctx {
     PinnedBuf file_stage[2];     // g16_pk_upload_from_file: double-buffered pread -> H2D
     DevBuf fb_table_g1, fb_table_g2;
     int msm_c = 0, msm_waves = 4;
+    int dist_sync = 1;           // g16_dist_*_dev return after the stream has drained (0: stream-ordered, caller synchronises)
     int msm_precompute = 1;      // keep 2^(c j) multiples of every key base resident (one shared bucket set, larger windows)
 
     NttDomain& domain(int logn) {
@@ -240,6 +241,7 @@ int g16_ctx_set(g16_ctx* ctx, const char* key, int64_t value) {
     else if (k == "msm_waves") ctx->msm_waves = (int)value;
     else if (k == "streams") ctx->streams = (int)value;
     else if (k == "msm_precompute") ctx->msm_precompute = (int)value;
+    else if (k == "dist_sync") ctx->dist_sync = (int)value;
     else { ctx->err = "unknown tunable " + k; return 1; }
     return 0;
 }
@@ -1143,14 +1145,14 @@ int g16_dist_ntt_stages_dev(g16_ctx* ctx, void* data_d, int count, uint64_t n_gl
         Fr::T* p = (Fr::T*)data_d;
         NttBatch b{{p, p + (count > 1 ? n_local : 0), p + (count > 2 ? 2 * n_local : 0)}, count};
         ntt_dist_stages(d, b, (NttTable)table, dif != 0, g, (uint32_t)rank, cyclic != 0, split, ctx->stream);
-        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (ctx->dist_sync) G16_CUDA(cudaStreamSynchronize(ctx->stream));
     });
 }
 int g16_dist_permute_dev(g16_ctx* ctx, const void* src_d, void* dst_d, int count, uint64_t n_local, int world, int block_layout, int to_wire) {
     return guarded(ctx, [&] {
         if (world < 1 || n_local % (uint64_t)world) throw std::runtime_error("g16_dist_permute_dev: n_local must be a multiple of world");
         ntt_dist_permute((const Fr::T*)src_d, (Fr::T*)dst_d, count, n_local, (uint32_t)world, block_layout, to_wire, ctx->stream);
-        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (ctx->dist_sync) G16_CUDA(cudaStreamSynchronize(ctx->stream));
     });
 }
 int g16_dist_pointwise_h_dev(g16_ctx* ctx, void* abc_d, uint64_t n_local, uint64_t n_global) {
@@ -1159,7 +1161,7 @@ int g16_dist_pointwise_h_dev(g16_ctx* ctx, void* abc_d, uint64_t n_local, uint64
         NttDomain& d = ctx->domain(ilog2_ceil(n_global));
         Fr::T* p = (Fr::T*)abc_d;
         fr_pointwise_h(p, p + n_local, p + 2 * n_local, n_local, d.h_c1, d.h_c2, ctx->stream);
-        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (ctx->dist_sync) G16_CUDA(cudaStreamSynchronize(ctx->stream));
     });
 }
 int g16_prove_msms_dev(g16_ctx* ctx, uint64_t pk_handle, const void* W_d, const void* h_local_d, void* out_points, g16_stats* stats) {

@@ -73,9 +73,30 @@ def compute_h_steps(ctx, abc, n, rank, world):
     return abc[0]
 
 
-def compute_h_distributed(ctx, abc, n, rank, world, group=None):
-    """NCCL driver of compute_h_steps (torch.distributed must be initialised when world > 1)."""
+def compute_h_distributed(ctx, abc, n, rank, world, group=None, stream=None):
+    """NCCL driver of compute_h_steps (torch.distributed must be initialised when world > 1).
+
+    stream: a torch stream wrapping g16_ctx_stream(ctx) (torch.cuda.ExternalStream).  When given, the whole pipeline is
+    stream-ordered: the library calls only enqueue ("dist_sync" 0), the all-to-alls are issued with that stream current
+    (NCCL orders itself after the work already on it and the stream waits for NCCL), and the host never waits -- the MSM
+    call that consumes h runs on the same stream.  Without it every step is followed by a host synchronisation."""
     import torch.distributed as dist
+    if stream is not None:
+        ctx.set("dist_sync", 0)
+        try:
+            with torch.cuda.stream(stream):
+                gen = compute_h_steps(ctx, abc, n, rank, world)
+                try:
+                    while True:
+                        send, recv = next(gen)
+                        if world > 1:
+                            dist.all_to_all_single(recv, send, group=group)
+                        else:
+                            recv.copy_(send)
+                except StopIteration as done:
+                    return done.value
+        finally:
+            ctx.set("dist_sync", 1)
     gen = compute_h_steps(ctx, abc, n, rank, world)
     try:
         while True:

@@ -190,6 +190,9 @@ int g16_compute_h(g16_ctx* ctx, const void* a, const void* b, const void* c, uin
 /* a_d,b_d,c_d: domain_n elements each (zero padded); h is left in a_d, b_d/c_d are clobbered */
 int g16_compute_h_dev(g16_ctx* ctx, void* a_d, void* b_d, void* c_d, uint64_t domain_n);
 
+/* The three g16_dist_*_dev calls below return after ctx's stream has drained, unless g16_ctx_set(ctx, "dist_sync", 0):
+ * then they only enqueue, and the caller orders its exchanges against g16_ctx_stream(ctx) (e.g. by issuing the NCCL
+ * all-to-all on that same stream). */
 /* ---- distributed computeH (one context per GPU; the caller moves data between ranks, e.g. NCCL all-to-all) ----
  * A size-n transform over world = 2^g ranks is split at global stage `split` (g <= split <= log2(n) - g): stages
  * with half-size >= 2^split run on the CYCLIC distribution (rank r holds positions q*world + r), the others on
