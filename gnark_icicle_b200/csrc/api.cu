@@ -858,6 +858,18 @@ int g16_compute_h(g16_ctx* ctx, const void* a, const void* b, const void* c, uin
     });
 }
 
+// No counterpart in the reference: computeH for callers that may not allocate device memory (see ntt.cu).  The only
+// scratch is the library's static device array; this call performs no cudaMalloc / cudaFree.
+int g16_compute_h_noalloc_dev(g16_ctx* ctx, const void* a_d, const void* b_d, const void* c_d, uint64_t n_constraints,
+                              uint64_t domain_n, void* h_out_d) {
+    return guarded(ctx, [&] {
+        if (!h_out_d || (n_constraints && (!a_d || !b_d || !c_d))) throw std::runtime_error("null argument");
+        compute_h_noalloc(ctx->device, (const Fr::T*)a_d, (const Fr::T*)b_d, (const Fr::T*)c_d, n_constraints, domain_n,
+                          (Fr::T*)h_out_d, ctx->stream);
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+
 int g16_fr_mul_vec(g16_ctx* ctx, const void* a, const void* b, uint64_t n, void* out) {
     return guarded(ctx, [&] {
         upload(ctx->stage[0], a, n * 32, ctx->stream);

@@ -82,23 +82,28 @@ void NttDomain::init(int logn_) {
     h_c2 = Fr::mul(den, Fr::sqr(n_inv));
 }
 
-const Fr::T* NttDomain::table(NttTable t, cudaStream_t st) {
-    if (tw[t]) return tw[t];
-    if (logn == 0) { G16_CUDA(cudaMalloc(&tw[t], 32)); return tw[t]; }
+// fills p[0, n-1) with table t of domain d (layout in ntt.cuh); enqueues one kernel, allocates nothing
+static void fill_table(const NttDomain& d, NttTable t, Fr::T* p, cudaStream_t st) {
     StageParams sp;
-    Fr::T w = (t == TW_FWD || t == TW_COSET_FWD) ? omega : omega_inv;
-    Fr::T g = (t == TW_COSET_FWD) ? coset_gen : (t == TW_COSET_INV ? coset_inv : Fr::one());
+    Fr::T w = (t == TW_FWD || t == TW_COSET_FWD) ? d.omega : d.omega_inv;
+    Fr::T g = (t == TW_COSET_FWD) ? d.coset_gen : (t == TW_COSET_INV ? d.coset_inv : Fr::one());
     // stage s = logn-1 uses w and g; each lower stage squares both
-    for (int s = logn - 1; s >= 0; s--) {
+    for (int s = d.logn - 1; s >= 0; s--) {
         sp.root[s] = w; sp.shift[s] = g;
         w = Fr::sqr(w); g = Fr::sqr(g);
     }
-    for (int s = logn; s < 28; s++) { sp.root[s] = Fr::one(); sp.shift[s] = Fr::one(); }
+    for (int s = d.logn; s < 28; s++) { sp.root[s] = Fr::one(); sp.shift[s] = Fr::one(); }
+    uint64_t threads = (d.n + 7) / 8;
+    k_build_table<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(p, d.n, sp);
+    G16_LAUNCH_CHECK();
+}
+
+const Fr::T* NttDomain::table(NttTable t, cudaStream_t st) {
+    if (tw[t]) return tw[t];
+    if (logn == 0) { G16_CUDA(cudaMalloc(&tw[t], 32)); return tw[t]; }
     Fr::T* p = nullptr;
     G16_CUDA(cudaMalloc(&p, (size_t)n * sizeof(Fr::T)));
-    uint64_t threads = (n + 7) / 8;
-    k_build_table<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(p, n, sp);
-    G16_LAUNCH_CHECK();
+    fill_table(*this, t, p, st);
     tw[t] = p;
     return p;
 }
@@ -342,6 +347,54 @@ void compute_h_device(NttDomain& d, Fr::T* a, Fr::T* b, Fr::T* c, cudaStream_t s
     fr_pointwise_h(a, b, c, d.n, d.h_c1, d.h_c2, st);
     NttBatch one{{a, a, a}, 1};
     ntt_dif(d, one, TW_COSET_INV, st);    // h coefficients, bit-reversed order
+}
+
+// ------------------------------------------------------------------ computeH without any device allocation
+// For callers that may not allocate (CUDA graph capture, tight serving loops): the padded working copies of a, b, c
+// and the three twiddle tables live in a file-scope device array instead of cudaMalloc'ed buffers.  The array is
+// shared by every call on the device (calls that overlap on the GPU race) and keeps the previous call's contents:
+// everything a call reads from it is (re)written by that call first -- the tables are rebuilt, the padding rows
+// [n_constraints, n) are cleared.  No counterpart in the reference.
+constexpr uint64_t NOALLOC_N = 1ull << 16;                 // G16_NOALLOC_MAX_DOMAIN (include/g16b200.h)
+// [a | b | c | TW_INV | TW_COSET_FWD | TW_COSET_INV], NOALLOC_N Fr each: 12 MiB per device (per curve)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[6 * NOALLOC_N * sizeof(Fr::T)];
+
+// device address of the array, resolved once per device with that device current (in host code the array's name is
+// only a stand-in for the symbol, not an address a kernel can use)
+static Fr::T* noalloc_scratch(int device) {
+    static std::mutex mu;
+    static Fr::T* ptr[64] = {};
+    if (device < 0 || device >= 64) throw std::runtime_error("compute_h_noalloc: device ordinal out of range");
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptr[device]) {
+        void* p = nullptr;
+        G16_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        ptr[device] = reinterpret_cast<Fr::T*>(p);
+    }
+    return ptr[device];
+}
+
+void compute_h_noalloc(int device, const Fr::T* a, const Fr::T* b, const Fr::T* c, uint64_t n_constraints, uint64_t n,
+                       Fr::T* h_out, cudaStream_t st) {
+    if (!n || (n & (n - 1))) throw std::runtime_error("compute_h_noalloc: domain_n must be a power of two");
+    if (n > NOALLOC_N) throw std::runtime_error("compute_h_noalloc: domain_n " + std::to_string(n) + " exceeds the static scratch (maximum 2^16 = " + std::to_string(NOALLOC_N) + "); use g16_compute_h_dev");
+    if (n_constraints > n) throw std::runtime_error("compute_h_noalloc: more constraints than the domain holds");
+    Fr::T* base = noalloc_scratch(device);
+    NttDomain d;                     // host constants only; its tables point into the static array
+    d.init(ilog2_ceil(n));
+    const Fr::T* src[3] = {a, b, c};
+    Fr::T* w[3] = {base, base + NOALLOC_N, base + 2 * NOALLOC_N};
+    for (int i = 0; i < 3; i++) {
+        if (n_constraints) G16_CUDA(cudaMemcpyAsync(w[i], src[i], (size_t)n_constraints * sizeof(Fr::T), cudaMemcpyDeviceToDevice, st));
+        if (n > n_constraints) G16_CUDA(cudaMemsetAsync(w[i] + n_constraints, 0, (size_t)(n - n_constraints) * sizeof(Fr::T), st));
+    }
+    const NttTable tabs[3] = {TW_INV, TW_COSET_FWD, TW_COSET_INV};
+    for (int i = 0; i < 3; i++) {
+        d.tw[tabs[i]] = base + (3 + i) * NOALLOC_N;
+        if (d.logn > 0) fill_table(d, tabs[i], d.tw[tabs[i]], st);
+    }
+    compute_h_device(d, w[0], w[1], w[2], st);
+    G16_CUDA(cudaMemcpyAsync(h_out, w[0], (size_t)n * sizeof(Fr::T), cudaMemcpyDeviceToDevice, st));
 }
 
 }  // namespace g16

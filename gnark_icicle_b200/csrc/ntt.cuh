@@ -47,6 +47,10 @@ void fr_pointwise_h(Fr::T* a, const Fr::T* b, const Fr::T* c, uint64_t n, const 
 // computeH on device: a,b,c are n-element device arrays (zero padded); result (bit-reversed order) lands in a
 void compute_h_device(NttDomain& d, Fr::T* a, Fr::T* b, Fr::T* c, cudaStream_t st);
 void fr_mul_vec(Fr::T* out, const Fr::T* a, const Fr::T* b, uint64_t n, cudaStream_t st);
+// computeH with all scratch in a static device array (n <= 2^16): no cudaMalloc / cudaFree; a, b, c (n_constraints
+// elements each) are left untouched, h_out receives n elements in bit-reversed order.  See ntt.cu.
+void compute_h_noalloc(int device, const Fr::T* a, const Fr::T* b, const Fr::T* c, uint64_t n_constraints, uint64_t n,
+                       Fr::T* h_out, cudaStream_t st);
 
 // distributed building blocks (see ntt.cu)
 void ntt_dist_stages(NttDomain& d, const NttBatch& b, NttTable t, bool dif, int world_log, uint32_t rank, bool cyclic, int split, cudaStream_t st);

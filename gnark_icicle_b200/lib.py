@@ -88,7 +88,7 @@ SYMBOLS = [
     "g16_bases_upload", "g16_bases_free", "g16_msm_resident_dev", "g16_msm_resident",
     "g16_commitment_key_upload", "g16_commitment_key_free", "g16_commit",
     "g16_msm_g1", "g16_msm_g1_dev", "g16_msm_g2", "g16_msm_g2_dev", "g16_ntt", "g16_ntt_dev",
-    "g16_compute_h", "g16_compute_h_dev", "g16_fr_mul_vec",
+    "g16_compute_h", "g16_compute_h_dev", "g16_compute_h_noalloc_dev", "g16_fr_mul_vec",
     "g16_dist_ntt_stages_dev", "g16_dist_permute_dev", "g16_dist_pointwise_h_dev", "g16_prove_msms_dev", "g16_prove_msms_begin_dev",
     "g16_g1_fixed_base_mul", "g16_g2_fixed_base_mul", "g16_g1_fixed_base_mul_dev", "g16_g2_fixed_base_mul_dev",
     "g16_g1_add", "g16_g2_add", "g16_g1_scalar_mul", "g16_g2_scalar_mul", "g16_imad_peak", "g16_pipe_rates", "g16_ctx_stream",
@@ -255,6 +255,11 @@ class Context:
 
     def compute_h_dev(self, a_ptr, b_ptr, c_ptr, domain_n):
         self._check(self._lib.g16_compute_h_dev(self._h, _ptr(a_ptr), _ptr(b_ptr), _ptr(c_ptr), u64(domain_n)), "g16_compute_h_dev")
+
+    def compute_h_noalloc_dev(self, a_ptr, b_ptr, c_ptr, n_constraints, domain_n, h_out_ptr):
+        """computeH with the library's static device scratch only (no device allocation); domain_n <= 2^16."""
+        self._check(self._lib.g16_compute_h_noalloc_dev(self._h, _ptr(a_ptr), _ptr(b_ptr), _ptr(c_ptr), u64(n_constraints),
+                                                        u64(domain_n), _ptr(h_out_ptr)), "g16_compute_h_noalloc_dev")
 
     def g1_fixed_base_mul_dev(self, scalars_ptr, n, out_ptr):
         self._check(self._lib.g16_g1_fixed_base_mul_dev(self._h, _ptr(scalars_ptr), u64(n), _ptr(out_ptr)), "g16_g1_fixed_base_mul_dev")

@@ -190,6 +190,19 @@ int g16_compute_h(g16_ctx* ctx, const void* a, const void* b, const void* c, uin
 /* a_d,b_d,c_d: domain_n elements each (zero padded); h is left in a_d, b_d/c_d are clobbered */
 int g16_compute_h_dev(g16_ctx* ctx, void* a_d, void* b_d, void* c_d, uint64_t domain_n);
 
+/* NO COUNTERPART IN THE REFERENCE -- added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).  computeH like
+ * g16_compute_h_dev, but every byte of scratch (the zero-padded working copies of a, b, c and the three twiddle
+ * tables) lives in a static device array inside the library: 6 x G16_NOALLOC_MAX_DOMAIN x 32 B = 12 MiB, held by
+ * every GPU that loads the library until the process exits.  The call performs no cudaMalloc, cudaFree or other
+ * allocating routine.  a_d, b_d, c_d: n_constraints Fr each on the context's GPU, left untouched (no padding needed);
+ * h_out_d: domain_n Fr, bit-reversed order, must not overlap the inputs.  domain_n > G16_NOALLOC_MAX_DOMAIN is
+ * rejected with an error.  Every call on a GPU shares the one array: calls that overlap on the GPU (two contexts,
+ * two threads) race -- serialise them.  Returns after the context's stream has drained. */
+#define G16_NOALLOC_MAX_DOMAIN 65536
+int g16_compute_h_noalloc_dev(g16_ctx* ctx, const void* a_d, const void* b_d, const void* c_d, uint64_t n_constraints,
+                              uint64_t domain_n, void* h_out_d);
+
 /* The three g16_dist_*_dev calls below return after ctx's stream has drained, unless g16_ctx_set(ctx, "dist_sync", 0):
  * then they only enqueue, and the caller orders its exchanges against g16_ctx_stream(ctx) (e.g. by issuing the NCCL
  * all-to-all on that same stream). */
