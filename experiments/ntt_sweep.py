@@ -1,4 +1,4 @@
-"""tunes the NTT tile shape: prints ms for a 2^22 / 2^24 coset DIT under G16_NTT_LOG_TILE / G16_NTT_LOG_COLS (env, read at first use)."""
+"""tunes the NTT tile shape: prints ms for a 2^22 / 2^24 coset DIT for the tile shape compiled into ntt.cu (ntt_log_tile / ntt_log_cols: edit, rebuild, rerun)."""
 import os, sys, json
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -17,4 +17,4 @@ for logn in (22, 24):
         e0.record(ext); ctx.ntt_dev(x.data_ptr(), m, False, True, 1); e1.record(ext); torch.cuda.synchronize()
         best = min(best, e0.elapsed_time(e1))
     out[logn] = round(best, 3)
-print(os.environ.get("G16_NTT_LOG_TILE"), os.environ.get("G16_NTT_LOG_COLS"), json.dumps(out))
+print(json.dumps(out))

@@ -1,9 +1,11 @@
-"""resident-bases G1 MSM time against the window of the table (G16_PRE_C, read once per process): run once per c."""
+"""resident-bases G1 MSM time against the window of the table: python experiments/pre_c_sweep.py <c> (g16_ctx_set "msm_pre_c")."""
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 from gnark_icicle_b200 import lib
 ctx = lib.Context(0)
+C = int(sys.argv[1]) if len(sys.argv) > 1 else 0
+ctx.set("msm_pre_c", C)
 gen = torch.Generator(device="cuda"); gen.manual_seed(1)
 ext = torch.cuda.ExternalStream(ctx.stream)
 for logn in (17, 18, 19, 20, 21):
@@ -22,5 +24,5 @@ for logn in (17, 18, 19, 20, 21):
         ctx.msm_resident_dev(h, s.data_ptr())
     e1.record(ext)
     torch.cuda.synchronize()
-    print(f"c={os.environ.get('G16_PRE_C', 'auto')} 2^{logn}: {e0.elapsed_time(e1) / 5:.3f} ms")
+    print(f"c={C or 'auto'} 2^{logn}: {e0.elapsed_time(e1) / 5:.3f} ms")
     ctx.bases_free(h)

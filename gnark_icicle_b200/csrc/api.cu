@@ -64,6 +64,7 @@ struct g16_ctx {
     int msm_c = 0, msm_waves = 4;
     int dist_sync = 1;           // g16_dist_*_dev return after the stream has drained (0: stream-ordered, caller synchronises)
     int msm_precompute = 1;      // keep 2^(c j) multiples of every key base resident (one shared bucket set, larger windows)
+    int msm_pre_c = 0;           // window bits of the tables built by the next uploads (0 = chosen from the array size)
 
     NttDomain& domain(int logn) {
         auto it = domains.find(logn);
@@ -151,7 +152,7 @@ void upload_bases(g16_ctx* ctx, DevBuf& dst, const Src& src, uint64_t n, int& pr
     const size_t row = (size_t)n * sizeof(typename C::Aff);
     pre_c = 0;
     if (ctx->msm_precompute && n >= PRECOMPUTE_MIN_POINTS) {
-        const int c = msm_pre_choose_c(n, IS_G2);
+        const int c = msm_pre_choose_c(n, IS_G2, ctx->msm_pre_c);
         const size_t total = row * (size_t)(255 / c + 1);
         size_t free_b = 0, total_b = 0;
         G16_CUDA(cudaMemGetInfo(&free_b, &total_b));
@@ -189,21 +190,16 @@ int g16_ctx_create(g16_ctx** out, int curve_id, const int* device_ids, int n_dev
         if (count < 1) throw std::runtime_error("no CUDA device: libg16b200 has no CPU fallback");
         c->device = (device_ids && n_devices == 1) ? device_ids[0] : 0;
         G16_CUDA(cudaSetDevice(c->device));
-        if (const char* e = getenv("G16_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(e));   // experiment knob
         int prio_lo = 0, prio_hi = 0;
         G16_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
         // the main stream carries computeH and then the H.Z MSM.  Measured (G16_TIMELINE=1): at high priority h is ready
         // after 6.8 ms instead of ~50, but the proof takes the same 69 ms -- the GPU is busy throughout and some MSM
         // has to finish last -- and the host-buffer entry point gets slower (75.9 vs 72.0 ms); default = normal priority
-        int prio_main = prio_lo;
-        if (const char* e = getenv("G16_MAIN_PRIO")) prio_main = atoi(e);
+        const int prio_main = prio_lo;
         G16_CUDA(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_main));
         for (auto& a : c->aux) G16_CUDA(cudaStreamCreateWithFlags(&a, cudaStreamNonBlocking));
         for (auto& t : c->tails) G16_CUDA(cudaStreamCreateWithPriority(&t, cudaStreamNonBlocking, prio_hi));
         for (auto& e : c->ev) G16_CUDA(cudaEventCreate(&e));
-        if (const char* e = getenv("G16_STREAMS")) c->streams = atoi(e);
-        if (const char* e = getenv("G16_MSM_C")) c->msm_c = atoi(e);
-        if (const char* e = getenv("G16_MSM_WAVES")) c->msm_waves = atoi(e);
     } catch (const std::exception& e) {
         fprintf(stderr, "g16_ctx_create: %s\n", e.what());
         return 2;
@@ -241,6 +237,7 @@ int g16_ctx_set(g16_ctx* ctx, const char* key, int64_t value) {
     else if (k == "msm_waves") ctx->msm_waves = (int)value;
     else if (k == "streams") ctx->streams = (int)value;
     else if (k == "msm_precompute") ctx->msm_precompute = (int)value;
+    else if (k == "msm_pre_c") ctx->msm_pre_c = (int)value;
     else if (k == "dist_sync") ctx->dist_sync = (int)value;
     else { ctx->err = "unknown tunable " + k; return 1; }
     return 0;
@@ -523,7 +520,7 @@ extern "C" int g16_bases_upload(g16_ctx* ctx, const void* bases, uint64_t n, int
             int pre_c = 0;
             const size_t row = (size_t)n * (g2 ? G2SZ : G1SZ);
             if (ctx->msm_precompute && n >= PRECOMPUTE_MIN_POINTS) {
-                const int c = msm_pre_choose_c(n, g2 != 0);
+                const int c = msm_pre_choose_c(n, g2 != 0, ctx->msm_pre_c);
                 size_t free_b = 0, total_b = 0;
                 G16_CUDA(cudaMemGetInfo(&free_b, &total_b));
                 if (row * (size_t)(255 / c + 1) <= free_b / 2) pre_c = c;

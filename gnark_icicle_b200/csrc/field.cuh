@@ -4,6 +4,10 @@
 // Replaces the arithmetic the reference obtains from gnark-crypto fr/fp (go.mod:11; call sites
 // backend/groth16/bn254/prove.go:356-399 for fr, :202-304 for fp) and, on its GPU path, from icicle's
 // device field (backend/groth16/bn254/icicle/icicle.go:489-510 NTT/vec ops, :302-382 MSM).
+// Multiplier lineage: mul_n / cmad_n / madc_n_rshift / mad_redc below are the even/odd-accumulator CIOS layout for
+// 32-bit limbs published in supranational/sppark (ff/mont_t.cuh) and reused by ICICLE's device field header: two
+// interleaved accumulators so that every mad.lo.cc/madc.hi.cc pair continues one carry chain.  Neither project is
+// in /root/reference; the layout is restated here from the published technique, the code is this repository's.
 // Memory image = gnark-crypto's: N/2 little-endian uint64 limbs == N little-endian uint32 limbs,
 // Montgomery form with R = 2^(32N).
 #pragma once

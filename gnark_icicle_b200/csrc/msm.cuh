@@ -80,9 +80,8 @@ inline MsmPlan msm_plan(uint64_t n, int force_c, bool g2) {
 // affordable -- the bucket count no longer multiplies with the window count.  Entries per scalar drop from
 // ceil(255/16) = 16 to ceil(255/20) = 13 at 2^22 points.
 constexpr int MSM_PRE_CMIN = 16, MSM_PRE_CMAX = 21, MSM_PRE_HI_BITS = 8;
-inline int msm_pre_choose_c(uint64_t n, bool g2) {
-    static const int forced = [] { const char* e = getenv("G16_PRE_C"); return e ? atoi(e) : 0; }();   // experiment knob
-    if (forced >= MSM_PRE_CMIN && forced <= MSM_PRE_CMAX) return forced;
+inline int msm_pre_choose_c(uint64_t n, bool g2, int forced = 0) {
+    if (forced >= MSM_PRE_CMIN && forced <= MSM_PRE_CMAX) return forced;   // g16_ctx_set(ctx, "msm_pre_c", c) before the upload
     // G1, small arrays (the shards of a multi-GPU prove): measured on B200 (experiments/pre_c_sweep.py, resident MSM in ms for
     // c = 16 / 17 / 18 / 19 / 20): 2^19 points 2.23 / 2.27 / 2.70 / 2.48 / 2.56, 2^20: 3.73 / 3.57 / 4.23 / 4.22 / 3.90,
     // 2^21: 6.74 / 6.36 / 7.31 / 7.25 / 6.34 -- the cost model below overrates 18 and 19

@@ -7,24 +7,15 @@ namespace g16 {
 
 void msm_g2_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const G2::Aff* bases_d, uint64_t n,
                     int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail, int pre_c, MsmWorkspace* sort_from) {
-    static const int variant = [] { const char* e = getenv("G16_ACC_VARIANT_G2"); return e ? atoi(e) : 0; }();
-    // 128 x 2.  Measured (profiles/README.md): the G2 kernel is issue-bound -- every integer instruction, IADD3 included,
-    // takes the same two-cycle slot as an IMAD -- so more CTAs/SM do not help (3-4 CTAs/SM: +15..50 %).  Parking the
-    // accumulator in shared memory (SmemAcc) costs 15 % on BN254 (extra LDS/STS issue slots) but removes enough spills
-    // on the 12-limb BLS12-377 field to win 5 % there.  Variants 3 / 4 call at the Fp2 level (three base-field
-    // multiplications inlined per call): 252 / 222 registers and 10 % slower than the per-Fp calls (23.4 vs 21.3 ms).
+    // 128 threads x 2 CTAs per SM, base-field multiplications as register-ABI calls.  Measured (profiles/README.md,
+    // experiments/README.md): more CTAs per SM do not help (3-4 CTAs/SM: +15..50 %); calling at the Fp2 level (three
+    // multiplications inlined per call) needs 252 registers and is 10 % slower; parking the accumulator in shared
+    // memory (SmemAcc) costs 15 % on BN254 but removes enough spills on the 12-limb BLS12-377 field to win 5 % there.
 #if G16_CURVE == 377
-    const bool smem_acc = variant != 1;
+    msm_enqueue<G2, 128, 2, true>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
 #else
-    const bool smem_acc = variant == 1;
+    msm_enqueue<G2, 128, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
 #endif
-    if (variant == 5) msm_enqueue<G2, 64, 1>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
-    else if (variant == 6) msm_enqueue<G2, 32, 1>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
-    else if (variant == 7) msm_enqueue<G2, 96, 1>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
-    else if (variant == 3) msm_enqueue<G2, 128, 2, false, 1>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
-    else if (variant == 4) msm_enqueue<G2, 128, 2, true, 1>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
-    else if (smem_acc) msm_enqueue<G2, 128, 2, true>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
-    else msm_enqueue<G2, 128, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
 }
 void msm_g2_precompute(G2::Aff* table_d, uint64_t n, int c, cudaStream_t st) {
     if (!n) return;

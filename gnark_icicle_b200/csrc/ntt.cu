@@ -27,14 +27,9 @@ static const uint32_t ROOT_2_28[8] = {0x725b19f0u, 0x9bd61b6eu, 0x41112ed4u, 0x4
 static const uint64_t COSET_GEN = 5;
 #endif
 
-int ntt_log_tile() {
-    static int v = [] { const char* e = getenv("G16_NTT_LOG_TILE"); int x = e ? atoi(e) : 10; return x < 4 ? 4 : (x > 12 ? 12 : x); }();
-    return v;
-}
-int ntt_log_cols() {
-    static int v = [] { const char* e = getenv("G16_NTT_LOG_COLS"); int x = e ? atoi(e) : 2; return x < 0 ? 0 : (x > 3 ? 3 : x); }();
-    return v;
-}
+// tile shape, tuned on B200 (experiments/ntt_sweep.py): 2^10 elements = 32 KB of shared memory per CTA, 4 columns
+int ntt_log_tile() { return 10; }
+int ntt_log_cols() { return 2; }
 
 // ------------------------------------------------------------------ twiddle tables
 struct StageParams {

@@ -56,7 +56,7 @@ void compute_h_noalloc(int device, const Fr::T* a, const Fr::T* b, const Fr::T* 
 void ntt_dist_stages(NttDomain& d, const NttBatch& b, NttTable t, bool dif, int world_log, uint32_t rank, bool cyclic, int split, cudaStream_t st);
 void ntt_dist_permute(const Fr::T* src, Fr::T* dst, int count, uint64_t n_local, uint32_t world, int block_layout, int to_wire, cudaStream_t st);
 
-// tunables (env G16_NTT_LOG_TILE, G16_NTT_LOG_COLS)
+// tile shape of a sweep: log2 of the elements per tile / of the columns per tile
 int ntt_log_tile();
 int ntt_log_cols();
 

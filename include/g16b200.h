@@ -65,7 +65,8 @@ const char* g16_last_error(const g16_ctx* ctx);
  * "msm_precompute" (default 1: g16_pk_upload also keeps the 2^(c j) multiples of every key base resident -- the
  * analogue of icicle's precompute_factor -- so that all windows of a prove MSM share one bucket set and the window
  * can grow to 20 bits; costs 13x the key in HBM and is skipped when that exceeds half of the free memory; set 0
- * before the upload to skip the tables, or after it to run the classic per-window path on the same key) */
+ * before the upload to skip the tables, or after it to run the classic per-window path on the same key),
+ * "msm_pre_c" (window bits, 16..21, of the tables built by later uploads; 0 = chosen from the array size) */
 int g16_ctx_set(g16_ctx* ctx, const char* key, int64_t value);
 /* total kernels launched by this library in this process (bench.py's gpu_launches evidence) */
 uint64_t g16_kernel_launch_count(void);

@@ -1,5 +1,8 @@
 """prints the measured integer-pipe rates of this GPU (roofline denominators)."""
 import json
+import os
+import sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from gnark_icicle_b200 import lib
 c = lib.Context(0)
 imad, wide = c.imad_peak()
