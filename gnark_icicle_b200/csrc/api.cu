@@ -8,114 +8,16 @@
 #include <memory>
 #include <unistd.h>
 
-#include "curve_select.h"
-#include "../../include/g16b200.h"
-#include "msm_api.cuh"
-#include "ntt.cuh"
-#include "r1cs.cuh"
+#include "ctx.cuh"
 
 using namespace g16;
 
-static constexpr size_t G1SZ = sizeof(G1::Aff), G2SZ = sizeof(G2::Aff);   // 64 / 128 B (BN254), 96 / 192 B (BLS12-377)
-
 namespace {
-
-struct PkDev {
-    uint64_t domain_n = 0;
-    int logn = 0;
-    uint64_t n_wires = 0;
-    // this shard's slices
-    DevBuf g1_a, g1_b, g1_k, g1_z, g2_b;
-    DevBuf map_a, map_b, map_k;   // u32 wire index per base
-    uint64_t n_a = 0, n_b = 0, n_k = 0, n_z = 0, n_b2 = 0;
-    int pre_c[5] = {0, 0, 0, 0, 0}; // window bits of the precomputed-multiples table per MSM (G16_OUT_* order); 0 = none
-    uint64_t z_off = 0;           // first h index of this shard's Z slice
-    uint64_t w_lo = 0, w_hi = 0;  // wires [w_lo, w_hi) are the only ones this shard's A / B / K maps read
-    void release() {
-        g1_a.release(); g1_b.release(); g1_k.release(); g1_z.release(); g2_b.release();
-        map_a.release(); map_b.release(); map_k.release();
-    }
-};
-
-}  // namespace
-
-struct g16_ctx {
-    int device = 0;
-    cudaStream_t stream = nullptr;
-    cudaStream_t aux[4] = {};   // the MSMs that do not depend on h
-    cudaStream_t tails[5] = {}; // high-priority streams for the latency-bound MSM tails
-    int streams = 5;
-    cudaEvent_t ev[32] = {};
-    std::string err;
-    std::map<int, NttDomain> domains;
-    std::map<uint64_t, PkDev> pks;
-    std::map<uint64_t, R1csDev> r1cs;
-    struct Bases { DevBuf table; uint64_t n = 0; int pre_c = 0; bool g2 = false; };
-    std::map<uint64_t, Bases> bases;
-    struct CommitKey { Bases basis, basis_exp_sigma; };   // pedersen.ProvingKey (setup.go:57)
-    std::map<uint64_t, CommitKey> commit_keys;
-    uint64_t next_pk = 1;
-    MsmPlan pend_plan[5];        // g16_prove_msms_begin_dev .. g16_prove_msms_dev: plans of the MSMs already in flight
-    uint64_t pend_pk = 0;        // 0 = nothing pending
-    MsmWorkspace ws[5];
-    DevBuf stage[4];             // host-pointer variants: staged inputs
-    PinnedBuf file_stage[2];     // g16_pk_upload_from_file: double-buffered pread -> H2D
-    DevBuf fb_table_g1, fb_table_g2;
-    int msm_c = 0, msm_waves = 4;
-    int dist_sync = 1;           // g16_dist_*_dev return after the stream has drained (0: stream-ordered, caller synchronises)
-    int msm_precompute = 1;      // keep 2^(c j) multiples of every key base resident (one shared bucket set, larger windows)
-    int msm_pre_c = 0;           // window bits of the tables built by the next uploads (0 = chosen from the array size)
-
-    NttDomain& domain(int logn) {
-        auto it = domains.find(logn);
-        if (it != domains.end()) return it->second;
-        NttDomain& d = domains[logn];
-        d.init(logn);
-        return d;
-    }
-};
-
-namespace {
-
-template <class F>
-int guarded(g16_ctx* ctx, F&& f) {
-    if (!ctx) return 1;
-    try {
-        G16_CUDA(cudaSetDevice(ctx->device));
-        f();
-        return 0;
-    } catch (const std::exception& e) {
-        ctx->err = e.what();
-        cudaGetLastError();   // clear a sticky launch error so that later calls report their own
-        return 2;
-    }
-}
-
-bool is_pow2(uint64_t n) { return n && !(n & (n - 1)); }
-
-void slice(uint64_t len, uint32_t idx, uint32_t cnt, uint64_t& lo, uint64_t& hi) {
-    if (cnt <= 1) { lo = 0; hi = len; return; }
-    lo = len * idx / cnt;
-    hi = len * (idx + 1) / cnt;
-}
-
-void upload(DevBuf& dst, const void* src, size_t bytes, cudaStream_t st) {
-    dst.reserve(bytes ? bytes : 16);
-    if (bytes) G16_CUDA(cudaMemcpyAsync(dst.p, src, bytes, cudaMemcpyHostToDevice, st));
-}
 
 // Key bases: row 0 of a table that, when it fits comfortably (less than half of the free HBM) and the array is
 // large enough to pay for it, also holds the 2^(c j) multiples used by the shared-bucket MSM (msm.cuh, precomputed
 // mode).  pre_c = window bits of the table, 0 = bases only.
 constexpr uint64_t PRECOMPUTE_MIN_POINTS = 1 << 14;
-// Where key material comes from: host memory, or a byte range of a file (a ProvingKey.WriteDump image, whose point
-// slices are raw memory = the device format; marshal.go:386-456).
-struct Src {
-    const char* host = nullptr;
-    int fd = -1;
-    uint64_t off = 0;
-    Src at(uint64_t bytes) const { Src s = *this; if (host) s.host += bytes; s.off += bytes; return s; }
-};
 Src host_src(const void* p) { Src s; s.host = (const char*)p; return s; }
 
 // file -> HBM without an intermediate pageable copy: pread into two pinned staging buffers, the H2D copy of one
@@ -172,43 +74,39 @@ void upload_bases(g16_ctx* ctx, DevBuf& dst, const void* src, uint64_t n, int& p
 
 }  // namespace
 
-extern "C" {
+namespace g16 {
 
-int g16_ctx_create(g16_ctx** out, int curve_id, const int* device_ids, int n_devices) {
-    if (!out) return 1;
-    *out = nullptr;
-    if (curve_id != (G16_CURVE == 377 ? G16_CURVE_BLS12_377 : G16_CURVE_BN254)) return 3;   // one entry-point set per curve (curve_select.h)
-    if (n_devices > 1) return 4;
+g16_ctx* ctx_create_single(int device) {
     std::unique_ptr<g16_ctx> c(new g16_ctx());
+    // A prove uses 10 streams (main, 4 MSM streams, 5 tail streams); with the default 8 hardware queues two of them
+    // share one and the later MSM starts only when the earlier one has finished.  Takes effect only if CUDA has not
+    // been initialised in this process yet (hosts that initialise CUDA first should export it themselves).
+    setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
+    int count = 0;
+    G16_CUDA(cudaGetDeviceCount(&count));
+    if (count < 1) throw std::runtime_error("no CUDA device: libg16b200 has no CPU fallback");
+    if (device < 0 || device >= count) throw std::runtime_error("device ordinal " + std::to_string(device) + " out of range (" + std::to_string(count) + " visible)");
+    c->device = device;
+    G16_CUDA(cudaSetDevice(c->device));
+    int prio_lo = 0, prio_hi = 0;
+    G16_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    // the main stream carries computeH and then the H.Z MSM.  Measured (G16_TIMELINE=1): at high priority h is ready
+    // after 6.8 ms instead of ~50, but the proof takes the same 69 ms -- the GPU is busy throughout and some MSM
+    // has to finish last -- and the host-buffer entry point gets slower (75.9 vs 72.0 ms); default = normal priority
+    const int prio_main = prio_lo;
     try {
-        // A prove uses 10 streams (main, 4 MSM streams, 5 tail streams); with the default 8 hardware queues two of them
-        // share one and the later MSM starts only when the earlier one has finished.  Takes effect only if CUDA has not
-        // been initialised in this process yet (hosts that initialise CUDA first should export it themselves).
-        setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
-        int count = 0;
-        G16_CUDA(cudaGetDeviceCount(&count));
-        if (count < 1) throw std::runtime_error("no CUDA device: libg16b200 has no CPU fallback");
-        c->device = (device_ids && n_devices == 1) ? device_ids[0] : 0;
-        G16_CUDA(cudaSetDevice(c->device));
-        int prio_lo = 0, prio_hi = 0;
-        G16_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
-        // the main stream carries computeH and then the H.Z MSM.  Measured (G16_TIMELINE=1): at high priority h is ready
-        // after 6.8 ms instead of ~50, but the proof takes the same 69 ms -- the GPU is busy throughout and some MSM
-        // has to finish last -- and the host-buffer entry point gets slower (75.9 vs 72.0 ms); default = normal priority
-        const int prio_main = prio_lo;
         G16_CUDA(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_main));
         for (auto& a : c->aux) G16_CUDA(cudaStreamCreateWithFlags(&a, cudaStreamNonBlocking));
         for (auto& t : c->tails) G16_CUDA(cudaStreamCreateWithPriority(&t, cudaStreamNonBlocking, prio_hi));
         for (auto& e : c->ev) G16_CUDA(cudaEventCreate(&e));
-    } catch (const std::exception& e) {
-        fprintf(stderr, "g16_ctx_create: %s\n", e.what());
-        return 2;
+    } catch (...) {
+        ctx_destroy_single(c.release());
+        throw;
     }
-    *out = c.release();
-    return 0;
+    return c.release();
 }
 
-void g16_ctx_destroy(g16_ctx* ctx) {
+void ctx_destroy_single(g16_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
@@ -228,6 +126,35 @@ void g16_ctx_destroy(g16_ctx* ctx) {
     delete ctx;
 }
 
+}  // namespace g16
+
+extern "C" {
+
+int g16_ctx_create(g16_ctx** out, int curve_id, const int* device_ids, int n_devices) {
+    if (!out) return 1;
+    *out = nullptr;
+    if (curve_id != (G16_CURVE == 377 ? G16_CURVE_BLS12_377 : G16_CURVE_BN254)) return 3;   // one entry-point set per curve (curve_select.h)
+    if (n_devices > 8 || (n_devices > 1 && (n_devices & (n_devices - 1)))) return 4;        // 1, 2, 4 or 8 GPUs
+    if (n_devices >= 1 && !device_ids) return 1;
+    g16_ctx* c = nullptr;
+    try {
+        c = ctx_create_single(n_devices >= 1 ? device_ids[0] : 0);
+        if (n_devices > 1) c->multi = multi_create(c, device_ids, n_devices);
+    } catch (const std::exception& e) {
+        fprintf(stderr, "g16_ctx_create: %s\n", e.what());
+        if (c) ctx_destroy_single(c);
+        return 2;
+    }
+    *out = c;
+    return 0;
+}
+
+void g16_ctx_destroy(g16_ctx* ctx) {
+    if (!ctx) return;
+    if (ctx->multi) { multi_destroy(ctx->multi); ctx->multi = nullptr; }
+    ctx_destroy_single(ctx);
+}
+
 const char* g16_last_error(const g16_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
 
 int g16_ctx_set(g16_ctx* ctx, const char* key, int64_t value) {
@@ -239,7 +166,9 @@ int g16_ctx_set(g16_ctx* ctx, const char* key, int64_t value) {
     else if (k == "msm_precompute") ctx->msm_precompute = (int)value;
     else if (k == "msm_pre_c") ctx->msm_pre_c = (int)value;
     else if (k == "dist_sync") ctx->dist_sync = (int)value;
+    else if (k == "g2_weight") ctx->g2_weight = (int)value;
     else { ctx->err = "unknown tunable " + k; return 1; }
+    if (ctx->multi) multi_set(ctx->multi, key, value);
     return 0;
 }
 
@@ -249,66 +178,92 @@ void* g16_ctx_stream(g16_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; 
 }  // extern "C"
 
 // =================================================================== proving key
-namespace {
+namespace g16 {
+
+void pk_validate(const g16_pk_desc* d) {
+    if (!d) throw std::runtime_error("null argument");
+    if (!is_pow2(d->domain_n)) throw std::runtime_error("domain_n must be a power of two");
+    if (d->n_b2 != d->n_b) throw std::runtime_error("G2.B and G1.B must have the same length");
+    if (d->n_z + 1 != d->domain_n && d->n_z != d->domain_n) throw std::runtime_error("G1.Z must have domain_n - 1 entries");
+    if (d->n_k > d->n_wires) throw std::runtime_error("G1.K longer than the wire vector");
+    if (d->n_wires >= 0xffffffffull) throw std::runtime_error("wire vector too long for 32-bit wire indices");
+}
+
+// slice shard_index of shard_count of every base array; Z follows the block distribution of h over the domain (so a
+// distributed computeH leaves each rank's block of h exactly under its Z slice); the last block loses the dropped
+// degree-(n-1) coefficient (h[:n-1], prove.go:235-237)
+PkRanges pk_shard_ranges(const g16_pk_desc* d) {
+    const uint32_t sc = d->shard_count ? d->shard_count : 1, si = d->shard_index;
+    if (si >= sc) throw std::runtime_error("shard_index out of range");
+    PkRanges rg;
+    slice(d->n_a, si, sc, rg.lo[G16_OUT_AR], rg.hi[G16_OUT_AR]);
+    slice(d->n_b, si, sc, rg.lo[G16_OUT_BS1], rg.hi[G16_OUT_BS1]);
+    slice(d->n_k, si, sc, rg.lo[G16_OUT_KRS_K], rg.hi[G16_OUT_KRS_K]);
+    slice(d->n_b, si, sc, rg.lo[G16_OUT_BS2], rg.hi[G16_OUT_BS2]);
+    const uint64_t nz = d->n_z < d->domain_n ? d->n_z : d->domain_n - 1;
+    uint64_t lo, hi;
+    slice(d->domain_n, si, sc, lo, hi);
+    rg.lo[G16_OUT_KRS_HZ] = lo > nz ? nz : lo;
+    rg.hi[G16_OUT_KRS_HZ] = hi > nz ? nz : hi;
+    return rg;
+}
+
 // src: G1.A, G1.B, G1.K, G1.Z, G2.B
-int pk_upload_impl(g16_ctx* ctx, const g16_pk_desc* d, const Src* src, uint64_t* pk_handle) {
-    return guarded(ctx, [&] {
-        if (!d || !pk_handle) throw std::runtime_error("null argument");
-        if (!is_pow2(d->domain_n)) throw std::runtime_error("domain_n must be a power of two");
-        if (d->n_b2 != d->n_b) throw std::runtime_error("G2.B and G1.B must have the same length");
-        if (d->n_z + 1 != d->domain_n && d->n_z != d->domain_n) throw std::runtime_error("G1.Z must have domain_n - 1 entries");
-        if (d->n_k > d->n_wires) throw std::runtime_error("G1.K longer than the wire vector");
-        const uint32_t sc = d->shard_count ? d->shard_count : 1, si = d->shard_index;
-        if (si >= sc) throw std::runtime_error("shard_index out of range");
-        cudaStream_t st = ctx->stream;
-        PkDev pk;
-        pk.domain_n = d->domain_n;
-        pk.logn = ilog2_ceil(d->domain_n);
-        pk.n_wires = d->n_wires;
+void pk_upload_ranges(g16_ctx* ctx, const g16_pk_desc* d, const Src* src, const PkRanges& rg, uint64_t handle) {
+    pk_validate(d);
+    const uint64_t lens[5] = {d->n_a, d->n_b, d->n_k, d->n_z < d->domain_n ? d->n_z : d->domain_n - 1, d->n_b2};
+    for (int i = 0; i < 5; i++)
+        if (rg.lo[i] > rg.hi[i] || rg.hi[i] > lens[i]) throw std::runtime_error("proving-key slice out of range");
+    cudaStream_t st = ctx->stream;
+    PkDev pk;
+    pk.domain_n = d->domain_n;
+    pk.logn = ilog2_ceil(d->domain_n);
+    pk.n_wires = d->n_wires;
 
-        // wire index of every A / B base: position among the non-infinity wires (prove.go:152-178)
-        std::vector<uint32_t> ma, mb, mk;
-        ma.reserve(d->n_a); mb.reserve(d->n_b);
-        for (uint64_t i = 0; i < d->n_wires; i++) {
-            if (!d->infinity_a || !d->infinity_a[i]) ma.push_back((uint32_t)i);
-            if (!d->infinity_b || !d->infinity_b[i]) mb.push_back((uint32_t)i);
-        }
-        if (ma.size() != d->n_a) throw std::runtime_error("InfinityA does not match len(G1.A): " + std::to_string(ma.size()) + " vs " + std::to_string(d->n_a));
-        if (mb.size() != d->n_b) throw std::runtime_error("InfinityB does not match len(G1.B): " + std::to_string(mb.size()) + " vs " + std::to_string(d->n_b));
-        mk.resize(d->n_k);
-        for (uint64_t i = 0; i < d->n_k; i++) {
-            mk[i] = d->k_index ? d->k_index[i] : (uint32_t)(d->n_wires - d->n_k + i);
-            if (mk[i] >= d->n_wires) throw std::runtime_error("k_index out of range");
-        }
+    // wire index of every A / B base: position among the non-infinity wires (prove.go:152-178)
+    std::vector<uint32_t> ma, mb, mk;
+    ma.reserve(d->n_a); mb.reserve(d->n_b);
+    for (uint64_t i = 0; i < d->n_wires; i++) {
+        if (!d->infinity_a || !d->infinity_a[i]) ma.push_back((uint32_t)i);
+        if (!d->infinity_b || !d->infinity_b[i]) mb.push_back((uint32_t)i);
+    }
+    if (ma.size() != d->n_a) throw std::runtime_error("InfinityA does not match len(G1.A): " + std::to_string(ma.size()) + " vs " + std::to_string(d->n_a));
+    if (mb.size() != d->n_b) throw std::runtime_error("InfinityB does not match len(G1.B): " + std::to_string(mb.size()) + " vs " + std::to_string(d->n_b));
+    mk.resize(d->n_k);
+    for (uint64_t i = 0; i < d->n_k; i++) {
+        mk[i] = d->k_index ? d->k_index[i] : (uint32_t)(d->n_wires - d->n_k + i);
+        if (mk[i] >= d->n_wires) throw std::runtime_error("k_index out of range");
+    }
 
-        uint64_t lo, hi;
-        pk.w_lo = d->n_wires; pk.w_hi = 0;
-        auto touch = [&](const std::vector<uint32_t>& m, uint64_t a, uint64_t b) {   // maps are not assumed monotone (k_index)
-            for (uint64_t i = a; i < b; i++) { if (m[i] < pk.w_lo) pk.w_lo = m[i]; if ((uint64_t)m[i] + 1 > pk.w_hi) pk.w_hi = (uint64_t)m[i] + 1; }
-        };
-        slice(d->n_a, si, sc, lo, hi);
+    pk.ranges = rg;
+    pk.w_lo = d->n_wires; pk.w_hi = 0;
+    auto touch = [&](const std::vector<uint32_t>& m, uint64_t a, uint64_t b) {   // maps are not assumed monotone (k_index)
+        for (uint64_t i = a; i < b; i++) { if (m[i] < pk.w_lo) pk.w_lo = m[i]; if ((uint64_t)m[i] + 1 > pk.w_hi) pk.w_hi = (uint64_t)m[i] + 1; }
+    };
+    try {
+        uint64_t lo = rg.lo[G16_OUT_AR], hi = rg.hi[G16_OUT_AR];
         touch(ma, lo, hi);
         pk.n_a = hi - lo;
         upload_bases<G1>(ctx, pk.g1_a, src[0].at(lo * G1SZ), pk.n_a, pk.pre_c[G16_OUT_AR], st);
         upload(pk.map_a, ma.data() + lo, pk.n_a * 4, st);
-        slice(d->n_b, si, sc, lo, hi);
+        lo = rg.lo[G16_OUT_BS1]; hi = rg.hi[G16_OUT_BS1];
         touch(mb, lo, hi);
-        pk.n_b = pk.n_b2 = hi - lo;
+        pk.n_b = hi - lo;
         upload_bases<G1>(ctx, pk.g1_b, src[1].at(lo * G1SZ), pk.n_b, pk.pre_c[G16_OUT_BS1], st);
-        upload_bases<G2>(ctx, pk.g2_b, src[4].at(lo * G2SZ), pk.n_b, pk.pre_c[G16_OUT_BS2], st);
         upload(pk.map_b, mb.data() + lo, pk.n_b * 4, st);
-        slice(d->n_k, si, sc, lo, hi);
+        pk.same_b = rg.lo[G16_OUT_BS2] == lo && rg.hi[G16_OUT_BS2] == hi;
+        lo = rg.lo[G16_OUT_BS2]; hi = rg.hi[G16_OUT_BS2];
+        touch(mb, lo, hi);
+        pk.n_b2 = hi - lo;
+        upload_bases<G2>(ctx, pk.g2_b, src[4].at(lo * G2SZ), pk.n_b2, pk.pre_c[G16_OUT_BS2], st);
+        if (!pk.same_b) upload(pk.map_b2, mb.data() + lo, pk.n_b2 * 4, st);
+        lo = rg.lo[G16_OUT_KRS_K]; hi = rg.hi[G16_OUT_KRS_K];
         touch(mk, lo, hi);
         if (pk.w_hi <= pk.w_lo) pk.w_lo = pk.w_hi = 0;
         pk.n_k = hi - lo;
         upload_bases<G1>(ctx, pk.g1_k, src[2].at(lo * G1SZ), pk.n_k, pk.pre_c[G16_OUT_KRS_K], st);
         upload(pk.map_k, mk.data() + lo, pk.n_k * 4, st);
-        uint64_t nz = d->n_z < d->domain_n ? d->n_z : d->domain_n - 1;   // h[:n-1] (prove.go:235-237)
-        // Z follows the block distribution of h over the domain (so a distributed computeH leaves each rank's
-        // block of h exactly under its Z slice); the last block loses the dropped degree-(n-1) coefficient
-        slice(d->domain_n, si, sc, lo, hi);
-        if (lo > nz) lo = nz;
-        if (hi > nz) hi = nz;
+        lo = rg.lo[G16_OUT_KRS_HZ]; hi = rg.hi[G16_OUT_KRS_HZ];
         pk.n_z = hi - lo;
         pk.z_off = lo;
         upload_bases<G1>(ctx, pk.g1_z, src[3].at(lo * G1SZ), pk.n_z, pk.pre_c[G16_OUT_KRS_HZ], st);
@@ -319,8 +274,24 @@ int pk_upload_impl(g16_ctx* ctx, const g16_pk_desc* d, const Src* src, uint64_t*
         dom.table(TW_COSET_FWD, st);
         dom.table(TW_COSET_INV, st);
         G16_CUDA(cudaStreamSynchronize(st));   // host vectors above go out of scope
-        uint64_t h = ctx->next_pk++;
-        ctx->pks[h] = pk;
+    } catch (...) {
+        cudaStreamSynchronize(st);
+        pk.release();                          // nothing of a half-uploaded key stays allocated
+        throw;
+    }
+    ctx->pks[handle] = pk;
+}
+
+}  // namespace g16
+
+namespace {
+int pk_upload_impl(g16_ctx* ctx, const g16_pk_desc* d, const Src* src, uint64_t* pk_handle) {
+    return guarded(ctx, [&] {
+        if (!d || !pk_handle) throw std::runtime_error("null argument");
+        if (ctx->multi) { multi_pk_upload(ctx, d, src, pk_handle); return; }
+        pk_validate(d);
+        const uint64_t h = ctx->next_pk++;
+        pk_upload_ranges(ctx, d, src, pk_shard_ranges(d), h);
         *pk_handle = h;
     });
 }
@@ -346,15 +317,32 @@ extern "C" int g16_pk_upload_from_file(g16_ctx* ctx, const g16_pk_file_desc* f, 
 
 extern "C" int g16_pk_wire_range(g16_ctx* ctx, uint64_t pk_handle, uint64_t* lo, uint64_t* hi) {
     return guarded(ctx, [&] {
+        if (!lo || !hi) throw std::runtime_error("null argument");
+        if (ctx->multi) { multi_pk_wire_range(ctx, pk_handle, lo, hi); return; }
         auto it = ctx->pks.find(pk_handle);
         if (it == ctx->pks.end()) throw std::runtime_error("unknown proving-key handle");
-        if (!lo || !hi) throw std::runtime_error("null argument");
         *lo = it->second.w_lo; *hi = it->second.w_hi;
+    });
+}
+
+extern "C" int g16_pk_placement(g16_ctx* ctx, uint64_t pk_handle, int rank, uint64_t lo[5], uint64_t hi[5]) {
+    return guarded(ctx, [&] {
+        if (!lo || !hi) throw std::runtime_error("null argument");
+        const PkDev* pk;
+        if (ctx->multi) pk = &multi_pk_of_rank(ctx, pk_handle, rank);
+        else {
+            auto it = ctx->pks.find(pk_handle);
+            if (it == ctx->pks.end()) throw std::runtime_error("unknown proving-key handle");
+            if (rank != 0) throw std::runtime_error("rank out of range");
+            pk = &it->second;
+        }
+        for (int i = 0; i < 5; i++) { lo[i] = pk->ranges.lo[i]; hi[i] = pk->ranges.hi[i]; }
     });
 }
 
 extern "C" int g16_pk_free(g16_ctx* ctx, uint64_t pk_handle) {
     return guarded(ctx, [&] {
+        if (ctx->multi) { multi_pk_free(ctx, pk_handle); return; }
         auto it = ctx->pks.find(pk_handle);
         if (it == ctx->pks.end()) throw std::runtime_error("unknown proving-key handle");
         G16_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -364,15 +352,12 @@ extern "C" int g16_pk_free(g16_ctx* ctx, uint64_t pk_handle) {
 }
 
 // =================================================================== prove
-namespace {
-
-template <class Aff>
-void copy_out(void* dst, const Aff& p) { memcpy(dst, &p, sizeof(Aff)); }
+namespace g16 {
 
 // phase 0: the whole device section.  phase 1: enqueue the four MSMs over W and return (they run while the caller
-// produces h, e.g. the distributed computeH with its all-to-alls); phase 2: enqueue the H.Z MSM, wait for all five, finish.
+// produces h, e.g. the distributed computeH with its exchanges); phase 2: enqueue the H.Z MSM, wait for all five, finish.
 void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* b_d, Fr::T* c_d, void* out_points,
-                  g16_stats* stats, uint64_t launches0, cudaEvent_t w_ready, bool h_given = false, int phase = 0) {
+                  g16_stats* stats, uint64_t launches0, cudaEvent_t w_ready, bool h_given, int phase, ProvePartial* partial) {
     cudaStream_t st = ctx->stream;
     NttDomain& dom = ctx->domain(pk.logn);
     cudaEvent_t* ev = ctx->ev;
@@ -402,7 +387,7 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
         G16_CUDA(cudaEventRecord(ev[6 + idx], s));
     };
     if (phase != 2) run(G16_OUT_BS2, s2, [&](cudaStream_t s) {
-        msm_g2_enqueue(ctx->ws[G16_OUT_BS2], W_d, pk.map_b.as<uint32_t>(), pk.g2_b.as<G2::Aff>(), pk.n_b2, ctx->msm_c, ctx->msm_waves, s, plan[4], &ms[4], overlap ? ctx->tails[4] : nullptr, pre(G16_OUT_BS2)); });
+        msm_g2_enqueue(ctx->ws[G16_OUT_BS2], W_d, (pk.same_b ? pk.map_b : pk.map_b2).as<uint32_t>(), pk.g2_b.as<G2::Aff>(), pk.n_b2, ctx->msm_c, ctx->msm_waves, s, plan[4], &ms[4], overlap ? ctx->tails[4] : nullptr, pre(G16_OUT_BS2)); });
     if (phase != 1) {
         G16_CUDA(cudaEventRecord(ev[12], st));
         if (!h_given) compute_h_device(dom, a_d, b_d, c_d, st);   // h (bit-reversed) in a_d; h_given: a_d is this shard's block of h
@@ -414,7 +399,7 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
         msm_g1_enqueue(ctx->ws[G16_OUT_KRS_HZ], a_d + (h_given ? 0 : pk.z_off), nullptr, pk.g1_z.as<G1::Aff>(), pk.n_z, ctx->msm_c, ctx->msm_waves, s, plan[3], &ms[3], overlap ? ctx->tails[3] : nullptr, pre(G16_OUT_KRS_HZ)); });
     if (phase != 2) run(G16_OUT_BS1, sB, [&](cudaStream_t s) {
         msm_g1_enqueue(ctx->ws[G16_OUT_BS1], W_d, pk.map_b.as<uint32_t>(), pk.g1_b.as<G1::Aff>(), pk.n_b, ctx->msm_c, ctx->msm_waves, s, plan[1], &ms[1], overlap ? ctx->tails[1] : nullptr, pre(G16_OUT_BS1),
-                       pk.n_b == pk.n_b2 ? &ctx->ws[G16_OUT_BS2] : nullptr); });   // same scalars, same map: reuse the G2 MSM's sort
+                       pk.same_b && pk.n_b == pk.n_b2 ? &ctx->ws[G16_OUT_BS2] : nullptr); });   // same scalars, same map: reuse the G2 MSM's sort
     if (phase != 2) run(G16_OUT_KRS_K, sK, [&](cudaStream_t s) {
         msm_g1_enqueue(ctx->ws[G16_OUT_KRS_K], W_d, pk.map_k.as<uint32_t>(), pk.g1_k.as<G1::Aff>(), pk.n_k, ctx->msm_c, ctx->msm_waves, s, plan[2], &ms[2], overlap ? ctx->tails[2] : nullptr, pre(G16_OUT_KRS_K)); });
     if (phase == 1) {
@@ -430,8 +415,13 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
     auto t0 = std::chrono::steady_clock::now();
     char* out = (char*)out_points;
     const uint64_t ns[5] = {pk.n_a, pk.n_b, pk.n_k, pk.n_z, pk.n_b2};
-    for (int i = 0; i < 4; i++) copy_out(out + G1SZ * i, ns[i] ? msm_g1_finish(ctx->ws[i], plan[i]) : G1::aff_inf());
-    copy_out(out + 4 * G1SZ, ns[4] ? msm_g2_finish(ctx->ws[4], plan[4]) : G2::aff_inf());
+    if (partial) {
+        for (int i = 0; i < 4; i++) partial->g1[i] = ns[i] ? msm_g1_finish_xyzz(ctx->ws[i], plan[i]) : G1::inf();
+        partial->g2 = ns[4] ? msm_g2_finish_xyzz(ctx->ws[4], plan[4]) : G2::inf();
+    } else {
+        for (int i = 0; i < 4; i++) copy_out(out + G1SZ * i, ns[i] ? msm_g1_finish(ctx->ws[i], plan[i]) : G1::aff_inf());
+        copy_out(out + 4 * G1SZ, ns[4] ? msm_g2_finish(ctx->ws[4], plan[4]) : G2::aff_inf());
+    }
     auto t1 = std::chrono::steady_clock::now();
     if (stats) {
         G16_CUDA(cudaEventElapsedTime(&stats->ms_compute_h, ev[12], ev[13]));
@@ -457,16 +447,21 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
     }
 }
 
-}  // namespace
+}  // namespace g16
 
 extern "C" int g16_prove_bn254_dev(g16_ctx* ctx, uint64_t pk_handle, const void* W_d, void* a_d, void* b_d, void* c_d,
                                    void* out_points, g16_stats* stats) {
     return guarded(ctx, [&] {
+        if (!W_d || !a_d || !b_d || !c_d || !out_points) throw std::runtime_error("null argument");
+        if (stats) memset(stats, 0, sizeof(*stats));
+        if (ctx->multi) {   // device pointers live on the group's first GPU; every rank pulls its share over NVLink
+            MultiIn in; in.W = W_d; in.a = a_d; in.b = b_d; in.c = c_d; in.device = true;
+            multi_prove(ctx, pk_handle, in, out_points, stats);
+            return;
+        }
         auto it = ctx->pks.find(pk_handle);
         if (it == ctx->pks.end()) throw std::runtime_error("unknown proving-key handle");
-        if (!W_d || !a_d || !b_d || !c_d || !out_points) throw std::runtime_error("null argument");
         uint64_t l0 = launch_counter().load();
-        if (stats) memset(stats, 0, sizeof(*stats));
         prove_device(ctx, it->second, (const Fr::T*)W_d, (Fr::T*)a_d, (Fr::T*)b_d, (Fr::T*)c_d, out_points, stats, l0, nullptr);
     });
 }
@@ -474,14 +469,19 @@ extern "C" int g16_prove_bn254_dev(g16_ctx* ctx, uint64_t pk_handle, const void*
 extern "C" int g16_prove_bn254(g16_ctx* ctx, uint64_t pk_handle, const void* W, uint64_t n_wires, const void* a,
                                const void* b, const void* c, uint64_t n_constraints, void* out_points, g16_stats* stats) {
     return guarded(ctx, [&] {
+        if (!W || !a || !b || !c || !out_points) throw std::runtime_error("null argument");
+        if (stats) memset(stats, 0, sizeof(*stats));
+        if (ctx->multi) {
+            MultiIn in; in.W = W; in.a = a; in.b = b; in.c = c; in.n_wires = n_wires; in.n_constraints = n_constraints;
+            multi_prove(ctx, pk_handle, in, out_points, stats);
+            return;
+        }
         auto it = ctx->pks.find(pk_handle);
         if (it == ctx->pks.end()) throw std::runtime_error("unknown proving-key handle");
         PkDev& pk = it->second;
-        if (!W || !a || !b || !c || !out_points) throw std::runtime_error("null argument");
         if (n_wires != pk.n_wires) throw std::runtime_error("witness length does not match the proving key");
         if (n_constraints > pk.domain_n) throw std::runtime_error("more constraints than the domain holds");
         uint64_t l0 = launch_counter().load();
-        if (stats) memset(stats, 0, sizeof(*stats));
         cudaStream_t st = ctx->stream;
         const size_t nb = (size_t)pk.domain_n * 32, cb = (size_t)n_constraints * 32;
         G16_CUDA(cudaEventRecord(ctx->ev[26], st));
@@ -686,6 +686,10 @@ extern "C" int g16_r1cs_upload(g16_ctx* ctx, const g16_r1cs_desc* d, uint64_t* h
         }
         uint64_t h = ctx->next_pk++;
         ctx->r1cs[h] = r;
+        if (ctx->multi) {
+            try { multi_r1cs_upload(ctx, d, h); }
+            catch (...) { ctx->r1cs[h].release(); ctx->r1cs.erase(h); throw; }
+        }
         *handle = h;
     });
 }
@@ -694,8 +698,10 @@ extern "C" int g16_r1cs_free(g16_ctx* ctx, uint64_t handle) {
     return guarded(ctx, [&] {
         auto it = ctx->r1cs.find(handle);
         if (it == ctx->r1cs.end()) throw std::runtime_error("unknown R1CS handle");
+        G16_CUDA(cudaStreamSynchronize(ctx->stream));
         it->second.release();
         ctx->r1cs.erase(it);
+        if (ctx->multi) multi_r1cs_free(ctx, handle);
     });
 }
 
@@ -713,24 +719,28 @@ extern "C" int g16_r1cs_eval_dev(g16_ctx* ctx, uint64_t handle, const void* W_d,
 extern "C" int g16_prove_bn254_wires(g16_ctx* ctx, uint64_t pk_handle, uint64_t r1cs_handle, const void* W, uint64_t n_wires,
                                      void* out_points, g16_stats* stats) {
     return guarded(ctx, [&] {
+        if (!W || !out_points) throw std::runtime_error("null argument");
+        if (stats) memset(stats, 0, sizeof(*stats));
+        if (ctx->multi) {
+            MultiIn in; in.W = W; in.n_wires = n_wires; in.r1cs = r1cs_handle;
+            multi_prove(ctx, pk_handle, in, out_points, stats);
+            return;
+        }
         auto it = ctx->pks.find(pk_handle);
         if (it == ctx->pks.end()) throw std::runtime_error("unknown proving-key handle");
         auto ir = ctx->r1cs.find(r1cs_handle);
         if (ir == ctx->r1cs.end()) throw std::runtime_error("unknown R1CS handle");
         PkDev& pk = it->second;
         const R1csDev& r = ir->second;
-        if (!W || !out_points) throw std::runtime_error("null argument");
         if (n_wires != pk.n_wires || n_wires != r.n_wires) throw std::runtime_error("witness length does not match the key / constraint system");
         if (r.n_constraints > pk.domain_n) throw std::runtime_error("more constraints than the domain holds");
         uint64_t l0 = launch_counter().load();
-        if (stats) memset(stats, 0, sizeof(*stats));
         cudaStream_t st = ctx->stream;
         const size_t nb = (size_t)pk.domain_n * 32;
         G16_CUDA(cudaEventRecord(ctx->ev[26], st));
-        // a sharded key reads only the wires [w_lo, w_hi) of W: nothing else crosses PCIe
-        ctx->stage[3].reserve((size_t)n_wires * 32);
-        const size_t w_bytes = (size_t)(pk.w_hi - pk.w_lo) * 32;
-        if (w_bytes) G16_CUDA(cudaMemcpyAsync((char*)ctx->stage[3].p + (size_t)pk.w_lo * 32, (const char*)W + (size_t)pk.w_lo * 32, w_bytes, cudaMemcpyHostToDevice, st));
+        // the WHOLE wire vector is uploaded, also for a sharded key: the constraint matrices gather arbitrary wires
+        // (a public wire may appear in O only, i.e. in none of this shard's A / B / K maps)
+        upload(ctx->stage[3], W, (size_t)n_wires * 32, st);
         G16_CUDA(cudaEventRecord(ctx->ev[15], st));
         G16_CUDA(cudaEventRecord(ctx->ev[27], st));
         for (int i = 0; i < 3; i++) ctx->stage[i].reserve(nb);

@@ -871,7 +871,7 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
 
 // Horner over the window sums (host, O(W*c) group operations) -> affine
 template <class C>
-typename C::Aff msm_finish(const MsmWorkspace& ws, const MsmPlan& pl) {
+typename C::Xyzz msm_finish_xyzz(const MsmWorkspace& ws, const MsmPlan& pl) {
     typedef typename C::Xyzz Xyzz;
     const Xyzz* wsum = ws.host_wsum.as<Xyzz>();
     Xyzz acc = C::inf();
@@ -882,7 +882,9 @@ typename C::Aff msm_finish(const MsmWorkspace& ws, const MsmPlan& pl) {
         C::add(u, C::neg(wsum[pl.W + w]));
         C::add(acc, u);
     }
-    return C::to_aff(acc);
+    return acc;
 }
+template <class C>
+typename C::Aff msm_finish(const MsmWorkspace& ws, const MsmPlan& pl) { return C::to_aff(msm_finish_xyzz<C>(ws, pl)); }
 
 }  // namespace g16

@@ -10,6 +10,9 @@ void msm_g1_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* ma
                     int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail = nullptr,
                     int pre_c = 0, MsmWorkspace* sort_from = nullptr);
 G1::Aff msm_g1_finish(const MsmWorkspace& ws, const MsmPlan& plan);
+// the same without the final inversion (multi-GPU: the ranks' partial sums are added before going affine)
+G1::Xyzz msm_g1_finish_xyzz(const MsmWorkspace& ws, const MsmPlan& plan);
+G2::Xyzz msm_g2_finish_xyzz(const MsmWorkspace& ws, const MsmPlan& plan);
 void msm_g2_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const G2::Aff* bases_d, uint64_t n,
                     int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail = nullptr,
                     int pre_c = 0, MsmWorkspace* sort_from = nullptr);

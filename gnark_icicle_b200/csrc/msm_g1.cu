@@ -25,6 +25,7 @@ void msm_g1_precompute(G1::Aff* table_d, uint64_t n, int c, cudaStream_t st) {
     G16_LAUNCH_CHECK();
 }
 G1::Aff msm_g1_finish(const MsmWorkspace& ws, const MsmPlan& plan) { return msm_finish<G1>(ws, plan); }
+G1::Xyzz msm_g1_finish_xyzz(const MsmWorkspace& ws, const MsmPlan& plan) { return msm_finish_xyzz<G1>(ws, plan); }
 
 G1::Aff g1_generator() {
     G1::Aff g;

@@ -23,6 +23,7 @@ void msm_g2_precompute(G2::Aff* table_d, uint64_t n, int c, cudaStream_t st) {
     G16_LAUNCH_CHECK();
 }
 G2::Aff msm_g2_finish(const MsmWorkspace& ws, const MsmPlan& plan) { return msm_finish<G2>(ws, plan); }
+G2::Xyzz msm_g2_finish_xyzz(const MsmWorkspace& ws, const MsmPlan& plan) { return msm_finish_xyzz<G2>(ws, plan); }
 
 // bn254.Generators() G2 (EIP-197), plain integers -> Montgomery
 G2::Aff g2_generator() {

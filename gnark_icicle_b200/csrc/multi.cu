@@ -1,0 +1,616 @@
+// Several GPUs behind ONE context: g16_ctx_create(..., device_ids, n) with n in {2, 4, 8} builds a group of single-GPU
+// contexts ("ranks", one persistent host thread each) and g16_pk_upload / g16_prove_bn254 then shard internally, so a
+// host that can only make the reference's one in-process call (icicle_bn254.Prove, backend/groth16/bn254/icicle/
+// icicle.go:133) reaches every GPU of the box.  No NCCL and no second process: the exchanges of the
+// distributed computeH are stores into peer memory over NVLink / NVSwitch issued by the kernel that changes the layout
+// (ntt.cu k_dist_exchange), ordered by CUDA events across the devices.
+//
+//  * key placement (SURVEY.md 8(e) levels 1 + 2): the five MSMs are laid end to end on a cost line (a G2 point costs
+//    g2_weight/100 G1 points) and the line is cut into n equal parts, so every GPU holds at most two or three LARGE
+//    pieces (G2.B alone fills ~3 of 8 GPUs) instead of 1/n of all five: larger windows, fewer sort heads and tails;
+//  * computeH (level 3): every size-N transform is "local stages - exchange - local stages" between the distribution
+//    D(rb) (rank = position bits [rb, rb+g)) and the block distribution; a, b, c are loaded from the host straight into
+//    D(rb) (strided copies of 2^rb x 32 B), h leaves block-distributed in bit-reversed order and the GPUs that hold a
+//    slice of G1.Z pull the matching range of h from its owners;
+//  * the W MSMs start as soon as W is on the device and run beside computeH; the five partial results of every rank
+//    are summed on the host in XYZZ form and go affine once.
+#include "ctx.cuh"
+
+#include <chrono>
+#include <condition_variable>
+#include <functional>
+#include <thread>
+
+extern "C" int g16_prove_bn254(g16_ctx*, uint64_t, const void*, uint64_t, const void*, const void*, const void*, uint64_t, void*, g16_stats*);
+extern "C" int g16_prove_bn254_dev(g16_ctx*, uint64_t, const void*, void*, void*, void*, void*, g16_stats*);
+extern "C" int g16_prove_bn254_wires(g16_ctx*, uint64_t, uint64_t, const void*, uint64_t, void*, g16_stats*);
+
+namespace g16 {
+
+namespace {
+
+// rendezvous of the rank threads; a failing rank releases everybody
+struct HostBarrier {
+    std::mutex m;
+    std::condition_variable cv;
+    int n = 1, waiting = 0;
+    uint64_t gen = 0;
+    bool failed = false;
+    void reset(int n_) { std::lock_guard<std::mutex> lk(m); n = n_; waiting = 0; failed = false; }
+    bool wait() {
+        std::unique_lock<std::mutex> lk(m);
+        if (failed) return false;
+        const uint64_t g = gen;
+        if (++waiting == n) { waiting = 0; gen++; cv.notify_all(); }
+        else cv.wait(lk, [&] { return gen != g || failed; });
+        return !failed;
+    }
+    void fail() { std::lock_guard<std::mutex> lk(m); failed = true; cv.notify_all(); }
+};
+
+// one persistent host thread per rank >= 1; rank 0 runs on the calling thread
+struct Team {
+    int n = 0;
+    std::vector<std::thread> th;
+    std::mutex m;
+    std::condition_variable cv_go, cv_done;
+    const std::function<void(int)>* job = nullptr;
+    uint64_t gen = 0;
+    int pending = 0;
+    bool stop = false;
+    std::vector<std::string> err;
+
+    void start(int n_) {
+        n = n_;
+        err.assign(n, "");
+        for (int r = 1; r < n; r++) th.emplace_back([this, r] { loop(r); });
+    }
+    void loop(int r) {
+        uint64_t seen = 0;
+        for (;;) {
+            const std::function<void(int)>* f;
+            {
+                std::unique_lock<std::mutex> lk(m);
+                cv_go.wait(lk, [&] { return stop || gen != seen; });
+                if (stop) return;
+                seen = gen;
+                f = job;
+            }
+            try { (*f)(r); } catch (const std::exception& e) { err[r] = e.what(); if (err[r].empty()) err[r] = "error"; }
+            {
+                std::lock_guard<std::mutex> lk(m);
+                pending--;
+            }
+            cv_done.notify_all();
+        }
+    }
+    // f(r) for every rank, concurrently; throws the first rank's error
+    void run(const std::function<void(int)>& f) {
+        for (auto& e : err) e.clear();
+        {
+            std::lock_guard<std::mutex> lk(m);
+            job = &f; gen++; pending = n - 1;
+        }
+        cv_go.notify_all();
+        try { f(0); } catch (const std::exception& e) { err[0] = e.what(); if (err[0].empty()) err[0] = "error"; }
+        {
+            std::unique_lock<std::mutex> lk(m);
+            cv_done.wait(lk, [&] { return pending == 0; });
+        }
+        for (int r = 0; r < n; r++)
+            if (!err[r].empty() && err[r] != "another rank failed") throw std::runtime_error("rank " + std::to_string(r) + ": " + err[r]);
+        for (int r = 0; r < n; r++)
+            if (!err[r].empty()) throw std::runtime_error("rank " + std::to_string(r) + ": " + err[r]);
+    }
+    void shutdown() {
+        {
+            std::lock_guard<std::mutex> lk(m);
+            stop = true;
+        }
+        cv_go.notify_all();
+        for (auto& t : th) t.join();
+        th.clear();
+    }
+};
+
+struct RankState {
+    g16_ctx* ctx = nullptr;
+    cudaStream_t hs = nullptr;       // the distributed computeH (high priority: other GPUs wait for its exchanges)
+    DevBuf buf[2];                   // ping-pong arrays of the distributed computeH, 3 x n/world Fr each
+    DevBuf hbuf;                     // the range of h under this rank's G1.Z slice when other ranks own (part of) it
+    cudaEvent_t ev_x[4] = {};        // [k]: this rank's exchange k has landed everywhere; [3]: its block of h is final
+    cudaEvent_t ev_in = nullptr;     // rank 0: the caller's device-resident inputs are ready
+    ProvePartial part;
+    g16_stats st;
+};
+
+struct GroupPk {
+    int active = 1;                  // ranks that hold a slice (1: a domain too small to distribute lives on rank 0)
+    uint64_t domain_n = 0, n_wires = 0;
+};
+
+}  // namespace
+
+struct MultiGpu {
+    int n = 0, g = 0;
+    std::vector<RankState> rk;
+    Team team;
+    HostBarrier bar;
+    std::map<uint64_t, GroupPk> pks;
+};
+
+namespace {
+
+int split_stage(int L, int g) {
+    int x = L / 2;
+    if (x > L - g) x = L - g;
+    if (x < g) x = g;
+    return x;
+}
+
+void set_device(const RankState& R) { G16_CUDA(cudaSetDevice(R.ctx->device)); }
+
+// dst[arr][q] = src[arr][i(q)], i(q) = the q-th position of this rank under D(rb): device-resident inputs on another
+// (or the same) GPU are read through the peer mapping
+struct PullArgs { const Fr::T* src[3]; Fr::T* dst; uint64_t n_local; int count, rb, g; uint32_t rank; };
+__global__ void __launch_bounds__(256) k_dist_pull(PullArgs a) {
+    const uint64_t total = (uint64_t)a.count * a.n_local, rmask = (1ull << a.rb) - 1;
+    for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t arr = e / a.n_local, q = e % a.n_local;
+        const uint64_t i = ((q >> a.rb) << (a.rb + a.g)) | ((uint64_t)a.rank << a.rb) | (q & rmask);
+        const uint4* s = reinterpret_cast<const uint4*>(a.src[arr] + i);
+        uint4* d = reinterpret_cast<uint4*>(a.dst + e);
+        const uint4 lo = s[0], hi = s[1];
+        d[0] = lo; d[1] = hi;
+    }
+}
+
+// one array of a, b, c from host memory into D(rb): rows of 2^rb elements, `n_constraints` elements exist, the rest is zero
+void load_host_rows(Fr::T* dst, const void* src, uint64_t n_constraints, uint64_t n, uint64_t n_local, int rb, int g, uint32_t rank, cudaStream_t st) {
+    const uint64_t row = 1ull << rb, rows = n_local >> rb, pitch = row << g;
+    auto start = [&](uint64_t hi) { return hi * pitch + (uint64_t)rank * row; };
+    if (n_constraints < n) G16_CUDA(cudaMemsetAsync(dst, 0, (size_t)n_local * sizeof(Fr::T), st));
+    uint64_t full = 0;                                   // rows that lie wholly below n_constraints
+    if (n_constraints >= (uint64_t)rank * row + row) {
+        full = (n_constraints - (uint64_t)rank * row - row) / pitch + 1;
+        if (full > rows) full = rows;
+    }
+    const char* s = (const char*)src;
+    if (full) {
+        if (g == 0 || rows == 1) G16_CUDA(cudaMemcpyAsync(dst, s + start(0) * 32, (size_t)full * row * 32, cudaMemcpyHostToDevice, st));
+        else G16_CUDA(cudaMemcpy2DAsync(dst, row * 32, s + start(0) * 32, pitch * 32, row * 32, full, cudaMemcpyHostToDevice, st));
+    }
+    if (full < rows && start(full) < n_constraints)
+        G16_CUDA(cudaMemcpyAsync(dst + full * row, s + start(full) * 32, (size_t)(n_constraints - start(full)) * 32, cudaMemcpyHostToDevice, st));
+}
+
+// cut the cost line [BS2 | AR | KRS_K | BS1 | KRS_HZ] into `parts` equal pieces
+std::vector<PkRanges> place_key(const uint64_t lens[5], int parts, double g2_weight) {
+    const int order[5] = {G16_OUT_BS2, G16_OUT_AR, G16_OUT_KRS_K, G16_OUT_BS1, G16_OUT_KRS_HZ};
+    double w[5], begin[5], total = 0;
+    for (int k = 0; k < 5; k++) {
+        const int i = order[k];
+        w[i] = i == G16_OUT_BS2 ? g2_weight : 1.0;
+        begin[i] = total;
+        total += (double)lens[i] * w[i];
+    }
+    // position of cut c (cost c * total / parts) inside array i, snapped to the array's ends when it falls within 3 % of a part
+    auto cut = [&](int c, int i) -> uint64_t {
+        if (c <= 0) return 0;
+        if (c >= parts) return lens[i];
+        const double cost = total * c / parts, tol = 0.03 * total / parts, len = (double)lens[i] * w[i];
+        if (cost <= begin[i] + tol) return 0;
+        if (cost >= begin[i] + len - tol) return lens[i];
+        uint64_t p = (uint64_t)((cost - begin[i]) / w[i] + 0.5);
+        return p > lens[i] ? lens[i] : p;
+    };
+    std::vector<PkRanges> out(parts);
+    for (int r = 0; r < parts; r++)
+        for (int i = 0; i < 5; i++) { out[r].lo[i] = cut(r, i); out[r].hi[i] = cut(r + 1, i); }
+    return out;
+}
+
+void upload_r1cs_to(g16_ctx* c, const g16_r1cs_desc* d, uint64_t handle) {
+    R1csDev r;
+    r.n_constraints = d->n_constraints; r.n_wires = d->n_wires; r.n_coeffs = d->n_coeffs;
+    cudaStream_t st = c->stream;
+    try {
+        upload(r.coeffs, d->coeffs, (size_t)d->n_coeffs * 32, st);
+        for (int m = 0; m < 3; m++) {
+            const uint64_t nnz = d->row_ptr[m][d->n_constraints];
+            upload(r.row_ptr[m], d->row_ptr[m], (size_t)(d->n_constraints + 1) * 4, st);
+            upload(r.wire[m], d->wire[m], (size_t)nnz * 4, st);
+            upload(r.cid[m], d->coeff_id[m], (size_t)nnz * 4, st);
+        }
+        G16_CUDA(cudaStreamSynchronize(st));
+    } catch (...) {
+        r.release();
+        throw;
+    }
+    c->r1cs[handle] = r;
+}
+
+}  // namespace
+
+// =================================================================== group life cycle
+MultiGpu* multi_create(g16_ctx* rank0, const int* device_ids, int n_devices) {
+    std::unique_ptr<MultiGpu> mg(new MultiGpu());
+    mg->n = n_devices;
+    mg->g = ilog2_ceil((uint64_t)n_devices);
+    mg->rk.resize(n_devices);
+    try {
+        mg->rk[0].ctx = rank0;
+        for (int r = 1; r < n_devices; r++) mg->rk[r].ctx = ctx_create_single(device_ids[r]);
+        // every GPU of the group maps every other one (NVLink / NVSwitch peer access); the same device may be listed
+        // several times (ranks emulated on one GPU: tests), which needs no mapping
+        for (int a = 0; a < n_devices; a++) {
+            RankState& R = mg->rk[a];
+            set_device(R);
+            for (int b = 0; b < n_devices; b++) {
+                const int da = R.ctx->device, db = mg->rk[b].ctx->device;
+                if (da == db) continue;
+                int can = 0;
+                G16_CUDA(cudaDeviceCanAccessPeer(&can, da, db));
+                if (!can) throw std::runtime_error("GPU " + std::to_string(da) + " cannot map GPU " + std::to_string(db) + " (no peer access)");
+                cudaError_t e = cudaDeviceEnablePeerAccess(db, 0);
+                if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+                else G16_CUDA(e);
+            }
+            int prio_lo = 0, prio_hi = 0;
+            G16_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+            G16_CUDA(cudaStreamCreateWithPriority(&R.hs, cudaStreamNonBlocking, prio_hi));
+            for (auto& e : R.ev_x) G16_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            G16_CUDA(cudaEventCreateWithFlags(&R.ev_in, cudaEventDisableTiming));
+        }
+        G16_CUDA(cudaSetDevice(rank0->device));
+    } catch (...) {
+        multi_destroy(mg.release());
+        cudaSetDevice(rank0->device);
+        throw;
+    }
+    mg->team.start(n_devices);
+    return mg.release();
+}
+
+void multi_destroy(MultiGpu* mg) {
+    if (!mg) return;
+    mg->team.shutdown();
+    for (int r = 0; r < mg->n; r++) {
+        RankState& R = mg->rk[r];
+        if (!R.ctx) continue;
+        cudaSetDevice(R.ctx->device);
+        cudaDeviceSynchronize();
+        R.buf[0].release(); R.buf[1].release(); R.hbuf.release();
+        for (auto& e : R.ev_x) if (e) cudaEventDestroy(e);
+        if (R.ev_in) cudaEventDestroy(R.ev_in);
+        if (R.hs) cudaStreamDestroy(R.hs);
+        if (r > 0) ctx_destroy_single(R.ctx);   // rank 0 belongs to the caller (g16_ctx_destroy)
+    }
+    cudaSetDevice(mg->rk[0].ctx->device);
+    delete mg;
+}
+
+void multi_set(MultiGpu* mg, const char* key, int64_t value) {
+    const std::string k(key);
+    for (int r = 1; r < mg->n; r++) {
+        g16_ctx* c = mg->rk[r].ctx;
+        if (k == "msm_c") c->msm_c = (int)value;
+        else if (k == "msm_waves") c->msm_waves = (int)value;
+        else if (k == "streams") c->streams = (int)value;
+        else if (k == "msm_precompute") c->msm_precompute = (int)value;
+        else if (k == "msm_pre_c") c->msm_pre_c = (int)value;
+    }
+}
+
+// =================================================================== key
+void multi_pk_upload(g16_ctx* ctx, const g16_pk_desc* d, const Src* src, uint64_t* pk_handle) {
+    MultiGpu& mg = *ctx->multi;
+    pk_validate(d);
+    if (d->shard_count > 1) throw std::runtime_error("a multi-GPU context shards the key itself: shard_count must be 0 or 1");
+    GroupPk gp;
+    gp.domain_n = d->domain_n; gp.n_wires = d->n_wires;
+    const int L = ilog2_ceil(d->domain_n);
+    gp.active = L >= 2 * mg.g + 4 ? mg.n : 1;   // every rank needs a few stages on either side of the exchanges
+    const uint64_t lens[5] = {d->n_a, d->n_b, d->n_k, d->n_z < d->domain_n ? d->n_z : d->domain_n - 1, d->n_b2};
+    std::vector<PkRanges> place = place_key(lens, gp.active, ctx->g2_weight / 100.0);
+    PkRanges none;
+    for (int i = 0; i < 5; i++) none.lo[i] = none.hi[i] = 0;
+    const uint64_t h = ctx->next_pk++;
+    try {
+        mg.team.run([&](int r) {
+            set_device(mg.rk[r]);
+            pk_upload_ranges(mg.rk[r].ctx, d, src, r < gp.active ? place[r] : none, h);
+        });
+    } catch (...) {
+        for (int r = 0; r < mg.n; r++) {
+            g16_ctx* c = mg.rk[r].ctx;
+            auto it = c->pks.find(h);
+            if (it != c->pks.end()) { cudaSetDevice(c->device); cudaDeviceSynchronize(); it->second.release(); c->pks.erase(it); }
+        }
+        cudaSetDevice(ctx->device);
+        throw;
+    }
+    G16_CUDA(cudaSetDevice(ctx->device));
+    mg.pks[h] = gp;
+    *pk_handle = h;
+}
+
+void multi_pk_free(g16_ctx* ctx, uint64_t pk_handle) {
+    MultiGpu& mg = *ctx->multi;
+    if (!mg.pks.count(pk_handle)) throw std::runtime_error("unknown proving-key handle");
+    for (int r = 0; r < mg.n; r++) {
+        g16_ctx* c = mg.rk[r].ctx;
+        G16_CUDA(cudaSetDevice(c->device));
+        G16_CUDA(cudaDeviceSynchronize());
+        auto it = c->pks.find(pk_handle);
+        if (it != c->pks.end()) { it->second.release(); c->pks.erase(it); }
+    }
+    G16_CUDA(cudaSetDevice(ctx->device));
+    mg.pks.erase(pk_handle);
+}
+
+void multi_pk_wire_range(g16_ctx* ctx, uint64_t pk_handle, uint64_t* lo, uint64_t* hi) {
+    MultiGpu& mg = *ctx->multi;
+    if (!mg.pks.count(pk_handle)) throw std::runtime_error("unknown proving-key handle");
+    uint64_t l = ~0ull, h = 0;
+    for (int r = 0; r < mg.n; r++) {
+        const PkDev& pk = mg.rk[r].ctx->pks.at(pk_handle);
+        if (pk.w_hi > pk.w_lo) { if (pk.w_lo < l) l = pk.w_lo; if (pk.w_hi > h) h = pk.w_hi; }
+    }
+    *lo = h > l ? l : 0; *hi = h > l ? h : 0;
+}
+
+const PkDev& multi_pk_of_rank(g16_ctx* ctx, uint64_t pk_handle, int rank) {
+    MultiGpu& mg = *ctx->multi;
+    if (!mg.pks.count(pk_handle)) throw std::runtime_error("unknown proving-key handle");
+    if (rank < 0 || rank >= mg.n) throw std::runtime_error("rank out of range");
+    return mg.rk[rank].ctx->pks.at(pk_handle);
+}
+
+void multi_r1cs_upload(g16_ctx* ctx, const g16_r1cs_desc* d, uint64_t handle) {
+    MultiGpu& mg = *ctx->multi;
+    try {
+        mg.team.run([&](int r) {
+            if (r == 0) return;                 // rank 0 = ctx itself: uploaded (and validated) by g16_r1cs_upload
+            set_device(mg.rk[r]);
+            upload_r1cs_to(mg.rk[r].ctx, d, handle);
+        });
+    } catch (...) {
+        multi_r1cs_free(ctx, handle);
+        throw;
+    }
+    G16_CUDA(cudaSetDevice(ctx->device));
+}
+
+void multi_r1cs_free(g16_ctx* ctx, uint64_t handle) {
+    MultiGpu& mg = *ctx->multi;
+    for (int r = 1; r < mg.n; r++) {
+        g16_ctx* c = mg.rk[r].ctx;
+        auto it = c->r1cs.find(handle);
+        if (it == c->r1cs.end()) continue;
+        cudaSetDevice(c->device);
+        cudaDeviceSynchronize();
+        it->second.release();
+        c->r1cs.erase(it);
+    }
+    cudaSetDevice(ctx->device);
+}
+
+// =================================================================== prove
+namespace {
+
+struct ProveJob {
+    MultiGpu* mg;
+    uint64_t handle;
+    const MultiIn* in;
+    int L, g, X, rb;
+    uint64_t n, n_local;
+    uint64_t launches0;
+};
+
+void rank_prove(const ProveJob& J, int r) {
+    MultiGpu& mg = *J.mg;
+    RankState& R = mg.rk[r];
+    g16_ctx* c = R.ctx;
+    const MultiIn& in = *J.in;
+    set_device(R);
+    PkDev& pk = c->pks.at(J.handle);
+    cudaStream_t st = c->stream, hs = R.hs;
+    const int g = J.g, rb = J.rb, X = J.X;
+    const uint64_t n = J.n, n_local = J.n_local;
+    memset(&R.st, 0, sizeof(R.st));
+
+    // buffers exist before anybody stores into them
+    R.buf[0].reserve((size_t)3 * n_local * sizeof(Fr::T));
+    R.buf[1].reserve((size_t)3 * n_local * sizeof(Fr::T));
+    const R1csDev* rdev = nullptr;
+    if (in.r1cs) {
+        auto ir = c->r1cs.find(in.r1cs);
+        if (ir == c->r1cs.end()) throw std::runtime_error("unknown R1CS handle");
+        rdev = &ir->second;
+        if (rdev->n_wires != pk.n_wires || rdev->n_constraints > n) throw std::runtime_error("constraint system does not match the proving key");
+    }
+    if (!mg.bar.wait()) throw std::runtime_error("another rank failed");
+
+    G16_CUDA(cudaEventRecord(c->ev[26], st));
+    if (in.device) {       // the caller's arrays are ready once rank 0's stream reaches ev_in (recorded before the ranks started)
+        G16_CUDA(cudaStreamWaitEvent(st, mg.rk[0].ev_in, 0));
+        G16_CUDA(cudaStreamWaitEvent(hs, mg.rk[0].ev_in, 0));
+    }
+    // ---- W: the wires this rank's slices of A, B, K read (all of them when a, b, c are evaluated here)
+    const uint64_t w_lo = rdev ? 0 : pk.w_lo, w_hi = rdev ? pk.n_wires : pk.w_hi;
+    const size_t w_bytes = (size_t)(w_hi - w_lo) * 32;
+    const Fr::T* W_ptr;
+    const int dev0 = mg.rk[0].ctx->device;
+    if (in.device && c->device == dev0) {
+        W_ptr = (const Fr::T*)in.W;
+    } else {
+        c->stage[3].reserve((size_t)pk.n_wires * 32);
+        char* dst = (char*)c->stage[3].p + (size_t)w_lo * 32;
+        const char* srcp = (const char*)in.W + (size_t)w_lo * 32;
+        if (w_bytes) {
+            if (in.device) G16_CUDA(cudaMemcpyPeerAsync(dst, c->device, srcp, dev0, w_bytes, st));
+            else G16_CUDA(cudaMemcpyAsync(dst, srcp, w_bytes, cudaMemcpyHostToDevice, st));
+        }
+        W_ptr = c->stage[3].as<Fr::T>();
+        R.st.h2d_bytes += in.device ? 0 : w_bytes;
+    }
+    G16_CUDA(cudaEventRecord(c->ev[15], st));
+    // ---- the MSMs over W start now, on their own streams
+    prove_device(c, pk, W_ptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, c->ev[15], true, 1);
+
+    // ---- a, b, c of this rank in D(rb)
+    Fr::T* A = R.buf[0].as<Fr::T>();
+    Fr::T* B = R.buf[1].as<Fr::T>();
+    if (rdev) {
+        G16_CUDA(cudaStreamWaitEvent(hs, c->ev[15], 0));
+        r1cs_eval(*rdev, W_ptr, A, A + n_local, A + 2 * n_local, n, hs, rb, g, (uint32_t)r);
+    } else if (in.device) {
+        PullArgs pa;
+        pa.src[0] = (const Fr::T*)in.a; pa.src[1] = (const Fr::T*)in.b; pa.src[2] = (const Fr::T*)in.c;
+        pa.dst = A; pa.n_local = n_local; pa.count = 3; pa.rb = rb; pa.g = g; pa.rank = (uint32_t)r;
+        unsigned blocks = (unsigned)((3 * n_local + 255) / 256);
+        if (blocks > 148 * 16) blocks = 148 * 16;
+        k_dist_pull<<<blocks, 256, 0, hs>>>(pa);
+        G16_LAUNCH_CHECK();
+    } else {
+        const void* srcs[3] = {in.a, in.b, in.c};
+        for (int i = 0; i < 3; i++) load_host_rows(A + i * n_local, srcs[i], in.n_constraints, n, n_local, rb, g, (uint32_t)r, hs);
+        uint64_t mine = 0;   // elements of one array that exist on this rank
+        for (uint64_t hi = 0; hi < (n_local >> rb); hi++) {
+            const uint64_t s = (hi << (rb + g)) + ((uint64_t)r << rb);
+            if (s >= in.n_constraints) break;
+            mine += in.n_constraints - s < (1ull << rb) ? in.n_constraints - s : (1ull << rb);
+        }
+        R.st.h2d_bytes += 3 * mine * 32;
+    }
+    G16_CUDA(cudaEventRecord(c->ev[27], hs));
+
+    // ---- distributed computeH (prove.go:356-399): 3 exchanges
+    NttDomain& dom = c->domain(J.L);
+    auto batch = [&](Fr::T* p, int count) { return NttBatch{{p, p + (count > 1 ? n_local : 0), p + (count > 2 ? 2 * n_local : 0)}, count}; };
+    auto exchange = [&](int k, const Fr::T* src, int target, int count, int to_block) {
+        DistExchange a;
+        for (int p = 0; p < 8; p++) a.dst[p] = p < mg.n ? mg.rk[p].buf[target].as<Fr::T>() : nullptr;
+        a.src = src; a.count = count; a.n_local = n_local; a.g = g; a.L = J.L; a.rb = rb; a.rank = (uint32_t)r; a.to_block = to_block;
+        ntt_dist_exchange(a, hs);
+        G16_CUDA(cudaEventRecord(R.ev_x[k], hs));
+        if (!mg.bar.wait()) throw std::runtime_error("another rank failed");        // every rank has recorded its event
+        for (int p = 0; p < mg.n; p++) G16_CUDA(cudaStreamWaitEvent(hs, mg.rk[p].ev_x[k], 0));
+    };
+    G16_CUDA(cudaEventRecord(c->ev[30], hs));
+    ntt_dist_stages(dom, batch(A, 3), TW_INV, true, g, (uint32_t)r, true, X, hs, rb);          // 3 x iNTT, upper stages
+    exchange(0, A, 1, 3, 1);
+    ntt_dist_stages(dom, batch(B, 3), TW_INV, true, g, (uint32_t)r, false, X, hs);             //           lower stages
+    ntt_dist_stages(dom, batch(B, 3), TW_COSET_FWD, false, g, (uint32_t)r, false, X, hs);      // 3 x coset NTT, lower stages
+    exchange(1, B, 0, 3, 0);
+    ntt_dist_stages(dom, batch(A, 3), TW_COSET_FWD, false, g, (uint32_t)r, true, X, hs, rb);   //               upper stages
+    fr_pointwise_h(A, A + n_local, A + 2 * n_local, n_local, dom.h_c1, dom.h_c2, hs);
+    ntt_dist_stages(dom, batch(A, 1), TW_COSET_INV, true, g, (uint32_t)r, true, X, hs, rb);    // coset iNTT, upper stages
+    exchange(2, A, 1, 1, 1);
+    ntt_dist_stages(dom, batch(B, 1), TW_COSET_INV, true, g, (uint32_t)r, false, X, hs);       //            lower stages
+    G16_CUDA(cudaEventRecord(R.ev_x[3], hs));   // this rank's block of h (bit-reversed order) is final in buf[1]
+    G16_CUDA(cudaEventRecord(c->ev[31], hs));
+    if (!mg.bar.wait()) throw std::runtime_error("another rank failed");
+
+    // ---- h under this rank's slice of G1.Z
+    const Fr::T* h_ptr = B;
+    if (pk.n_z) {
+        const uint64_t z_lo = pk.z_off, z_hi = pk.z_off + pk.n_z;
+        const uint64_t p0 = z_lo / n_local, p1 = (z_hi - 1) / n_local;
+        if (p0 == p1 && (int)p0 == r) {
+            G16_CUDA(cudaStreamWaitEvent(st, R.ev_x[3], 0));
+            h_ptr = B + (z_lo - p0 * n_local);
+        } else {
+            R.hbuf.reserve((size_t)pk.n_z * sizeof(Fr::T));
+            for (uint64_t p = p0; p <= p1; p++) {
+                const uint64_t s = z_lo > p * n_local ? z_lo : p * n_local, e = z_hi < (p + 1) * n_local ? z_hi : (p + 1) * n_local;
+                G16_CUDA(cudaStreamWaitEvent(st, mg.rk[p].ev_x[3], 0));
+                G16_CUDA(cudaMemcpyPeerAsync(R.hbuf.as<Fr::T>() + (s - z_lo), c->device, mg.rk[p].buf[1].as<Fr::T>() + (s - p * n_local),
+                                             mg.rk[p].ctx->device, (size_t)(e - s) * sizeof(Fr::T), st));
+            }
+            h_ptr = R.hbuf.as<Fr::T>();
+        }
+    }
+    // ---- H.Z MSM, wait for all five, window sums -> XYZZ partial results
+    prove_device(c, pk, W_ptr, const_cast<Fr::T*>(h_ptr), nullptr, nullptr, nullptr, &R.st, J.launches0, nullptr, true, 2, &R.part);
+    G16_CUDA(cudaStreamSynchronize(hs));
+    G16_CUDA(cudaEventElapsedTime(&R.st.ms_compute_h, c->ev[30], c->ev[31]));
+    G16_CUDA(cudaEventElapsedTime(&R.st.ms_total, c->ev[26], c->ev[14]));
+}
+
+}  // namespace
+
+void multi_prove(g16_ctx* ctx, uint64_t pk_handle, const MultiIn& in, void* out_points, g16_stats* stats) {
+    MultiGpu& mg = *ctx->multi;
+    auto ig = mg.pks.find(pk_handle);
+    if (ig == mg.pks.end()) throw std::runtime_error("unknown proving-key handle");
+    const GroupPk& gp = ig->second;
+    if (!in.device && in.n_wires != gp.n_wires) throw std::runtime_error("witness length does not match the proving key");
+    if (!in.device && !in.r1cs && in.n_constraints > gp.domain_n) throw std::runtime_error("more constraints than the domain holds");
+    if (gp.active == 1) {
+        // a domain too small to distribute: the whole key lives on rank 0, which proves alone
+        ctx->multi = nullptr;
+        int rc;
+        if (in.r1cs) rc = g16_prove_bn254_wires(ctx, pk_handle, in.r1cs, in.W, in.n_wires, out_points, stats);
+        else if (in.device) rc = g16_prove_bn254_dev(ctx, pk_handle, in.W, (void*)in.a, (void*)in.b, (void*)in.c, out_points, stats);
+        else rc = g16_prove_bn254(ctx, pk_handle, in.W, in.n_wires, in.a, in.b, in.c, in.n_constraints, out_points, stats);
+        ctx->multi = &mg;
+        if (rc) throw std::runtime_error(ctx->err);
+        return;
+    }
+    ProveJob J;
+    J.mg = &mg; J.handle = pk_handle; J.in = &in;
+    J.n = gp.domain_n; J.L = ilog2_ceil(J.n); J.g = mg.g; J.X = split_stage(J.L, J.g); J.rb = J.X - J.g;
+    J.n_local = J.n >> J.g;
+    J.launches0 = launch_counter().load();
+    if (in.device) G16_CUDA(cudaEventRecord(mg.rk[0].ev_in, ctx->stream));
+    mg.bar.reset(mg.n);
+    const auto t0 = std::chrono::steady_clock::now();
+    try {
+        mg.team.run([&](int r) {
+            try { rank_prove(J, r); }
+            catch (...) { mg.bar.fail(); cudaDeviceSynchronize(); cudaGetLastError(); throw; }
+        });
+    } catch (...) {
+        cudaSetDevice(ctx->device);
+        throw;
+    }
+    G16_CUDA(cudaSetDevice(ctx->device));
+    // sum the ranks' partial results in XYZZ form, one inversion per point
+    const auto t1 = std::chrono::steady_clock::now();
+    char* out = (char*)out_points;
+    for (int i = 0; i < 4; i++) {
+        G1::Xyzz acc = mg.rk[0].part.g1[i];
+        for (int r = 1; r < mg.n; r++) G1::add(acc, mg.rk[r].part.g1[i]);
+        copy_out(out + G1SZ * i, G1::to_aff(acc));
+    }
+    {
+        G2::Xyzz acc = mg.rk[0].part.g2;
+        for (int r = 1; r < mg.n; r++) G2::add(acc, mg.rk[r].part.g2);
+        copy_out(out + 4 * G1SZ, G2::to_aff(acc));
+    }
+    const auto t2 = std::chrono::steady_clock::now();
+    if (stats) {
+        memset(stats, 0, sizeof(*stats));
+        for (int r = 0; r < mg.n; r++) {
+            const g16_stats& s = mg.rk[r].st;
+            if (s.ms_total > stats->ms_total) stats->ms_total = s.ms_total;
+            if (s.ms_compute_h > stats->ms_compute_h) stats->ms_compute_h = s.ms_compute_h;
+            if (s.ms_host > stats->ms_host) stats->ms_host = s.ms_host;
+            for (int i = 0; i < 5; i++) {
+                if (s.ms_msm[i] > stats->ms_msm[i]) stats->ms_msm[i] = s.ms_msm[i];
+                if (s.ms_accumulate[i] > stats->ms_accumulate[i]) stats->ms_accumulate[i] = s.ms_accumulate[i];
+                if (s.msm_n[i] && (!stats->msm_c[i] || s.msm_c[i] < stats->msm_c[i])) { stats->msm_c[i] = s.msm_c[i]; stats->msm_windows[i] = s.msm_windows[i]; }
+                stats->msm_n[i] += s.msm_n[i];
+            }
+            stats->h2d_bytes += s.h2d_bytes;
+            stats->d2h_bytes += s.d2h_bytes;
+        }
+        stats->ms_host += std::chrono::duration<float, std::milli>(t2 - t1).count();
+        stats->kernel_launches = (uint32_t)(launch_counter().load() - J.launches0);
+        stats->ms_wall = std::chrono::duration<float, std::milli>(t2 - t0).count();   // wall clock of the group call
+    }
+}
+
+}  // namespace g16

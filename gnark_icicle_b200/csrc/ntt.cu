@@ -114,8 +114,9 @@ struct PassArgs {
     int s;   // log2 of the row stride (= log2 of the smallest half-size handled by this sweep)
     int k;   // stages in this sweep (tile rows = 2^k)
     int cb;  // log2 of tile columns
-    int g;   // cyclic-distributed sweeps: log2(world); local index q stands for global position q*2^g + rank
-    uint32_t rank;
+    int g;   // distributed sweeps on the D(rb) distribution: log2(world); the rank owns the positions whose bits
+    int rb;  //   [rb, rb+g) equal `rank`, local index q = those positions with the rank bits squeezed out
+    uint32_t rank;   //   (rb = 0: the cyclic distribution, local q stands for global position q*2^g + rank)
 };
 
 __device__ __forceinline__ Fr::T ld_planes(const uint4* lo, const uint4* hi, int e) {
@@ -171,7 +172,8 @@ __global__ void __launch_bounds__(NTT_THREADS) k_ntt_pass(PassArgs a) {
             int e1 = e0 + (1 << (m + cb));
             uint64_t q = qbase + c;
             uint64_t j = ((uint64_t)(r0 & mmask) << s) | (q & smask);
-            Fr::T t = ldg_fr(tws + ((j << a.g) | a.rank));
+            const uint64_t jg = ((j >> a.rb) << (a.rb + a.g)) | ((uint64_t)a.rank << a.rb) | (j & ((1ull << a.rb) - 1));
+            Fr::T t = ldg_fr(tws + jg);
             // butterflies in the lazily reduced field (values in [0, 2r) while the tile is in shared memory)
             Fr::T u = ld_planes(lo, hi, e0), v = ld_planes(lo, hi, e1);
             if (DIF) {
@@ -223,10 +225,10 @@ static std::vector<Sweep> plan_range(int lo, int hi) {
 static std::vector<Sweep> plan_sweeps(int logn) { return plan_range(0, logn); }
 
 template <bool DIF>
-static void launch_sweep(uint64_t n_local, const NttBatch& b, const Fr::T* tw, const Sweep& sw, cudaStream_t st, int g = 0, uint32_t rank = 0) {
+static void launch_sweep(uint64_t n_local, const NttBatch& b, const Fr::T* tw, const Sweep& sw, cudaStream_t st, int g = 0, uint32_t rank = 0, int rb = 0) {
     PassArgs a;
     for (int i = 0; i < 3; i++) a.p[i] = b.p[i < b.count ? i : 0];
-    a.tw = tw; a.s = sw.s; a.k = sw.k; a.cb = sw.cb; a.g = g; a.rank = rank;
+    a.tw = tw; a.s = sw.s; a.k = sw.k; a.cb = sw.cb; a.g = g; a.rank = rank; a.rb = rb;
     size_t smem = (size_t)2 * sizeof(uint4) << (sw.k + sw.cb);
     if (smem > 48 * 1024)
         G16_CUDA(cudaFuncSetAttribute(k_ntt_pass<DIF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -302,14 +304,50 @@ void fr_mul_vec(Fr::T* out, const Fr::T* a, const Fr::T* b, uint64_t n, cudaStre
 // CYCLIC distribution (rank r holds positions q*G + r; pairs stay local because the half-size is a multiple of G),
 // stages below X run on the BLOCK distribution (rank r holds [r n/G, (r+1) n/G)).  One all-to-all between the two
 // (the four-step transpose) -- the twiddles need no extra pass because every stage has its own table.
-void ntt_dist_stages(NttDomain& d, const NttBatch& b, NttTable t, bool dif, int world_log, uint32_t rank, bool cyclic, int split, cudaStream_t st) {
+// rb generalises "cyclic" (rb = 0) to the distribution D(rb): the rank is given by the position bits [rb, rb+g).  Every stage
+// with half-size 2^t, t outside [rb, rb+g), is local under D(rb); the block distribution is D(L-g).  With rb = split - g the
+// upper phase runs on runs of 2^rb consecutive positions, so host arrays can be loaded straight into it (strided copies of
+// 2^rb x 32 B) and the exchanges move contiguous runs (multi.cu).
+void ntt_dist_stages(NttDomain& d, const NttBatch& b, NttTable t, bool dif, int world_log, uint32_t rank, bool cyclic, int split, cudaStream_t st, int rb) {
     const Fr::T* tw = d.table(t, st);
     const int L = d.logn, g = world_log, Ll = L - g;
     if (split < g || split > Ll) throw std::runtime_error("distributed NTT: split stage must lie in [log2(world), log2(n/world)]");
+    if (rb < 0 || rb + g > split) throw std::runtime_error("distributed NTT: rank bits must lie below the split stage");
     const uint64_t n_local = d.n >> g;
     std::vector<Sweep> v = cyclic ? plan_range(split - g, Ll) : plan_range(0, split);
-    if (dif) for (int i = (int)v.size() - 1; i >= 0; i--) launch_sweep<true>(n_local, b, tw, v[i], st, cyclic ? g : 0, cyclic ? rank : 0);
-    else for (size_t i = 0; i < v.size(); i++) launch_sweep<false>(n_local, b, tw, v[i], st, cyclic ? g : 0, cyclic ? rank : 0);
+    if (dif) for (int i = (int)v.size() - 1; i >= 0; i--) launch_sweep<true>(n_local, b, tw, v[i], st, cyclic ? g : 0, cyclic ? rank : 0, cyclic ? rb : 0);
+    else for (size_t i = 0; i < v.size(); i++) launch_sweep<false>(n_local, b, tw, v[i], st, cyclic ? g : 0, cyclic ? rank : 0, cyclic ? rb : 0);
+}
+
+// The exchange between the two phases of a distributed transform, fused with both layout changes: every element of the
+// local arrays is stored straight into its final place on the GPU that owns it in the other distribution (peer memory
+// over NVLink / NVSwitch; the local share is an ordinary store).  Runs of 2^rb elements stay contiguous on both sides.
+__global__ void __launch_bounds__(256) k_dist_exchange(DistExchange a) {
+    const uint64_t total = (uint64_t)a.count * a.n_local;
+    const uint64_t rmask = (1ull << a.rb) - 1, lmask = a.n_local - 1;
+    const int Ll = a.L - a.g;
+    for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t arr = e / a.n_local, q = e & lmask;
+        uint64_t dq; uint32_t dr;
+        if (a.to_block) {   // D(rb) -> block
+            const uint64_t i = ((q >> a.rb) << (a.rb + a.g)) | ((uint64_t)a.rank << a.rb) | (q & rmask);
+            dr = (uint32_t)(i >> Ll); dq = i & lmask;
+        } else {            // block -> D(rb)
+            const uint64_t i = ((uint64_t)a.rank << Ll) | q;
+            dr = (uint32_t)(i >> a.rb) & ((1u << a.g) - 1); dq = ((i >> (a.rb + a.g)) << a.rb) | (i & rmask);
+        }
+        const uint4* src = reinterpret_cast<const uint4*>(a.src + e);
+        uint4* dst = reinterpret_cast<uint4*>(a.dst[dr] + arr * a.n_local + dq);
+        const uint4 lo = src[0], hi = src[1];
+        dst[0] = lo; dst[1] = hi;
+    }
+}
+void ntt_dist_exchange(const DistExchange& a, cudaStream_t st) {
+    const uint64_t total = (uint64_t)a.count * a.n_local;
+    unsigned blocks = (unsigned)((total + 255) / 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    k_dist_exchange<<<blocks, 256, 0, st>>>(a);
+    G16_LAUNCH_CHECK();
 }
 
 // wire layout of an all-to-all: [peer x][array][q'], q' < m = n_local / G.

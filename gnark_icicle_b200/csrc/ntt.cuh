@@ -53,7 +53,11 @@ void compute_h_noalloc(int device, const Fr::T* a, const Fr::T* b, const Fr::T* 
                        Fr::T* h_out, cudaStream_t st);
 
 // distributed building blocks (see ntt.cu)
-void ntt_dist_stages(NttDomain& d, const NttBatch& b, NttTable t, bool dif, int world_log, uint32_t rank, bool cyclic, int split, cudaStream_t st);
+void ntt_dist_stages(NttDomain& d, const NttBatch& b, NttTable t, bool dif, int world_log, uint32_t rank, bool cyclic, int split, cudaStream_t st, int rb = 0);
+// fused layout change + peer store between the D(rb) and the block distribution (see ntt.cu); dst[r] = base of rank r's
+// receive arrays (count arrays of n_local elements, back to back), peer-mapped
+struct DistExchange { Fr::T* dst[8]; const Fr::T* src; int count; uint64_t n_local; int g, L, rb; uint32_t rank; int to_block; };
+void ntt_dist_exchange(const DistExchange& a, cudaStream_t st);
 void ntt_dist_permute(const Fr::T* src, Fr::T* dst, int count, uint64_t n_local, uint32_t world, int block_layout, int to_wire, cudaStream_t st);
 
 // tile shape of a sweep: log2 of the elements per tile / of the columns per tile

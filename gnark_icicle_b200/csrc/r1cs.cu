@@ -20,11 +20,14 @@ __device__ __forceinline__ Fr::T ld_fr(const Fr::T* p) {
     return r;
 }
 
+// rb, g, rank: this GPU produces the rows whose index bits [rb, rb+g) equal `rank` (the distribution a multi-GPU
+// computeH starts from, multi.cu); local row q is global row i.  g = 0: all rows.
 __global__ void __launch_bounds__(256) k_r1cs_eval(R1csArgs a, const Fr::T* __restrict__ coeffs, const Fr::T* __restrict__ W,
-                                                   uint64_t n_constraints, uint64_t domain_n) {
-    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+                                                   uint64_t n_constraints, uint64_t n_local, int rb, int g, uint32_t rank) {
+    const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int m = blockIdx.y;
-    if (i >= domain_n) return;
+    if (q >= n_local) return;
+    const uint64_t i = ((q >> rb) << (rb + g)) | ((uint64_t)rank << rb) | (q & ((1ull << rb) - 1));
     Fr::T acc = Fr::zero();
     if (i < n_constraints) {
         const uint32_t lo = a.row_ptr[m][i], hi = a.row_ptr[m][i + 1];
@@ -36,12 +39,14 @@ __global__ void __launch_bounds__(256) k_r1cs_eval(R1csArgs a, const Fr::T* __re
             acc = Fr::add(acc, w);
         }
     }
-    uint4* d = reinterpret_cast<uint4*>(a.out[m] + i);
+    uint4* d = reinterpret_cast<uint4*>(a.out[m] + q);
     const uint4* s = reinterpret_cast<const uint4*>(&acc);
     d[0] = s[0]; d[1] = s[1];
 }
 
-void r1cs_eval(const R1csDev& r, const Fr::T* W_d, Fr::T* a_d, Fr::T* b_d, Fr::T* c_d, uint64_t domain_n, cudaStream_t st) {
+void r1cs_eval(const R1csDev& r, const Fr::T* W_d, Fr::T* a_d, Fr::T* b_d, Fr::T* c_d, uint64_t domain_n, cudaStream_t st,
+               int rb, int g, uint32_t rank) {
+    domain_n >>= g;   // rows produced here
     if (!domain_n) return;
     R1csArgs a;
     Fr::T* outs[3] = {a_d, b_d, c_d};
@@ -52,7 +57,7 @@ void r1cs_eval(const R1csDev& r, const Fr::T* W_d, Fr::T* a_d, Fr::T* b_d, Fr::T
         a.out[m] = outs[m];
     }
     dim3 grid((unsigned)((domain_n + 255) / 256), 3);
-    k_r1cs_eval<<<grid, 256, 0, st>>>(a, r.coeffs.as<Fr::T>(), W_d, r.n_constraints, domain_n);
+    k_r1cs_eval<<<grid, 256, 0, st>>>(a, r.coeffs.as<Fr::T>(), W_d, r.n_constraints, domain_n, rb, g, rank);
     G16_LAUNCH_CHECK();
 }
 

@@ -19,6 +19,8 @@ struct R1csDev {
 };
 
 // out[m][i] = sum over the terms of row i of matrix m of coeffs[cid] * W[wire], i < n_constraints; rows up to domain_n zeroed
-void r1cs_eval(const R1csDev& r, const Fr::T* W_d, Fr::T* a_d, Fr::T* b_d, Fr::T* c_d, uint64_t domain_n, cudaStream_t st);
+// rb, g, rank != 0: produce only the domain_n >> g rows whose index bits [rb, rb+g) equal rank, packed (multi.cu)
+void r1cs_eval(const R1csDev& r, const Fr::T* W_d, Fr::T* a_d, Fr::T* b_d, Fr::T* c_d, uint64_t domain_n, cudaStream_t st,
+               int rb = 0, int g = 0, uint32_t rank = 0);
 
 }  // namespace g16

@@ -38,7 +38,7 @@ class Stats(ctypes.Structure):
         ("msm_c", ctypes.c_int32 * 5), ("msm_windows", ctypes.c_int32 * 5), ("msm_n", ctypes.c_uint64 * 5),
         ("h2d_bytes", ctypes.c_uint64), ("d2h_bytes", ctypes.c_uint64),
         ("kernel_launches", ctypes.c_uint32), ("reserved", ctypes.c_uint32),
-        ("ms_accumulate", ctypes.c_float * 5), ("reserved2", ctypes.c_float),
+        ("ms_accumulate", ctypes.c_float * 5), ("ms_wall", ctypes.c_float),
     ]
 
     def as_dict(self):
@@ -46,7 +46,7 @@ class Stats(ctypes.Structure):
                     ms_msm=list(self.ms_msm), ms_host=self.ms_host, msm_c=list(self.msm_c),
                     msm_windows=list(self.msm_windows), msm_n=list(self.msm_n), h2d_bytes=self.h2d_bytes,
                     d2h_bytes=self.d2h_bytes, kernel_launches=self.kernel_launches,
-                    ms_accumulate=list(self.ms_accumulate))
+                    ms_accumulate=list(self.ms_accumulate), ms_wall=self.ms_wall)
 
 
 class PkDesc(ctypes.Structure):
@@ -83,7 +83,7 @@ class R1csDesc(ctypes.Structure):
 # every symbol include/g16b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "g16_ctx_create", "g16_ctx_destroy", "g16_last_error", "g16_ctx_set", "g16_kernel_launch_count",
-    "g16_pk_upload", "g16_pk_upload_from_file", "g16_pk_free", "g16_pk_wire_range", "g16_prove_bn254", "g16_prove_bn254_dev", "g16_assemble_proof_bn254",
+    "g16_pk_upload", "g16_pk_upload_from_file", "g16_pk_free", "g16_pk_wire_range", "g16_pk_placement", "g16_prove_bn254", "g16_prove_bn254_dev", "g16_assemble_proof_bn254",
     "g16_r1cs_upload", "g16_r1cs_free", "g16_r1cs_eval_dev", "g16_prove_bn254_wires",
     "g16_bases_upload", "g16_bases_free", "g16_msm_resident_dev", "g16_msm_resident",
     "g16_commitment_key_upload", "g16_commitment_key_free", "g16_commit",
@@ -157,20 +157,24 @@ u64 = ctypes.c_uint64
 
 
 class Context:
-    """One GPU, one call in flight (g16_ctx)."""
+    """One GPU -- or a group of 2 / 4 / 8 -- and one call in flight (g16_ctx)."""
 
     def __init__(self, device=0, curve="bn254"):
+        """device: one ordinal, or a list of 2 / 4 / 8 ordinals = a multi-GPU group behind the same calls."""
         self._lib = load(curve)
         self.curve = curve
         curve_id, self.g1w, self.g2w = CURVES[curve]
         self.prove_out_words = 4 * self.g1w + self.g2w
         self._h = ctypes.c_void_p()
-        ids = (ctypes.c_int * 1)(device)
-        rc = self._lib.g16_ctx_create(ctypes.byref(self._h), curve_id, ids, 1)
+        devices = [int(device)] if isinstance(device, (int, np.integer)) else [int(d) for d in device]
+        ids = (ctypes.c_int * len(devices))(*devices)
+        rc = self._lib.g16_ctx_create(ctypes.byref(self._h), curve_id, ids, len(devices))
         if rc != 0:
             self._h = ctypes.c_void_p()
-            raise G16Error(f"g16_ctx_create failed with status {rc} (no usable CUDA device? there is no CPU fallback)")
-        self.device = device
+            raise G16Error(f"g16_ctx_create failed with status {rc} (no usable CUDA device, or devices that cannot map "
+                           "each other? there is no CPU fallback)")
+        self.device = devices[0]
+        self.devices = devices
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
@@ -301,6 +305,12 @@ class Context:
         lo, hi = u64(0), u64(0)
         self._check(self._lib.g16_pk_wire_range(self._h, u64(handle), ctypes.byref(lo), ctypes.byref(hi)), "g16_pk_wire_range")
         return lo.value, hi.value
+
+    def pk_placement(self, handle, rank=0):
+        """[(lo, hi)] x 5 in OUT_* order: the element ranges of G1.A, G1.B, G1.K, G1.Z, G2.B resident on `rank`."""
+        lo, hi = (u64 * 5)(), (u64 * 5)()
+        self._check(self._lib.g16_pk_placement(self._h, u64(handle), int(rank), lo, hi), "g16_pk_placement")
+        return [(int(lo[i]), int(hi[i])) for i in range(5)]
 
     def pk_free(self, handle):
         self._check(self._lib.g16_pk_free(self._h, u64(handle)), "g16_pk_free")

@@ -11,7 +11,8 @@
  *     (R = 2^256); G1Affine = X||Y (64 B); G2Affine = X.A0||X.A1||Y.A0||Y.A1 (128 B); infinity = all zero.
  *   - pointers are HOST pointers unless the function name ends in _dev, whose data pointers are DEVICE
  *     pointers on the context's GPU (results are still written to host memory).
- *   - a context is bound to one GPU and is thread-compatible: one call in flight per context.
+ *   - a context is bound to its GPU(s) and is thread-compatible: one call in flight per context (callers that prove
+ *     concurrently on one key serialise their calls or use one context per thread).
  *   - scalars equal to zero and bases equal to infinity are legal inputs everywhere; zero-length MSMs
  *     return infinity (the reference special-cases both on the host: icicle.go:98-105,330-333,343-347).
  */
@@ -50,13 +51,18 @@ typedef struct {
     uint32_t kernel_launches; /* kernels of this library launched by the call */
     uint32_t reserved;
     float ms_accumulate[5]; /* the bucket-accumulation kernel of each MSM (dominant kernel; roofline evidence) */
-    float reserved2;
+    float ms_wall;          /* multi-GPU contexts: host wall clock of the whole call (all ranks + the final sum) */
 } g16_stats;
 
 /* ---- context ------------------------------------------------------------------------------------- */
-/* device_ids/n_devices: this round binds one GPU per context (n_devices must be 1; one process per GPU,
- * shards are combined by the caller -- see INTEGRATION.md).  Replaces the implicit default-device state
- * of iciclegnark (icicle.go never passes a device id). */
+/* device_ids/n_devices: the GPUs this context drives, n_devices in {1, 2, 4, 8} (one context per process and GPU set;
+ * replaces the implicit default-device state of iciclegnark -- icicle.go never passes a device id).  With more than
+ * one device the context is a group: g16_pk_upload places slices of the key on every GPU (shard_count must be 0/1),
+ * g16_prove_bn254 / _dev / _wires run the distributed computeH (exchanges = peer stores over NVLink, no NCCL) and every
+ * GPU's share of the five MSMs inside the one call and return the COMBINED five points, exactly like a single-GPU
+ * context; _dev pointers live on device_ids[0]; every other entry point (primitives, commitments) runs on
+ * device_ids[0].  The devices must be peer-accessible.  The same ordinal may be listed more than once: the ranks then
+ * share that GPU (functional emulation for tests; no speed-up). */
 int g16_ctx_create(g16_ctx** out, int curve_id, const int* device_ids, int n_devices);
 void g16_ctx_destroy(g16_ctx* ctx);
 const char* g16_last_error(const g16_ctx* ctx);
@@ -108,6 +114,12 @@ int g16_pk_free(g16_ctx* ctx, uint64_t pk_handle);
  * whole vector for an unsharded key).  g16_prove_bn254 copies just that range; callers that keep W on the device
  * (g16_prove_bn254_dev, g16_prove_msms_dev) need to fill only that range. */
 int g16_pk_wire_range(g16_ctx* ctx, uint64_t pk_handle, uint64_t* lo, uint64_t* hi);
+
+/* Multi-GPU contexts: where the key lives.  lo[i], hi[i] (i = G16_OUT_*) receive the element range of G1.A, G1.B, G1.K,
+ * G1.Z, G2.B that the group's rank `rank` (0 .. n_devices-1) keeps resident; empty ranges have lo == hi.  On a
+ * single-GPU context rank must be 0 and the ranges are the context's shard (shard_index / shard_count).  Mirrors what
+ * setupDevicePointers would log about its uploads (icicle.go:31-130). */
+int g16_pk_placement(g16_ctx* ctx, uint64_t pk_handle, int rank, uint64_t lo[5], uint64_t hi[5]);
 
 /* ---- the proof hot path ---------------------------------------------------------------------------- */
 /* Replaces the device section of icicle_bn254.Prove (icicle.go:204-410): computeH + the five MSMs.
