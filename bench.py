@@ -1,16 +1,18 @@
 #!/usr/bin/env python
 """bench.py -- BN254 Groth16 prove @ 2^22 constraints on N B200s (BASELINE.json configs[3]).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--log-n 22] [--no-extras]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--log-n 22] [--no-extras] [--no-cpu]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-A step = one pass of the proving hot path (computeH + the five MSMs + window Horner on the host) over one
-synthetic R1CS solution.  `value` is timed with the inputs resident in HBM (g16_prove_bn254_dev); `e2e` goes
-through the plugin call with pinned HOST buffers (g16_prove_bn254: H2D of W,a,b,c inside the timed region, the
-five result points read back).  The proving key is a DummySetup-style synthetic key (distinct random bases
-[k_i]G made by the library's fixed-base kernel; the reference's own BenchmarkProver also uses a dummy key,
-backend/groth16/groth16_test.go:78) with the MiMC-chain shape |A| = |K| ~ n, |B| ~ 2n/3, |Z| = n-1.
-Only the cpu_baseline / --impl reference legs touch oracle/ (the CPU restatement of the reference prover).
+A step = one pass of the proving hot path (computeH + the five MSMs + window Horner on the host) over one solved
+instance of the MiMC-shaped chain R1CS (real witness, trapdoor setup; tests/helpers.py ChainCase).  `value` is timed with
+the inputs resident in HBM (g16_prove_bn254_dev); `e2e` goes through the plugin call with pinned HOST buffers
+(g16_prove_bn254: H2D of W, a, b, c inside the timed region, the five result points read back); `e2e_pageable` is the
+same call on plain pageable arrays (a Go caller's slices); `e2e_wires` ships only the wire vector.  N > 1: ONE process
+drives all N GPUs through one multi-GPU g16 context -- the reference surface is a single in-process call -- so under
+torchrun rank 0 makes the calls and the other ranks only keep the barriers and the max-over-ranks reduction.
+Before anything is timed, all five points of the instance are checked against the oracle (`parity` in the line).
+oracle/ is used only as that checker, for the instance's inputs, and in the cpu_baseline / --impl reference legs.
 """
 import argparse
 import json
@@ -98,50 +100,6 @@ def chain_shape(nc, power=5):
     return nw, inf_a, inf_b
 
 
-def chain_matrices(nc, power, coeffs):
-    """constraint matrices (CSR) with the MiMC-chain shape for the wires-only entry point: per
-    round t = x + k + c_i, then the squarings, then v * t; `coeffs` = [one, c_1, c_2, ...] (random constants)."""
-    per = 3 if power == 5 else 5
-    rounds = (nc - 1) // per
-    r = np.arange(rounds, dtype=np.int64)
-    base = 4 + per * r                                   # first new wire of round r
-    xw = np.where(r == 0, 2, base - 1)
-    t_w = np.stack([xw, np.full(rounds, 3), np.zeros(rounds, dtype=np.int64)], axis=1)
-    t_c = np.stack([np.zeros(rounds, dtype=np.int64), np.zeros(rounds, dtype=np.int64), 1 + r % (len(coeffs) - 1)], axis=1)
-    z1 = np.zeros((rounds, 1), dtype=np.int64)
-    col = lambda a: a.reshape(-1, 1)
-    sq = [(col(base + i), z1) for i in range(per - 1)]   # u, v (, v2, v3): squared by the next row, the last times t
-    Lr = [(t_w, t_c)] + sq
-    Rr = [(t_w, t_c)] + sq[:-1] + [(t_w, t_c)]
-    Or = [(col(base + i), z1) for i in range(per)]
-    nfill = nc - 1 - per * rounds
-    f = np.arange(nfill, dtype=np.int64)
-    last_state = int(base[-1] + per - 1) if rounds else 2
-    fx_in = np.where(f == 0, last_state, 3 + per * rounds + f)
-    fx_out = 4 + per * rounds + f
-    final_state = int(fx_out[-1]) if nfill else last_state
-
-    def matrix(per_round, fill_w, last_w):
-        lens = [p[0].shape[1] for p in per_round]
-        w = np.concatenate([p[0] for p in per_round], axis=1).reshape(-1)
-        c = np.concatenate([p[1] for p in per_round], axis=1).reshape(-1)
-        row_len = np.concatenate([np.tile(lens, rounds), np.ones(nfill, dtype=np.int64), [len(last_w)]])
-        rp = np.zeros(nc + 1, dtype=np.uint32)
-        rp[1:] = np.cumsum(row_len)
-        return (rp, np.concatenate([w, fill_w, last_w]).astype(np.uint32),
-                np.concatenate([c, np.zeros(nfill + len(last_w), dtype=np.int64)]).astype(np.uint32))
-
-    return matrix(Lr, fx_in, [final_state, 3]), matrix(Rr, fx_in, [0]), matrix(Or, fx_out, [1])
-
-
-def one_fr(curve):
-    """Montgomery image of 1 (R mod r) as 4 uint64 limbs."""
-    r = {"bn254": 21888242871839275222246405745257275088548364400416034343698204186575808495617,
-         "bls12_377": 8444461749428370424248824938781546531375899335154063827935233455917409239041}[curve]
-    v = (1 << 256) % r
-    return np.array([(v >> (64 * i)) & 0xFFFFFFFFFFFFFFFF for i in range(4)], dtype=np.uint64)
-
-
 def rand_fr_cuda(torch, n, gen, dev):
     x = torch.randint(-(2 ** 63), 2 ** 63 - 1, (n, 4), dtype=torch.int64, device=dev, generator=gen)
     x[:, 3] &= FR_TOP_MASK
@@ -185,212 +143,251 @@ def build_inputs(torch, ctx, nc, dev, seed=20260422):
     return key, sol_dev, sol_host, n, nw
 
 
-# ------------------------------------------------------------------------------------------------ CPU leg (oracle)
-def cpu_prove_sample(log_nc, steps=1, warmup=0):
-    """The reference's CPU prover algorithm (backend/groth16/bn254/prove.go:141-320) as restated in oracle/c,
-    timed on the host cores on a bounded sample: a full prove at 2^log_nc constraints.  Returns ms per prove."""
+# ------------------------------------------------------------------------------------------------ the BN254 instance
+BENCH_SEED = 22
+POINT_NAMES = ["ar", "bs1", "krs_k", "krs_hz", "bs2"]
+
+
+def chain_case(nc, g1_mul=None, g2_mul=None):
+    """BASELINE config 4: the MiMC-shaped chain at `nc` constraints with a trapdoor setup (tests/helpers.py ChainCase:
+    witness, a, b, c and the setup scalars A(t), B(t), K, Z from oracle/c; bases = [scalar]G from g1_mul / g2_mul --
+    the library's fixed-base kernel in the GPU arm, oracle/c's in the reference arm: same seed, identical key)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
-    from oracle import cpu as ocpu
     from helpers import ChainCase
-    nc = 1 << log_nc
-    case = ChainCase(nc, seed=11)
+    return ChainCase(nc, seed=BENCH_SEED, g1_mul=g1_mul, g2_mul=g2_mul)
+
+
+def workload_config(case, log_n):
+    pk = case.pk
+    return {"workload": f"groth16_bn254_prove_2p{log_n}_mimc_chain", "constraints": case.nc, "domain": case.n,
+            "wires": case.nw,
+            "msm_sizes": {"g1_a": int(len(pk.g1_a)), "g1_b": int(len(pk.g1_b)), "g1_k": int(len(pk.g1_k)),
+                          "g1_z": int(len(pk.g1_z)), "g2_b": int(len(pk.g2_b))},
+            "instance": f"MiMC-shaped pow5 chain (3 constraints per round), trapdoor setup, xoshiro seed {BENCH_SEED}",
+            "l2": "inputs larger than L2"}
+
+
+def cpu_prove(case, ocpu):
+    """the reference's CPU prover schedule (backend/groth16/bn254/prove.go:141-150,306-320) as restated in oracle/c:
+    computeH on all cores, then the five MultiExps; returns (ms, the five points, h)."""
     pk = case.pk
     wa, wb, wk = case.W[~case.inf_a], case.W[~case.inf_b], case.W[2:]
-    times = []
-    for it in range(warmup + steps):
-        t0 = time.perf_counter()
-        h = ocpu.compute_h(case.a, case.b, case.c, case.n)
-        ocpu.msm_g1(pk.g1_a, wa)
-        ocpu.msm_g1(pk.g1_b, wb)
-        ocpu.msm_g1(pk.g1_k, wk)
-        ocpu.msm_g1(pk.g1_z, h[: case.n - 1])
-        ocpu.msm_g2(pk.g2_b, wb)
-        if it >= warmup:
-            times.append((time.perf_counter() - t0) * 1e3)
-    return sum(times) / len(times), ocpu.threads()
+    t0 = time.perf_counter()
+    h = ocpu.compute_h(case.a, case.b, case.c, case.n)
+    pts = np.concatenate([ocpu.msm_g1(pk.g1_a, wa), ocpu.msm_g1(pk.g1_b, wb), ocpu.msm_g1(pk.g1_k, wk),
+                          ocpu.msm_g1(pk.g1_z, h[: case.n - 1]), ocpu.msm_g2(pk.g2_b, wb)])
+    return (time.perf_counter() - t0) * 1e3, pts, h
 
 
-def cpu_scale(log_s, log_t):
-    """bucket-method work ~ points x windows; the oracle picks c = log2(n) - 4 (<= 16) like gnark-crypto's size table."""
-    c = lambda l: min(16, max(4, l - 4))
-    return 2.0 ** (log_t - log_s) * (c(log_s) / c(log_t))
+def parity_report(got, want, method):
+    got, want = np.asarray(got, dtype=np.uint64).reshape(-1), np.asarray(want, dtype=np.uint64).reshape(-1)
+    bounds = [0, 8, 16, 24, 32, 48]
+    bad = [POINT_NAMES[i] for i in range(5) if not np.array_equal(got[bounds[i]:bounds[i + 1]], want[bounds[i]:bounds[i + 1]])]
+    return {"checked": POINT_NAMES, "bytes": int(got.size * 8), "mismatches": len(bad), "mismatched": bad, "method": method}
 
 
 def run_reference(args):
+    """--impl reference: the CPU prover (oracle/c restatement of backend/groth16/bn254/prove.go; gnark-crypto itself
+    needs Go, which neither machine has) on the SAME instance and config as the GPU arm, all host cores, every timed
+    step a full 2^log_n prove.  Touches no CUDA and does not load libg16b200.so."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    log_s = args.cpu_log_n
-    ms, cores = cpu_prove_sample(log_s, steps=max(1, args.steps), warmup=min(args.warmup, 1))
-    scale = cpu_scale(log_s, args.log_n)
-    v = ms * scale
-    sample = (f"CPU restatement (oracle/c, not gnark-crypto: no Go toolchain) of a full prove at 2^{log_s} constraints, "
-              f"x{scale:.1f} extrapolation to 2^{args.log_n} (points x windows)")
+    from oracle import cpu as ocpu
+    t_build = time.perf_counter()
+    case = chain_case(1 << args.log_n)          # key from oracle/c's batch fixed-base multiplication
+    t_build = time.perf_counter() - t_build
+    want = None
+    times, budget = [], args.cpu_budget_s
+    warm = min(args.warmup, 1)                  # one untimed prove warms the page cache / thread pool; a CPU needs no more
+    for it in range(warm + args.steps):
+        ms, pts, h = cpu_prove(case, ocpu)
+        if want is None:
+            want = case.expected_points(h)      # exponent side: [sum w_i s_i]G with the setup's trapdoor scalars
+        par = parity_report(pts, want, "trapdoor identity on the oracle prover's five points")
+        if par["mismatches"]:
+            raise SystemExit(f"bench.py --impl reference: CPU prover disagrees with the trapdoor identity: {par}")
+        if it >= warm:
+            times.append(ms)
+            if sum(times) / 1e3 > budget:       # bounded: stop once the timed region exceeds the budget
+                break
+    v = sum(times) / len(times)
+    cores = ocpu.threads()
+    sample = (f"oracle/c restatement of the gnark-crypto CPU prover (not gnark-crypto itself: no Go toolchain, no ADX/BMI2 "
+              f"assembly), {len(times)} full prove(s) at 2^{args.log_n} constraints on {cores} threads; key built by oracle/c in {t_build:.0f} s")
     line = {"impl": "reference", "metric": "groth16_bn254_prove_ms", "value": v, "unit": "ms", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": v, "higher_is_better": False, "scaling": "strong",
-            "vs_baseline": None, "dtype": "u32x8-montgomery", "data": "synthetic",
-            "config": {"workload": f"groth16_bn254_prove_2p{args.log_n}_mimc_chain", "constraints": 1 << args.log_n},
+            "steps": len(times), "steps_requested": args.steps, "steps_run": len(times), "warmup": warm, "warmup_requested": args.warmup,
+            "ms_per_step": v, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "u32x8-montgomery",
+            "data": "synthetic", "config": workload_config(case, args.log_n), "parity": par,
             "cpu_baseline": {"value": v, "unit": "ms", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
-def timed(torch, ext, fn, steps, warmup, world, dist):
-    """W warm-up calls, then K calls bracketed by barrier + synchronize and CUDA events on the library's stream."""
+class Ranks:
+    """torchrun plumbing.  The product drives all N GPUs from ONE process through one multi-GPU g16 context (the
+    reference surface is a single in-process call); under torchrun rank 0 does that while the other ranks keep the
+    contract's barriers and the max-over-ranks reduction company."""
+
+    def __init__(self, torch):
+        self.torch = torch
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+            self.dist = dist
+            dev = torch.device(f"cuda:{self.local}")
+            torch.cuda.set_device(dev)
+            # NCCL prints its version banner on stdout when the communicator comes up; rank 0 must print ONE JSON line
+            # there, so stdout points at stderr until then
+            sys.stdout.flush()
+            saved = os.dup(1)
+            os.dup2(2, 1)
+            try:
+                dist.init_process_group("nccl", device_id=dev)
+                warm = torch.zeros(1, device=dev)
+                dist.all_reduce(warm)
+                torch.cuda.synchronize(dev)
+                # host-side rendezvous: a rank that waits inside an NCCL collective keeps a spinning kernel on its GPU,
+                # which time-slices with the kernels rank 0's context runs there (measured: 2x slower steps)
+                self.host_group = dist.new_group(backend="gloo")
+            finally:
+                sys.stdout.flush()
+                os.dup2(saved, 1)
+                os.close(saved)
+
+    def barrier(self):
+        if self.dist:
+            self.dist.barrier(group=self.host_group)   # wait on the CPU until every rank is here ...
+            self.dist.barrier()                        # ... then the NCCL barrier returns at once
+
+    def max_ms(self, ms):
+        if not self.dist:
+            return ms
+        self.dist.barrier(group=self.host_group)
+        t = self.torch.tensor([ms], device=f"cuda:{self.local}")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def close(self):
+        if self.dist:
+            self.dist.destroy_process_group()
+
+
+def timed(torch, ranks, ext, fn, steps, warmup):
+    """W warm-up calls, then K calls bracketed by barrier + synchronize and CUDA events on the library's stream (the
+    calls are synchronous: the closing event is recorded after the last one has returned); max over ranks."""
     for _ in range(warmup):
         fn()
-    if world > 1:
-        dist.barrier()
+    ranks.barrier()
     torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(ext)
-    last = None
-    for _ in range(steps):
-        last = fn()
-    e1.record(ext)
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    ms = e0.elapsed_time(e1)
-    if world > 1:
-        t = torch.tensor([ms], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    return ms / steps, last
+    ms, last = 0.0, None
+    if fn is not None and ext is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(ext)
+        for _ in range(steps):
+            last = fn()
+        e1.record(ext)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+    ranks.barrier()
+    return ranks.max_ms(ms) / steps, last
+
+
+def idle_rank(torch, ranks, legs, steps):
+    for _ in range(legs):
+        ranks.barrier()
+        torch.cuda.synchronize()
+        ranks.barrier()
+        ranks.max_ms(0.0)
+    ranks.close()
 
 
 def run_ours(args):
     import torch
-    import torch.distributed as dist
     from gnark_icicle_b200 import lib
-    import gnark_icicle_b200 as g16
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the accelerated path has no CPU fallback")
-    dev = torch.device(f"cuda:{local}")
+    if args.curve != "bn254":
+        return run_ours_synthetic(args)
+    ranks = Ranks(torch)
+    world = ranks.world if ranks.world > 1 else max(args.gpus, 1)   # without torchrun: the same single process, N devices
+    LEGS = 4                                     # value, e2e (pinned), e2e (pageable), e2e (wires only)
+    if ranks.rank != 0:
+        return idle_rank(torch, ranks, LEGS, args.steps)
+    from oracle import cpu as ocpu               # the checker: expected points, and the cpu_baseline leg
+    dev = torch.device("cuda:0")
     torch.cuda.set_device(dev)
-    if world > 1:
-        # NCCL prints its version banner on stdout when the communicator comes up (NCCL_DEBUG=VERSION from the box's
-        # environment or nccl.conf); rank 0 must print ONE JSON line there, so stdout points at stderr until then
-        sys.stdout.flush()
-        saved = os.dup(1)
-        os.dup2(2, 1)
-        try:
-            dist.init_process_group("nccl", device_id=dev)
-            warm = torch.zeros(1, device=dev)
-            dist.all_reduce(warm)
-            torch.cuda.synchronize(dev)
-        finally:
-            sys.stdout.flush()
-            os.dup2(saved, 1)
-            os.close(saved)
-    ctx = lib.Context(local, curve=args.curve)
-    fp_eq = IMAD_EQ_PER_FP_MUL if args.curve == "bn254" else IMAD_EQ_PER_FP_MUL_12
+    devices = list(range(world))
+    ctx = lib.Context(devices if world > 1 else 0)
     ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
     nc = 1 << args.log_n
-    key, sd, sh, n, nw = build_inputs(torch, ctx, nc, dev)
-    handle = ctx.pk_upload(key["domain_n"], key["g1_a"], key["g1_b"], key["g1_k"], key["g1_z"], key["g2_b"],
-                           key["inf_a"], key["inf_b"], nw, shard_index=rank, shard_count=world)
-    sizes = {k: int(len(key[k])) for k in ("g1_a", "g1_b", "g1_k", "g1_z", "g2_b")}
-    del key
-    wa, wb, wc = (torch.empty_like(sd[k]) for k in ("a", "b", "c"))
-    gather = [torch.empty(ctx.prove_out_words, dtype=torch.int64, device=dev) for _ in range(world)] if world > 1 else None
+    case = chain_case(nc, g1_mul=ctx.g1_fixed_base_mul, g2_mul=ctx.g2_fixed_base_mul)
+    n, nw, pk = case.n, case.nw, case.pk
+    cfg = workload_config(case, args.log_n)
+    t_up = time.perf_counter()
+    handle = ctx.pk_upload(pk.domain_n, pk.g1_a, pk.g1_b, pk.g1_k, pk.g1_z, pk.g2_b, pk.infinity_a, pk.infinity_b, nw)
+    t_up = time.perf_counter() - t_up
+    placement = [ctx.pk_placement(handle, r) for r in range(world)]
 
-    def combine(pts):
-        if world == 1:
-            return pts
-        t = torch.from_numpy(pts.view(np.int64)).to(dev)
-        dist.all_gather(gather, t)                      # 384 B per rank over NCCL/NVLink
-        if rank != 0:
-            return pts
-        return g16.combine_shards([g.cpu().numpy().view(np.uint64) for g in gather], curve=args.curve)
+    # ---- parity first (SURVEY.md 8(c)): every one of the five points of THIS instance against the exponent-side
+    # expectation [sum_i w_i s_i]G, s = the setup's trapdoor scalars, h from the CPU oracle's computeH
+    h_cpu = ocpu.compute_h(case.a, case.b, case.c, n)
+    want = case.expected_points(h_cpu)
+    pinned = {k: torch.from_numpy(v.view(np.int64)).pin_memory() for k, v in (("W", case.W), ("a", case.a), ("b", case.b), ("c", case.c))}
+    hW, ha, hb, hc = (pinned[k].numpy().view(np.uint64) for k in ("W", "a", "b", "c"))
+    pts, _ = ctx.prove(handle, hW, ha, hb, hc)
+    parity = parity_report(pts, want, "trapdoor identity [sum w_i s_i]G on all five points of the benchmarked instance, h from the "
+                                      "CPU oracle's computeH; checked before timing" + (f", on the points combined over {world} GPUs" if world > 1 else ""))
+    if parity["mismatches"]:
+        raise SystemExit(f"bench.py: GPU prove disagrees with the oracle: {parity}")
 
-    hW, ha, hb, hc = (sh[k].numpy().view(np.uint64) for k in ("W", "a", "b", "c"))
-    if world == 1:
-        def step_dev():
-            with torch.cuda.stream(ext):                    # a,b,c are clobbered by the transform pipeline
-                wa.copy_(sd["a"], non_blocking=True)
-                wb.copy_(sd["b"], non_blocking=True)
-                wc.copy_(sd["c"], non_blocking=True)
-            pts, st = ctx.prove_dev(handle, sd["W"].data_ptr(), wa.data_ptr(), wb.data_ptr(), wc.data_ptr())
-            return combine(pts), st
+    # ---- device-resident inputs (value)
+    Wd = pinned["W"].to(dev)
+    abc_master = torch.zeros((3, n, 4), dtype=torch.int64, device=dev)
+    for i, k in enumerate(("a", "b", "c")):
+        abc_master[i, :nc] = pinned[k].to(dev)
+    abc_work = torch.empty_like(abc_master)
 
-        def step_e2e():
-            pts, st = ctx.prove(handle, hW, ha, hb, hc)     # pinned host buffers in, 5 points out
-            return combine(pts), st
-    else:
-        # four-step computeH across the ranks (gnark_icicle_b200/dist.py): every rank owns the cyclic part of a, b, c,
-        # ends with its block of h, and runs the five MSMs over its point-range shard of the key
-        from gnark_icicle_b200 import dist as gdist
-        n_local = n // world
-        abc_master = torch.stack([sd[k][rank::world] for k in ("a", "b", "c")]).contiguous()
-        abc_work = torch.empty_like(abc_master)
-        abc_pin = abc_master.cpu().pin_memory()
-        # G16_DIST_ASYNC=1: stream-ordered distributed computeH (no host waits between its steps).  Measured at N=2:
-        # 40.9 vs 40.5 ms host-synchronised -- the GPU is the bottleneck, not the host -- so the plain form is the default
-        dist_stream = ext if os.environ.get("G16_DIST_ASYNC") else None
-        W_stage = torch.zeros_like(sd["W"])
-        w_lo, w_hi = ctx.pk_wire_range(handle)           # the wires this rank's shard of the A, B, K bases reads
-        del wa, wb, wc
-
-        def msms(W_t):
-            torch.cuda.current_stream().synchronize()
-            # (g16_prove_msms_begin_dev could start the W MSMs here, under the distributed computeH; measured: 41.3 vs 40.4 ms
-            #  at N=2, 13.7 vs 13.8 at N=8 -- the GPUs are busy either way, and h arriving late leaves the H.Z MSM alone at the end)
-            h_blk = gdist.compute_h_distributed(ctx, abc_work, n, rank, world, stream=dist_stream)
-            pts, st = ctx.prove_msms_dev(handle, W_t.data_ptr(), h_blk.data_ptr())
-            return combine(pts), st
-
-        def step_dev():
+    def step_dev():
+        with torch.cuda.stream(ext):                    # a, b, c are clobbered by the transform pipeline
             abc_work.copy_(abc_master, non_blocking=True)
-            return msms(sd["W"])
+        return ctx.prove_dev(handle, Wd.data_ptr(), abc_work[0].data_ptr(), abc_work[1].data_ptr(), abc_work[2].data_ptr())
 
-        def step_e2e():
-            # this rank's 1/world of a, b, c and the wire range its key shard reads, from pinned host memory
-            abc_work.copy_(abc_pin, non_blocking=True)
-            W_stage[w_lo:w_hi].copy_(sh["W"][w_lo:w_hi], non_blocking=True)
-            pts, st = msms(W_stage)
-            st["h2d_bytes"] = (w_hi - w_lo) * W_stage.shape[1] * 8 + abc_pin.numel() * 8
-            return pts, st
+    def step_e2e():
+        return ctx.prove(handle, hW, ha, hb, hc)        # pinned host buffers in, 5 points out
 
-    if world > 1:
-        # one-time check of the multi-rank path: this rank's block of the distributed h == the same block of h computed
-        # by this GPU alone from the full a, b, c
-        abc_work.copy_(abc_master)
-        torch.cuda.synchronize()
-        h_blk = gdist.compute_h_distributed(ctx, abc_work, n, rank, world, stream=dist_stream)
-        torch.cuda.synchronize()
-        full = [sd[k].clone() for k in ("a", "b", "c")]
-        torch.cuda.synchronize()                     # the clones were made on torch's stream, computeH runs on the library's
-        ctx.compute_h_dev(full[0].data_ptr(), full[1].data_ptr(), full[2].data_ptr(), n)
-        torch.cuda.synchronize()
-        if not torch.equal(h_blk, full[0][rank * n_local:(rank + 1) * n_local]):
-            raise SystemExit(f"bench.py: rank {rank}: distributed computeH differs from the single-GPU h")
-        del full
+    pW, pa, pb, pc = case.W, case.a, case.b, case.c     # plain numpy = pageable memory: what a Go caller passes
+
+    def step_pageable():
+        return ctx.prove(handle, pW, pa, pb, pc)
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from helpers import chain_csr
+    from oracle.prng import SEED_BASE
+    cs = chain_csr(nc, SEED_BASE + 2000 + BENCH_SEED)
+    r1 = ctx.r1cs_upload(cs.nb_constraints, cs.nb_wires, cs.coefficients, (cs.L, cs.R, cs.O))
+
+    def step_wires():
+        return ctx.prove_wires(handle, r1, hW)          # SURVEY.md 8(f) N1: only the wire vector crosses PCIe
+
     l0 = lib.kernel_launch_count(args.curve)
-    with ClockSampler(local) as clk:
-        ms_dev, (pts_dev, st) = timed(torch, ext, step_dev, args.steps, args.warmup, world, dist)
+    with ClockSampler(0) as clk:
+        ms_dev, (pts_dev, st) = timed(torch, ranks, ext, step_dev, args.steps, args.warmup)
     launches = (lib.kernel_launch_count(args.curve) - l0) * args.steps // (args.steps + args.warmup)
-    ms_e2e, (pts_e2e, st_e) = timed(torch, ext, step_e2e, args.steps, args.warmup, world, dist)
-    if rank == 0 and not np.array_equal(pts_dev, pts_e2e):
-        raise SystemExit("bench.py: device-resident and host-buffer proofs differ")
-    e2e_wires = None
-    if world == 1:
-        # SURVEY.md 8(f) N1: constraint matrices resident, only the wire vector crosses PCIe
-        gen = torch.Generator(device=dev)
-        gen.manual_seed(99)
-        coeffs = np.concatenate([ctx.fr_mul_vec(np.zeros((0, 4), dtype=np.uint64), np.zeros((0, 4), dtype=np.uint64)),
-                                 rand_fr_cuda(torch, 1025, gen, dev).cpu().numpy().view(np.uint64)])
-        coeffs[0] = one_fr(args.curve)
-        r1 = ctx.r1cs_upload(nc, nw, coeffs, chain_matrices(nc, 5 if args.curve == "bn254" else 17, coeffs))
-        ms_w, (_, st_w) = timed(torch, ext, lambda: ctx.prove_wires(handle, r1, hW), args.steps, args.warmup, world, dist)
-        e2e_wires = {"value": ms_w, "unit": "ms", "h2d_bytes_per_step": int(st_w["h2d_bytes"]), "d2h_bytes_per_step": int(st_w["d2h_bytes"]),
-                     "note": "g16_prove_bn254_wires: a, b, c evaluated on the device from resident constraint matrices (8(f) N1)"}
-        ctx.r1cs_free(r1)
+    ms_e2e, (pts_e2e, st_e) = timed(torch, ranks, ext, step_e2e, args.steps, args.warmup)
+    ms_pg, (pts_pg, st_pg) = timed(torch, ranks, ext, step_pageable, args.steps, args.warmup)
+    ms_w, (pts_w, st_w) = timed(torch, ranks, ext, step_wires, args.steps, args.warmup)
+    for name, p in (("device-resident", pts_dev), ("pinned e2e", pts_e2e), ("pageable e2e", pts_pg), ("wires-only e2e", pts_w)):
+        if not np.array_equal(p, want):
+            raise SystemExit(f"bench.py: {name} prove differs from the oracle's expectation")
+    parity["legs_checked"] = ["value", "e2e", "e2e_pageable", "e2e_wires"]
+    ctx.r1cs_free(r1)
+    ranks.close()
 
     # per-kernel durations for the roofline: one extra step with the MSMs serialised (with overlap on, kernels of
     # different MSMs share the SMs and their individual event times are not meaningful)
@@ -398,76 +395,143 @@ def run_ours(args):
     step_dev()
     _, st = step_dev()
     ctx.set("streams", 5)
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
     imad, wide = ctx.imad_peak()
     wide_x, fr_mul, fp_mul = ctx.pipe_rates()
-    # dominant kernel: k_accumulate<G1> (4 launches per step); algorithmic IMAD-equivalents per launch =
-    # entries (points x windows) x 10 Fp multiplications per XYZZ mixed add x 272
+    fp_eq = IMAD_EQ_PER_FP_MUL
+    # dominant kernel: k_accumulate<G1> (4 launches per step and GPU); algorithmic IMAD-equivalents per launch =
+    # entries (points x windows) x 10 Fp multiplications per XYZZ mixed add x 272.  On a group the
+    # per-MSM time is the slowest rank's and the work is the whole job's: the fraction is of the N-GPU aggregate peak.
+    per_rank_entries = []
+    for r in range(world):
+        per_rank_entries.append([(hi - lo) for lo, hi in placement[r]])
+    g1_ops = sum(st["msm_n"][i] * st["msm_windows"][i] for i in range(4)) * MADD_MULS["g1"] * fp_eq
+    g1_ms = sum(st["ms_accumulate"][:4])
+    g2_ops = st["msm_n"][4] * st["msm_windows"][4] * MADD_MULS["g2"] * fp_eq
+    g2_ms = st["ms_accumulate"][4]
+    peak = imad * world
+    ach = g1_ops / (g1_ms * 1e-3) / 1e12
+    roof = {"bound": "int32-imad", "kernel": "k_accumulate<G1> (4 launches/step)", "achieved": ach, "peak": peak / 1e12,
+            "unit": "TIMAD/s", "frac": ach / (peak / 1e12), "traffic": None,
+            "peak_source": "g16_imad_peak microbenchmark, same run (independent mad.lo.u32 chains on all SMs)" + (f" x {world} GPUs" if world > 1 else ""),
+            "imad_wide_peak_tops": wide / 1e12, "imad_wide_carry_peak_tops": wide_x / 1e12,
+            "field_mul_peak_g_per_s": fp_mul / 1e9, "field_mul_achieved_g_per_s": g1_ops / fp_eq / (g1_ms * 1e-3) / 1e9 / world,
+            "frac_of_multiplier_ceiling": g1_ops / fp_eq / (g1_ms * 1e-3) / fp_mul / world,
+            "g2": {"kernel": "k_accumulate<G2>", "achieved": g2_ops / (g2_ms * 1e-3) / 1e12,
+                   "frac": g2_ops / (g2_ms * 1e-3) / peak},
+            "share_of_step": (g1_ms + g2_ms) / st["ms_total"],
+            "note": "kernel times from one extra step with the five MSMs serialised (streams=1); the timed steps overlap them"
+                    + ("; on a group: slowest rank's time per MSM against the whole job's work" if world > 1 else "")}
+    pk_, src = peaks()
+    # HBM view of the same kernel: 64 B affine point + 4 B sorted index per bucket entry (DESIGN.md 5); `traffic` is
+    # dram__bytes_read+write per launch of the 2^22-point launch from the ncu --set full capture in profiles/
+    g1_bytes = sum(st["msm_n"][i] * st["msm_windows"][i] for i in range(4)) * (8 * ctx.g1w + 4)
+    roof["hbm"] = {"bound": "hbm", "achieved": g1_bytes / (g1_ms * 1e-3) / 1e9, "peak": pk_["hbm_gbs"] * world, "unit": "GB/s",
+                   "frac": g1_bytes / (g1_ms * 1e-3) / 1e9 / (pk_["hbm_gbs"] * world), "peak_source": src,
+                   "algorithmic_bytes_per_launch_2p22": (1 << 22) * 13 * 68,
+                   "note": "the accumulate kernel is bound by the integer multiplier, not HBM: it moves <10 % of the copy bandwidth"}
+    if args.log_n == 22 and world == 1:
+        roof["traffic"] = 4.10e9
+        roof["traffic_source"] = ("profiles/r01d_accumulate_ntt_2p22_ncu_raw.csv: 3.97 GB read + 0.13 GB written per 2^22-point launch "
+                                  "(8.6 ms, 54.5 M entries x 68 B = 3.71 GB algorithmic); before the 64-byte L2 fill hint: 7.45 GB")
+    ntt_bytes = 7 * 64 * n
+    if st["ms_compute_h"] > 0:
+        roof["compute_h"] = {"bound": "hbm", "achieved": ntt_bytes / (st["ms_compute_h"] * 1e-3) / 1e9, "peak": pk_["hbm_gbs"] * world,
+                             "unit": "GB/s", "frac": ntt_bytes / (st["ms_compute_h"] * 1e-3) / 1e9 / (pk_["hbm_gbs"] * world),
+                             "peak_source": src, "ms": st["ms_compute_h"],
+                             "note": "7 transforms x 64n B algorithmic; the butterflies are IMAD-bound at 254 bits"
+                                     + ("; distributed: slowest rank, exchanges and their waits included" if world > 1 else "")}
+    par = "1 GPU" if world == 1 else (f"{world} GPUs behind one g16 context: key placed on a cost line (G2 point = 3.4 G1 points), computeH split at one "
+                                      "stage with 3 peer-store exchanges over NVLink, partial points summed on the host")
+    line = {"metric": "groth16_bn254_prove_ms", "value": ms_dev, "unit": "ms", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_dev, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
+            "dtype": "u32x8-montgomery", "data": "synthetic", "config": cfg, "parallelism": par, "parity": parity,
+            "e2e": {"value": ms_e2e, "unit": "ms", "h2d_bytes_per_step": int(st_e["h2d_bytes"]),
+                    "d2h_bytes_per_step": int(st_e["d2h_bytes"]), "host_memory": "pinned"},
+            "e2e_pageable": {"value": ms_pg, "unit": "ms", "h2d_bytes_per_step": int(st_pg["h2d_bytes"]), "d2h_bytes_per_step": int(st_pg["d2h_bytes"]),
+                             "note": "same call with plain (pageable) numpy arrays: what a Go caller's heap slices are"},
+            "e2e_wires": {"value": ms_w, "unit": "ms", "h2d_bytes_per_step": int(st_w["h2d_bytes"]), "d2h_bytes_per_step": int(st_w["d2h_bytes"]),
+                          "note": "g16_prove_bn254_wires: a, b, c evaluated on the device from resident constraint matrices (8(f) N1)"},
+            "gpu_launches": int(launches), "clocks": clk.summary(), "roofline": roof, "key_upload_s": t_up,
+            "placement": {f"gpu{r}": {POINT_NAMES[i]: list(placement[r][i]) for i in range(5) if placement[r][i][1] > placement[r][i][0]} for r in range(world)},
+            "stages_ms": {"serialised_total": st["ms_total"], "compute_h": st["ms_compute_h"], "msm": st["ms_msm"], "accumulate": st["ms_accumulate"],
+                          "host_epilogue": st["ms_host"], "msm_c": st["msm_c"], "e2e_h2d": st_e["ms_h2d"]}}
+    if world == 1 and not args.no_extras:
+        line["extras"] = extras(torch, ctx, ext, dev, pk_, imad, full=args.sweep)
+    if world == 1 and not args.no_cpu:
+        # cpu_baseline: the oracle prover on the SAME instance, once, all host cores (~10-30 s); its five points double as a
+        # second, Pippenger-side parity check of the GPU's
+        ctx.pk_free(handle)
+        ms_cpu, pts_cpu, _ = cpu_prove(case, ocpu)
+        if not np.array_equal(pts_cpu, pts_dev):
+            raise SystemExit("bench.py: the CPU oracle prover and the GPU disagree on the benchmarked instance")
+        line["parity"]["cpu_prover_points_equal"] = True
+        line["cpu_baseline"] = {"value": ms_cpu, "unit": "ms", "cores": ocpu.threads(), "kind": "port",
+                                "sample": f"one full prove of the same 2^{args.log_n}-constraint instance by the oracle/c restatement of the "
+                                          "gnark-crypto CPU prover (not gnark-crypto itself), all host threads"}
+    print(json.dumps(line))
+
+
+def run_ours_synthetic(args):
+    """BLS12-377 (BASELINE config 5): synthetic key and solution made on the device (the C oracle is BN254-only, so this
+    curve has no CPU leg; its parity evidence is tests/test_gpu_bls12_377.py against the Python oracle)."""
+    import torch
+    from gnark_icicle_b200 import lib
+    dev = torch.device("cuda:0")
+    torch.cuda.set_device(dev)
+    ranks = Ranks.__new__(Ranks)
+    ranks.torch, ranks.rank, ranks.world, ranks.local, ranks.dist = torch, 0, 1, 0, None
+    ctx = lib.Context(0, curve=args.curve)
+    fp_eq = IMAD_EQ_PER_FP_MUL_12
+    ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
+    nc = 1 << args.log_n
+    key, sd, sh, n, nw = build_inputs(torch, ctx, nc, dev)
+    handle = ctx.pk_upload(key["domain_n"], key["g1_a"], key["g1_b"], key["g1_k"], key["g1_z"], key["g2_b"], key["inf_a"], key["inf_b"], nw)
+    sizes = {k: int(len(key[k])) for k in ("g1_a", "g1_b", "g1_k", "g1_z", "g2_b")}
+    del key
+    wa, wb, wc = (torch.empty_like(sd[k]) for k in ("a", "b", "c"))
+    hW, ha, hb, hc = (sh[k].numpy().view(np.uint64) for k in ("W", "a", "b", "c"))
+
+    def step_dev():
+        with torch.cuda.stream(ext):
+            wa.copy_(sd["a"], non_blocking=True)
+            wb.copy_(sd["b"], non_blocking=True)
+            wc.copy_(sd["c"], non_blocking=True)
+        return ctx.prove_dev(handle, sd["W"].data_ptr(), wa.data_ptr(), wb.data_ptr(), wc.data_ptr())
+
+    l0 = lib.kernel_launch_count(args.curve)
+    with ClockSampler(0) as clk:
+        ms_dev, (pts_dev, st) = timed(torch, ranks, ext, step_dev, args.steps, args.warmup)
+    launches = (lib.kernel_launch_count(args.curve) - l0) * args.steps // (args.steps + args.warmup)
+    ms_e2e, (pts_e2e, st_e) = timed(torch, ranks, ext, lambda: ctx.prove(handle, hW, ha, hb, hc), args.steps, args.warmup)
+    if not np.array_equal(pts_dev, pts_e2e):
+        raise SystemExit("bench.py: device-resident and host-buffer proofs differ")
+    ctx.set("streams", 1)
+    step_dev()
+    _, st = step_dev()
+    ctx.set("streams", 5)
+    imad, wide = ctx.imad_peak()
+    wide_x, fr_mul, fp_mul = ctx.pipe_rates()
     g1_ops = sum(st["msm_n"][i] * st["msm_windows"][i] for i in range(4)) * MADD_MULS["g1"] * fp_eq
     g1_ms = sum(st["ms_accumulate"][:4])
     g2_ops = st["msm_n"][4] * st["msm_windows"][4] * MADD_MULS["g2"] * fp_eq
     g2_ms = st["ms_accumulate"][4]
     ach = g1_ops / (g1_ms * 1e-3) / 1e12
-    roof = {"bound": "int32-imad", "kernel": "k_accumulate<G1> (4 launches/step)", "achieved": ach, "peak": imad / 1e12,
-            "unit": "TIMAD/s", "frac": ach / (imad / 1e12), "traffic": None,
-            "peak_source": "g16_imad_peak microbenchmark, same run (independent mad.lo.u32 chains on all SMs)",
-            "imad_wide_peak_tops": wide / 1e12, "imad_wide_carry_peak_tops": wide_x / 1e12,
-            "field_mul_peak_g_per_s": fp_mul / 1e9, "field_mul_achieved_g_per_s": g1_ops / fp_eq / (g1_ms * 1e-3) / 1e9,
+    roof = {"bound": "int32-imad", "kernel": "k_accumulate<G1> (4 launches/step)", "achieved": ach, "peak": imad / 1e12, "unit": "TIMAD/s",
+            "frac": ach / (imad / 1e12), "traffic": None, "field_mul_peak_g_per_s": fp_mul / 1e9,
             "frac_of_multiplier_ceiling": g1_ops / fp_eq / (g1_ms * 1e-3) / fp_mul,
-            "g2": {"kernel": "k_accumulate<G2>", "achieved": g2_ops / (g2_ms * 1e-3) / 1e12,
-                   "frac": g2_ops / (g2_ms * 1e-3) / imad},
-            "share_of_step": (g1_ms + g2_ms) / st["ms_total"],
-            "note": "kernel times from one extra step with the five MSMs serialised (streams=1); the timed steps overlap them"}
-    pk_, src = peaks()
-    # HBM view of the same kernel: 64 B affine point + 4 B sorted index per bucket entry (DESIGN.md 5); `traffic` is
-    # dram__bytes_read+write per launch of the 2^22-point launch from the ncu --set full capture in profiles/
-    g1_bytes = sum(st["msm_n"][i] * st["msm_windows"][i] for i in range(4)) * (8 * ctx.g1w + 4)
-    roof["hbm"] = {"bound": "hbm", "achieved": g1_bytes / (g1_ms * 1e-3) / 1e9, "peak": pk_["hbm_gbs"], "unit": "GB/s",
-                   "frac": g1_bytes / (g1_ms * 1e-3) / 1e9 / pk_["hbm_gbs"], "peak_source": src,
-                   "algorithmic_bytes_per_launch_2p22": (1 << 22) * 13 * 68,
-                   "note": "the accumulate kernel is bound by the integer multiplier, not HBM: it moves <10 % of the copy bandwidth"}
-    if args.log_n == 22 and args.curve == "bn254":
-        roof["traffic"] = 4.10e9
-        roof["traffic_source"] = ("profiles/r01d_accumulate_ntt_2p22_ncu_raw.csv: 3.97 GB read + 0.13 GB written per 2^22-point launch "
-                                  "(8.6 ms, 54.5 M entries x 68 B = 3.71 GB algorithmic); before the 64-byte L2 fill hint: 7.45 GB")
-    ntt_bytes = 7 * 64 * n
-    if world == 1 and st["ms_compute_h"] > 0:
-      roof["compute_h"] = {"bound": "hbm", "achieved": ntt_bytes / (st["ms_compute_h"] * 1e-3) / 1e9, "peak": pk_["hbm_gbs"],
-                         "unit": "GB/s", "frac": ntt_bytes / (st["ms_compute_h"] * 1e-3) / 1e9 / pk_["hbm_gbs"],
-                         "peak_source": src, "note": "7 transforms x 64n B algorithmic; the butterflies are IMAD-bound at 254 bits"}
-    else:
-      roof["compute_h"] = {"note": "distributed four-step computeH: timed inside the step, not per kernel"}
-    cname, shape = args.curve, ("mimc_chain" if args.curve == "bn254" else "mimc17_chain")
-    line = {"metric": f"groth16_{cname}_prove_ms", "value": ms_dev, "unit": "ms", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_dev, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
-            "dtype": "u32x8-montgomery" if cname == "bn254" else "u32x12-montgomery", "data": "synthetic",
-            "config": {"workload": f"groth16_{cname}_prove_2p{args.log_n}_{shape}", "constraints": nc, "domain": n,
-                       "msm_sizes": sizes, "parallelism": f"MSM point-range shards x{world}" + (", four-step computeH (NCCL all-to-all)" if world > 1 else ""), "l2": "inputs larger than L2",
-                       "key": "synthetic distinct bases (fixed-base kernel), MiMC-chain infinity shape"},
-            "e2e": {"value": ms_e2e, "unit": "ms", "h2d_bytes_per_step": int(st_e["h2d_bytes"]),
-                    "d2h_bytes_per_step": int(st_e["d2h_bytes"])},
-            "e2e_wires": e2e_wires, "gpu_launches": int(launches), "clocks": clk.summary(), "roofline": roof,
-            "stages_ms": {"serialised_total": st["ms_total"], "compute_h": st["ms_compute_h"], "msm": st["ms_msm"], "accumulate": st["ms_accumulate"],
-                          "host_epilogue": st["ms_host"], "msm_c": st["msm_c"], "e2e_h2d": st_e["ms_h2d"]}}
-    if world == 1 and args.curve != "bn254":
-        line["cpu_baseline"] = None
-        line["cpu_baseline_note"] = ("the C restatement of the CPU prover (oracle/c) exists for BN254 only; the BLS12-377 "
-                                     "oracle is Python big-int code and is a checker, not a timing baseline")
-        if not args.no_extras:
-            line["extras"] = extras(torch, ctx, ext, dev, pk_, imad, full=args.sweep)
-    elif world == 1 and not args.no_extras:
-        line["extras"] = extras(torch, ctx, ext, dev, pk_, imad, full=args.sweep)
-        ms_cpu, cores = cpu_prove_sample(args.cpu_log_n)
-        scale = cpu_scale(args.cpu_log_n, args.log_n)
-        line["cpu_baseline"] = {"value": ms_cpu * scale, "unit": "ms", "cores": cores, "kind": "port",
-                                "sample": f"oracle/c CPU restatement of the reference prover (not gnark-crypto), full prove at "
-                                          f"2^{args.cpu_log_n} constraints = {ms_cpu:.0f} ms, x{scale:.1f} extrapolation (points x windows)"}
+            "g2": {"kernel": "k_accumulate<G2>", "achieved": g2_ops / (g2_ms * 1e-3) / 1e12, "frac": g2_ops / (g2_ms * 1e-3) / imad},
+            "share_of_step": (g1_ms + g2_ms) / st["ms_total"]}
+    line = {"metric": f"groth16_{args.curve}_prove_ms", "value": ms_dev, "unit": "ms", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_dev, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "u32x12-montgomery",
+            "data": "synthetic", "config": {"workload": f"groth16_{args.curve}_prove_2p{args.log_n}_mimc17_chain", "constraints": nc, "domain": n,
+                                            "msm_sizes": sizes, "l2": "inputs larger than L2",
+                                            "key": "synthetic distinct bases (fixed-base kernel), MiMC pow17 chain infinity shape"},
+            "e2e": {"value": ms_e2e, "unit": "ms", "h2d_bytes_per_step": int(st_e["h2d_bytes"]), "d2h_bytes_per_step": int(st_e["d2h_bytes"])},
+            "gpu_launches": int(launches), "clocks": clk.summary(), "roofline": roof, "cpu_baseline": None,
+            "cpu_baseline_note": "the C restatement of the CPU prover (oracle/c) exists for BN254 only",
+            "stages_ms": {"serialised_total": st["ms_total"], "compute_h": st["ms_compute_h"], "msm": st["ms_msm"],
+                          "accumulate": st["ms_accumulate"], "msm_c": st["msm_c"]}}
     print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
 
 
 def extras(torch, ctx, ext, dev, pk_, imad, full=False):
@@ -542,18 +606,13 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--log-n", type=int, default=22, help="log2 of the constraint count (BASELINE: 22)")
-    ap.add_argument("--cpu-log-n", type=int, default=18, help="log2 constraints of the bounded CPU sample")
+    ap.add_argument("--cpu-budget-s", type=float, default=150.0, help="--impl reference: stop timing further proves once the timed region exceeds this")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg of the GPU arm")
     ap.add_argument("--curve", default="bn254", choices=["bn254", "bls12_377"],
                     help="bls12_377 = BASELINE config 5 (use --log-n 24); the default line is the BN254 headline")
     ap.add_argument("--no-extras", action="store_true")
     ap.add_argument("--sweep", action="store_true", help="extras = the full 2^16..2^26 MSM and NTT sweeps (configs 2, 3)")
     args = ap.parse_args()
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    if args.impl == "ours" and args.gpus > 1 and world == 1:
-        # convenience: re-launch under torchrun, one rank per GPU
-        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
-               "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.abspath(__file__)] + sys.argv[1:]
-        raise SystemExit(subprocess.call(cmd))
     if args.impl == "reference":
         run_reference(args)
     else:

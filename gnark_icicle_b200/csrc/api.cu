@@ -357,7 +357,7 @@ namespace g16 {
 // phase 0: the whole device section.  phase 1: enqueue the four MSMs over W and return (they run while the caller
 // produces h, e.g. the distributed computeH with its exchanges); phase 2: enqueue the H.Z MSM, wait for all five, finish.
 void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* b_d, Fr::T* c_d, void* out_points,
-                  g16_stats* stats, uint64_t launches0, cudaEvent_t w_ready, bool h_given, int phase, ProvePartial* partial) {
+                  g16_stats* stats, uint64_t launches0, cudaEvent_t w_ready, bool h_given, int phase, ProvePartial* partial, cudaEvent_t acc_gate) {
     cudaStream_t st = ctx->stream;
     NttDomain& dom = ctx->domain(pk.logn);
     cudaEvent_t* ev = ctx->ev;
@@ -387,21 +387,21 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
         G16_CUDA(cudaEventRecord(ev[6 + idx], s));
     };
     if (phase != 2) run(G16_OUT_BS2, s2, [&](cudaStream_t s) {
-        msm_g2_enqueue(ctx->ws[G16_OUT_BS2], W_d, (pk.same_b ? pk.map_b : pk.map_b2).as<uint32_t>(), pk.g2_b.as<G2::Aff>(), pk.n_b2, ctx->msm_c, ctx->msm_waves, s, plan[4], &ms[4], overlap ? ctx->tails[4] : nullptr, pre(G16_OUT_BS2)); });
+        msm_g2_enqueue(ctx->ws[G16_OUT_BS2], W_d, (pk.same_b ? pk.map_b : pk.map_b2).as<uint32_t>(), pk.g2_b.as<G2::Aff>(), pk.n_b2, ctx->msm_c, ctx->msm_waves, s, plan[4], &ms[4], overlap ? ctx->tails[4] : nullptr, pre(G16_OUT_BS2), nullptr, acc_gate); });
     if (phase != 1) {
         G16_CUDA(cudaEventRecord(ev[12], st));
         if (!h_given) compute_h_device(dom, a_d, b_d, c_d, st);   // h (bit-reversed) in a_d; h_given: a_d is this shard's block of h
         G16_CUDA(cudaEventRecord(ev[13], st));
     }
     if (phase != 2) run(G16_OUT_AR, sA, [&](cudaStream_t s) {
-        msm_g1_enqueue(ctx->ws[G16_OUT_AR], W_d, pk.map_a.as<uint32_t>(), pk.g1_a.as<G1::Aff>(), pk.n_a, ctx->msm_c, ctx->msm_waves, s, plan[0], &ms[0], overlap ? ctx->tails[0] : nullptr, pre(G16_OUT_AR)); });
+        msm_g1_enqueue(ctx->ws[G16_OUT_AR], W_d, pk.map_a.as<uint32_t>(), pk.g1_a.as<G1::Aff>(), pk.n_a, ctx->msm_c, ctx->msm_waves, s, plan[0], &ms[0], overlap ? ctx->tails[0] : nullptr, pre(G16_OUT_AR), nullptr, acc_gate); });
     if (phase != 1) run(G16_OUT_KRS_HZ, st, [&](cudaStream_t s) {
         msm_g1_enqueue(ctx->ws[G16_OUT_KRS_HZ], a_d + (h_given ? 0 : pk.z_off), nullptr, pk.g1_z.as<G1::Aff>(), pk.n_z, ctx->msm_c, ctx->msm_waves, s, plan[3], &ms[3], overlap ? ctx->tails[3] : nullptr, pre(G16_OUT_KRS_HZ)); });
     if (phase != 2) run(G16_OUT_BS1, sB, [&](cudaStream_t s) {
         msm_g1_enqueue(ctx->ws[G16_OUT_BS1], W_d, pk.map_b.as<uint32_t>(), pk.g1_b.as<G1::Aff>(), pk.n_b, ctx->msm_c, ctx->msm_waves, s, plan[1], &ms[1], overlap ? ctx->tails[1] : nullptr, pre(G16_OUT_BS1),
-                       pk.same_b && pk.n_b == pk.n_b2 ? &ctx->ws[G16_OUT_BS2] : nullptr); });   // same scalars, same map: reuse the G2 MSM's sort
+                       pk.same_b && pk.n_b == pk.n_b2 ? &ctx->ws[G16_OUT_BS2] : nullptr, acc_gate); });   // same scalars, same map: reuse the G2 MSM's sort
     if (phase != 2) run(G16_OUT_KRS_K, sK, [&](cudaStream_t s) {
-        msm_g1_enqueue(ctx->ws[G16_OUT_KRS_K], W_d, pk.map_k.as<uint32_t>(), pk.g1_k.as<G1::Aff>(), pk.n_k, ctx->msm_c, ctx->msm_waves, s, plan[2], &ms[2], overlap ? ctx->tails[2] : nullptr, pre(G16_OUT_KRS_K)); });
+        msm_g1_enqueue(ctx->ws[G16_OUT_KRS_K], W_d, pk.map_k.as<uint32_t>(), pk.g1_k.as<G1::Aff>(), pk.n_k, ctx->msm_c, ctx->msm_waves, s, plan[2], &ms[2], overlap ? ctx->tails[2] : nullptr, pre(G16_OUT_KRS_K), nullptr, acc_gate); });
     if (phase == 1) {
         for (int i = 0; i < 5; i++) ctx->pend_plan[i] = plan[i];
         return;

@@ -134,11 +134,11 @@ PkRanges pk_shard_ranges(const g16_pk_desc* d);
 // The device section of a prove on one context.  phase 0: everything.  phase 1: enqueue the four MSMs over W and return
 // (they run while the caller produces h); phase 2: enqueue the H.Z MSM, wait for all five, finish.
 // partial: when non-null receives the five results as XYZZ (no inversion; multi.cu sums the ranks first) and out_points
-// is not written.
+// is not written.  acc_gate (phase 1): the bucket accumulations wait for this event, the sorts do not.
 struct ProvePartial { G1::Xyzz g1[4]; G2::Xyzz g2; };
 void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* b_d, Fr::T* c_d, void* out_points,
                   g16_stats* stats, uint64_t launches0, cudaEvent_t w_ready, bool h_given = false, int phase = 0,
-                  ProvePartial* partial = nullptr);
+                  ProvePartial* partial = nullptr, cudaEvent_t acc_gate = nullptr);
 
 // ---- multi.cu
 MultiGpu* multi_create(g16_ctx* rank0, const int* device_ids, int n_devices);

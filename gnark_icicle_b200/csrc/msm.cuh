@@ -706,7 +706,8 @@ struct MsmStats { int c = 0, W = 0; uint32_t acc_threads = 0; cudaEvent_t acc_be
 template <class C, int ACC_THREADS, int ACC_MINB, bool SMEM_ACC = false, int MODE = 0>
 void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const typename C::Aff* bases_d,
                  uint64_t n, int force_c, int waves, cudaStream_t st, MsmPlan& plan_out, MsmStats* stats,
-                 cudaStream_t tail = nullptr, int pre_c = 0, MsmWorkspace* sort_from = nullptr) {
+                 cudaStream_t tail = nullptr, int pre_c = 0, MsmWorkspace* sort_from = nullptr, cudaEvent_t acc_gate = nullptr) {
+    // acc_gate: the accumulation (long-lived CTAs that fill every SM) is not launched before this event; the sort is
     // pre_c != 0: bases_d is the table [255/pre_c + 1][n] of precomputed multiples (k_precompute)
     // sort_from: another MSM over the SAME scalars, map and n (bs1 / bs2 of a proof) whose sorted entries and bucket
     // offsets are reused when the plans agree -- its stream must already have the sort enqueued
@@ -822,6 +823,7 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
         ws.sort_n = n; ws.sort_c = pl.c; ws.sort_pre = pl.pre;
         G16_CUDA(cudaEventRecord(ws.sort_done, st));
     }
+    if (acc_gate) G16_CUDA(cudaStreamWaitEvent(st, acc_gate, 0));
     if (stats && stats->acc_begin) G16_CUDA(cudaEventRecord(stats->acc_begin, st));
     acc_kernel<<<(nthreads + ACC_THREADS - 1) / ACC_THREADS, ACC_THREADS, acc_smem, st>>>(
         bases_d, sorted, offsets, pl.NB, nthreads, buckets, ws.head.as<Xyzz>(), ws.tail.as<Xyzz>());

@@ -6,17 +6,17 @@
 namespace g16 {
 
 void msm_g1_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const G1::Aff* bases_d, uint64_t n,
-                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail, int pre_c, MsmWorkspace* sort_from) {
+                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail, int pre_c, MsmWorkspace* sort_from, cudaEvent_t acc_gate) {
 #if G16_CURVE == 377
     // 12-limb Fp: the accumulator alone is 48 registers; 128 threads x 3 CTAs (<= 168 registers), multiplications as calls
     // (inlined, 10 x 6.4 KB of SASS overflows the instruction cache: 26.6-27.5 vs 24.6 ms -- experiments/README.md)
-    msm_enqueue<G1, 128, 3>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+    msm_enqueue<G1, 128, 3>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from, acc_gate);
 #else
     // 256-thread CTAs, 2 per SM, the field multiplications of the group addition inlined and the loop not unrolled: the
     // body (one XYZZ mixed addition, ~32 KB of SASS) still fits the instruction cache, and the 16 + 8 register moves
     // per multiplication call disappear: 9.68 -> 8.61 ms per 2^22-point launch (63 G Fp-mul/s, 0.93 of the multiplier
     // ceiling).  The rejected launch shapes (call-based 256 x 2 and 128 x 4, inline 128 x 4) are listed in experiments/README.md.
-    msm_enqueue<G1, 256, 2, false, 1>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+    msm_enqueue<G1, 256, 2, false, 1>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from, acc_gate);
 #endif
 }
 void msm_g1_precompute(G1::Aff* table_d, uint64_t n, int c, cudaStream_t st) {

@@ -6,15 +6,15 @@
 namespace g16 {
 
 void msm_g2_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d, const G2::Aff* bases_d, uint64_t n,
-                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail, int pre_c, MsmWorkspace* sort_from) {
+                    int force_c, int waves, cudaStream_t st, MsmPlan& plan, MsmStats* stats, cudaStream_t tail, int pre_c, MsmWorkspace* sort_from, cudaEvent_t acc_gate) {
     // 128 threads x 2 CTAs per SM, base-field multiplications as register-ABI calls.  Measured (profiles/README.md,
     // experiments/README.md): more CTAs per SM do not help (3-4 CTAs/SM: +15..50 %); calling at the Fp2 level (three
     // multiplications inlined per call) needs 252 registers and is 10 % slower; parking the accumulator in shared
     // memory (SmemAcc) costs 15 % on BN254 but removes enough spills on the 12-limb BLS12-377 field to win 5 % there.
 #if G16_CURVE == 377
-    msm_enqueue<G2, 128, 2, true>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+    msm_enqueue<G2, 128, 2, true>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from, acc_gate);
 #else
-    msm_enqueue<G2, 128, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from);
+    msm_enqueue<G2, 128, 2>(ws, scalars_d, map_d, bases_d, n, force_c, waves, st, plan, stats, tail, pre_c, sort_from, acc_gate);
 #endif
 }
 void msm_g2_precompute(G2::Aff* table_d, uint64_t n, int c, cudaStream_t st) {

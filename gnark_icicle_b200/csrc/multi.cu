@@ -456,8 +456,6 @@ void rank_prove(const ProveJob& J, int r) {
         R.st.h2d_bytes += in.device ? 0 : w_bytes;
     }
     G16_CUDA(cudaEventRecord(c->ev[15], st));
-    // ---- the MSMs over W start now, on their own streams
-    prove_device(c, pk, W_ptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, c->ev[15], true, 1);
 
     // ---- a, b, c of this rank in D(rb)
     Fr::T* A = R.buf[0].as<Fr::T>();
@@ -511,6 +509,11 @@ void rank_prove(const ProveJob& J, int r) {
     ntt_dist_stages(dom, batch(B, 1), TW_COSET_INV, true, g, (uint32_t)r, false, X, hs);       //            lower stages
     G16_CUDA(cudaEventRecord(R.ev_x[3], hs));   // this rank's block of h (bit-reversed order) is final in buf[1]
     G16_CUDA(cudaEventRecord(c->ev[31], hs));
+    // ---- the MSMs over W, on their own streams.  Their sorts (short CTAs) run beside computeH; their accumulations --
+    // CTAs that own an SM for milliseconds, which a high-priority stream cannot displace -- are held back until this
+    // rank's share of computeH is through: the other GPUs wait for its exchanges (measured at N = 4: h arrived after
+    // 15 ms instead of < 3 when the accumulations were let loose first)
+    prove_device(c, pk, W_ptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, c->ev[15], true, 1, nullptr, R.ev_x[3]);
     if (!mg.bar.wait()) throw std::runtime_error("another rank failed");
 
     // ---- h under this rank's slice of G1.Z
