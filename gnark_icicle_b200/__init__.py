@@ -12,10 +12,10 @@ The directory ``gnark-icicle_b200`` at the repo root is a link to this package (
 """
 from . import lib, bsb22
 from .groth16 import (HasIcicle, Prove, ProvingKey, Proof, R1CSSolution, WithIcicleAcceleration, WithRandomness,
-                      WithDevice, NewProverConfig, prove_msms, assemble, combine_shards, ConstraintSystem,
+                      WithDevice, WithDevices, NewProverConfig, prove_msms, assemble, combine_shards, ConstraintSystem,
                       prove_msms_wires)
 from . import dump, marshal, witness
 
 __all__ = ["lib", "bsb22", "dump", "marshal", "witness", "HasIcicle", "Prove", "ProvingKey", "Proof", "R1CSSolution", "WithIcicleAcceleration",
-           "WithRandomness", "WithDevice", "NewProverConfig", "prove_msms", "assemble", "combine_shards",
+           "WithRandomness", "WithDevice", "WithDevices", "NewProverConfig", "prove_msms", "assemble", "combine_shards",
            "ConstraintSystem", "prove_msms_wires"]

@@ -118,6 +118,7 @@ void ctx_destroy_single(g16_ctx* ctx) {
     for (auto& w : ctx->ws) w.release();
     for (auto& s : ctx->stage) s.release();
     for (auto& s : ctx->file_stage) s.release();
+    ctx->stager.release();
     ctx->fb_table_g1.release(); ctx->fb_table_g2.release();
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
     for (auto& a : ctx->aux) if (a) cudaStreamDestroy(a);
@@ -149,6 +150,12 @@ int g16_ctx_create(g16_ctx** out, int curve_id, const int* device_ids, int n_dev
     return 0;
 }
 
+int g16_device_count(void) {
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return count;
+}
+
 void g16_ctx_destroy(g16_ctx* ctx) {
     if (!ctx) return;
     if (ctx->multi) { multi_destroy(ctx->multi); ctx->multi = nullptr; }
@@ -167,6 +174,7 @@ int g16_ctx_set(g16_ctx* ctx, const char* key, int64_t value) {
     else if (k == "msm_pre_c") ctx->msm_pre_c = (int)value;
     else if (k == "dist_sync") ctx->dist_sync = (int)value;
     else if (k == "g2_weight") ctx->g2_weight = (int)value;
+    else if (k == "stage_threads") ctx->stage_threads = (int)value;
     else { ctx->err = "unknown tunable " + k; return 1; }
     if (ctx->multi) multi_set(ctx->multi, key, value);
     return 0;
@@ -488,18 +496,21 @@ extern "C" int g16_prove_bn254(g16_ctx* ctx, uint64_t pk_handle, const void* W, 
         // W first: the four MSMs over W start on their own streams while a, b, c are still in flight
         // a sharded key reads only the wires [w_lo, w_hi) of W: nothing else crosses PCIe
         ctx->stage[3].reserve((size_t)n_wires * 32);
+        for (int i = 0; i < 3; i++) ctx->stage[i].reserve(nb);
         const size_t w_bytes = (size_t)(pk.w_hi - pk.w_lo) * 32;
-        if (w_bytes) G16_CUDA(cudaMemcpyAsync((char*)ctx->stage[3].p + (size_t)pk.w_lo * 32, (const char*)W + (size_t)pk.w_lo * 32, w_bytes, cudaMemcpyHostToDevice, st));
+        h2d_caller(ctx, (char*)ctx->stage[3].p + (size_t)pk.w_lo * 32, (const char*)W + (size_t)pk.w_lo * 32, w_bytes, st);
         G16_CUDA(cudaEventRecord(ctx->ev[15], st));
+        // pageable a, b, c are staged by this thread (h2d_caller blocks while it gathers): enqueue the W MSMs first
+        const bool split = cb >= ((size_t)1 << 20) && HostStager::pageable(a);
+        if (split) prove_device(ctx, pk, ctx->stage[3].as<Fr::T>(), nullptr, nullptr, nullptr, nullptr, nullptr, l0, ctx->ev[15], false, 1);
         const void* src[3] = {a, b, c};
         for (int i = 0; i < 3; i++) {      // pad to the domain size (icicle.go:463-467)
-            ctx->stage[i].reserve(nb);
-            G16_CUDA(cudaMemcpyAsync(ctx->stage[i].p, src[i], cb, cudaMemcpyHostToDevice, st));
+            h2d_caller(ctx, ctx->stage[i].p, src[i], cb, st);
             if (nb > cb) G16_CUDA(cudaMemsetAsync((char*)ctx->stage[i].p + cb, 0, nb - cb, st));
         }
         G16_CUDA(cudaEventRecord(ctx->ev[27], st));
         prove_device(ctx, pk, ctx->stage[3].as<Fr::T>(), ctx->stage[0].as<Fr::T>(), ctx->stage[1].as<Fr::T>(),
-                     ctx->stage[2].as<Fr::T>(), out_points, stats, l0, ctx->ev[15]);
+                     ctx->stage[2].as<Fr::T>(), out_points, stats, l0, ctx->ev[15], false, split ? 2 : 0);
         if (stats) {
             G16_CUDA(cudaEventElapsedTime(&stats->ms_h2d, ctx->ev[26], ctx->ev[27]));
             G16_CUDA(cudaEventElapsedTime(&stats->ms_total, ctx->ev[26], ctx->ev[14]));
@@ -740,7 +751,8 @@ extern "C" int g16_prove_bn254_wires(g16_ctx* ctx, uint64_t pk_handle, uint64_t 
         G16_CUDA(cudaEventRecord(ctx->ev[26], st));
         // the WHOLE wire vector is uploaded, also for a sharded key: the constraint matrices gather arbitrary wires
         // (a public wire may appear in O only, i.e. in none of this shard's A / B / K maps)
-        upload(ctx->stage[3], W, (size_t)n_wires * 32, st);
+        ctx->stage[3].reserve((size_t)n_wires * 32);
+        h2d_caller(ctx, ctx->stage[3].p, W, (size_t)n_wires * 32, st);
         G16_CUDA(cudaEventRecord(ctx->ev[15], st));
         G16_CUDA(cudaEventRecord(ctx->ev[27], st));
         for (int i = 0; i < 3; i++) ctx->stage[i].reserve(nb);

@@ -9,6 +9,7 @@
 #include "msm_api.cuh"
 #include "ntt.cuh"
 #include "r1cs.cuh"
+#include "team.h"
 
 #include <cstring>
 #include <memory>
@@ -42,6 +43,71 @@ struct PkDev {
 
 struct MultiGpu;   // multi.cu
 
+// Caller memory that is not page-locked (a Go caller's heap slices: runtime.Pinner pins against the garbage collector,
+// it does not page-lock) cannot be the source of an asynchronous DMA: cudaMemcpyAsync stages it through the driver's
+// own bounce buffer on the calling thread, measured ~10 GB/s.  The stager does that copy itself with several threads
+// into a ring of pinned buffers and issues the DMA of one chunk while the next is being gathered.
+struct HostStager {
+    static constexpr size_t CHUNK = (size_t)8 << 20;
+    static constexpr int NBUF = 4;
+    PinnedBuf buf[NBUF];
+    cudaEvent_t done[NBUF] = {};
+    bool used[NBUF] = {};
+    int next = 0;
+    Team team;
+    int threads = 0;            // 0 = not started
+
+    static bool pageable(const void* p) {
+        cudaPointerAttributes a;
+        if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return true; }
+        return a.type == cudaMemoryTypeUnregistered;
+    }
+    void start(int want_threads) {
+        if (threads) return;
+        threads = want_threads < 1 ? 1 : (want_threads > 16 ? 16 : want_threads);
+        for (int i = 0; i < NBUF; i++) { buf[i].reserve(CHUNK); G16_CUDA(cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming)); }
+        team.start(threads);
+    }
+    void release() {
+        if (threads) team.shutdown();
+        threads = 0;
+        for (int i = 0; i < NBUF; i++) { buf[i].release(); if (done[i]) cudaEventDestroy(done[i]); done[i] = nullptr; used[i] = false; }
+    }
+    // `rows` rows of row_bytes each, source pitch src_pitch (contiguous: rows = 1), packed densely at dst_d
+    void copy_rows(void* dst_d, const void* src_h, size_t row_bytes, size_t src_pitch, size_t rows, cudaStream_t st) {
+        if (!rows || !row_bytes) return;
+        const char* src = (const char*)src_h;
+        char* dst = (char*)dst_d;
+        if (rows == 1 || src_pitch == row_bytes) { src_pitch = row_bytes = row_bytes * rows; rows = 1; }
+        // pieces of at most CHUNK bytes: whole rows when they fit, else slices of one row
+        const size_t rows_per = row_bytes >= CHUNK ? 1 : CHUNK / row_bytes;
+        for (size_t r0 = 0; r0 < rows; r0 += rows_per) {
+            const size_t nr = rows - r0 < rows_per ? rows - r0 : rows_per;
+            for (size_t off = 0; off < row_bytes; off += CHUNK) {
+                const size_t len = row_bytes - off < CHUNK ? row_bytes - off : CHUNK;      // only < row_bytes when nr == 1
+                const size_t bytes = nr == 1 ? len : nr * row_bytes;
+                const int b = next++ % NBUF;
+                if (used[b]) G16_CUDA(cudaEventSynchronize(done[b]));
+                char* stage = buf[b].as<char>();
+                const int T = threads;
+                team.run([&](int t) {
+                    if (nr == 1) {
+                        const size_t lo = len * t / T, hi = len * (t + 1) / T;
+                        memcpy(stage + lo, src + r0 * src_pitch + off + lo, hi - lo);
+                    } else {
+                        for (size_t r = nr * t / T; r < nr * (t + 1) / T; r++) memcpy(stage + r * row_bytes, src + (r0 + r) * src_pitch, row_bytes);
+                    }
+                });
+                G16_CUDA(cudaMemcpyAsync(dst + r0 * row_bytes + off, stage, bytes, cudaMemcpyHostToDevice, st));
+                G16_CUDA(cudaEventRecord(done[b], st));
+                used[b] = true;
+                if (nr > 1) break;
+            }
+        }
+    }
+    void copy(void* dst_d, const void* src_h, size_t bytes, cudaStream_t st) { copy_rows(dst_d, src_h, bytes, bytes, 1, st); }
+};
+
 }  // namespace g16
 
 struct g16_ctx {
@@ -71,6 +137,8 @@ struct g16_ctx {
     int msm_precompute = 1;      // keep 2^(c j) multiples of every key base resident (one shared bucket set, larger windows)
     int msm_pre_c = 0;           // window bits of the tables built by the next uploads (0 = chosen from the array size)
     int g2_weight = 340;         // multi-GPU placement: cost of a G2 point in hundredths of a G1 point
+    int stage_threads = 0;       // copier threads for pageable caller memory (0 = from the core count)
+    g16::HostStager stager;
     g16::MultiGpu* multi = nullptr;   // non-null on a context created over several devices (this context is rank 0)
 
     g16::NttDomain& domain(int logn) {
@@ -104,6 +172,19 @@ inline void slice(uint64_t len, uint32_t idx, uint32_t cnt, uint64_t& lo, uint64
     if (cnt <= 1) { lo = 0; hi = len; return; }
     lo = len * idx / cnt;
     hi = len * (idx + 1) / cnt;
+}
+
+// host -> device copy of caller memory on `st`: asynchronous DMA when the source is page-locked, staged through the
+// context's pinned ring by its copier threads when it is pageable (returns when the last chunk has been handed to the DMA)
+inline void h2d_caller(g16_ctx* ctx, void* dst_d, const void* src_h, size_t bytes, cudaStream_t st, int ranks_sharing_host = 1) {
+    if (!bytes) return;
+    if (bytes < ((size_t)1 << 20) || !HostStager::pageable(src_h)) { G16_CUDA(cudaMemcpyAsync(dst_d, src_h, bytes, cudaMemcpyHostToDevice, st)); return; }
+    if (!ctx->stager.threads) {
+        int t = ctx->stage_threads;
+        if (t <= 0) { t = (int)std::thread::hardware_concurrency() / (2 * ranks_sharing_host); t = t < 2 ? 2 : (t > 8 ? 8 : t); }
+        ctx->stager.start(t);
+    }
+    ctx->stager.copy(dst_d, src_h, bytes, st);
 }
 
 inline void upload(DevBuf& dst, const void* src, size_t bytes, cudaStream_t st) {

@@ -17,9 +17,6 @@
 #include "ctx.cuh"
 
 #include <chrono>
-#include <condition_variable>
-#include <functional>
-#include <thread>
 
 extern "C" int g16_prove_bn254(g16_ctx*, uint64_t, const void*, uint64_t, const void*, const void*, const void*, uint64_t, void*, g16_stats*);
 extern "C" int g16_prove_bn254_dev(g16_ctx*, uint64_t, const void*, void*, void*, void*, void*, g16_stats*);
@@ -28,90 +25,6 @@ extern "C" int g16_prove_bn254_wires(g16_ctx*, uint64_t, uint64_t, const void*, 
 namespace g16 {
 
 namespace {
-
-// rendezvous of the rank threads; a failing rank releases everybody
-struct HostBarrier {
-    std::mutex m;
-    std::condition_variable cv;
-    int n = 1, waiting = 0;
-    uint64_t gen = 0;
-    bool failed = false;
-    void reset(int n_) { std::lock_guard<std::mutex> lk(m); n = n_; waiting = 0; failed = false; }
-    bool wait() {
-        std::unique_lock<std::mutex> lk(m);
-        if (failed) return false;
-        const uint64_t g = gen;
-        if (++waiting == n) { waiting = 0; gen++; cv.notify_all(); }
-        else cv.wait(lk, [&] { return gen != g || failed; });
-        return !failed;
-    }
-    void fail() { std::lock_guard<std::mutex> lk(m); failed = true; cv.notify_all(); }
-};
-
-// one persistent host thread per rank >= 1; rank 0 runs on the calling thread
-struct Team {
-    int n = 0;
-    std::vector<std::thread> th;
-    std::mutex m;
-    std::condition_variable cv_go, cv_done;
-    const std::function<void(int)>* job = nullptr;
-    uint64_t gen = 0;
-    int pending = 0;
-    bool stop = false;
-    std::vector<std::string> err;
-
-    void start(int n_) {
-        n = n_;
-        err.assign(n, "");
-        for (int r = 1; r < n; r++) th.emplace_back([this, r] { loop(r); });
-    }
-    void loop(int r) {
-        uint64_t seen = 0;
-        for (;;) {
-            const std::function<void(int)>* f;
-            {
-                std::unique_lock<std::mutex> lk(m);
-                cv_go.wait(lk, [&] { return stop || gen != seen; });
-                if (stop) return;
-                seen = gen;
-                f = job;
-            }
-            try { (*f)(r); } catch (const std::exception& e) { err[r] = e.what(); if (err[r].empty()) err[r] = "error"; }
-            {
-                std::lock_guard<std::mutex> lk(m);
-                pending--;
-            }
-            cv_done.notify_all();
-        }
-    }
-    // f(r) for every rank, concurrently; throws the first rank's error
-    void run(const std::function<void(int)>& f) {
-        for (auto& e : err) e.clear();
-        {
-            std::lock_guard<std::mutex> lk(m);
-            job = &f; gen++; pending = n - 1;
-        }
-        cv_go.notify_all();
-        try { f(0); } catch (const std::exception& e) { err[0] = e.what(); if (err[0].empty()) err[0] = "error"; }
-        {
-            std::unique_lock<std::mutex> lk(m);
-            cv_done.wait(lk, [&] { return pending == 0; });
-        }
-        for (int r = 0; r < n; r++)
-            if (!err[r].empty() && err[r] != "another rank failed") throw std::runtime_error("rank " + std::to_string(r) + ": " + err[r]);
-        for (int r = 0; r < n; r++)
-            if (!err[r].empty()) throw std::runtime_error("rank " + std::to_string(r) + ": " + err[r]);
-    }
-    void shutdown() {
-        {
-            std::lock_guard<std::mutex> lk(m);
-            stop = true;
-        }
-        cv_go.notify_all();
-        for (auto& t : th) t.join();
-        th.clear();
-    }
-};
 
 struct RankState {
     g16_ctx* ctx = nullptr;
@@ -166,7 +79,7 @@ __global__ void __launch_bounds__(256) k_dist_pull(PullArgs a) {
 }
 
 // one array of a, b, c from host memory into D(rb): rows of 2^rb elements, `n_constraints` elements exist, the rest is zero
-void load_host_rows(Fr::T* dst, const void* src, uint64_t n_constraints, uint64_t n, uint64_t n_local, int rb, int g, uint32_t rank, cudaStream_t st) {
+void load_host_rows(g16_ctx* c, int world, Fr::T* dst, const void* src, uint64_t n_constraints, uint64_t n, uint64_t n_local, int rb, int g, uint32_t rank, cudaStream_t st) {
     const uint64_t row = 1ull << rb, rows = n_local >> rb, pitch = row << g;
     auto start = [&](uint64_t hi) { return hi * pitch + (uint64_t)rank * row; };
     if (n_constraints < n) G16_CUDA(cudaMemsetAsync(dst, 0, (size_t)n_local * sizeof(Fr::T), st));
@@ -176,8 +89,15 @@ void load_host_rows(Fr::T* dst, const void* src, uint64_t n_constraints, uint64_
         if (full > rows) full = rows;
     }
     const char* s = (const char*)src;
+    const bool staged = (size_t)full * row * 32 >= ((size_t)1 << 20) && HostStager::pageable(src);
+    if (staged && !c->stager.threads) {
+        int t = c->stage_threads;
+        if (t <= 0) { t = (int)std::thread::hardware_concurrency() / (2 * world); t = t < 2 ? 2 : (t > 8 ? 8 : t); }
+        c->stager.start(t);
+    }
     if (full) {
-        if (g == 0 || rows == 1) G16_CUDA(cudaMemcpyAsync(dst, s + start(0) * 32, (size_t)full * row * 32, cudaMemcpyHostToDevice, st));
+        if (staged) c->stager.copy_rows(dst, s + start(0) * 32, row * 32, pitch * 32, full, st);
+        else if (g == 0 || rows == 1) G16_CUDA(cudaMemcpyAsync(dst, s + start(0) * 32, (size_t)full * row * 32, cudaMemcpyHostToDevice, st));
         else G16_CUDA(cudaMemcpy2DAsync(dst, row * 32, s + start(0) * 32, pitch * 32, row * 32, full, cudaMemcpyHostToDevice, st));
     }
     if (full < rows && start(full) < n_constraints)
@@ -450,7 +370,7 @@ void rank_prove(const ProveJob& J, int r) {
         const char* srcp = (const char*)in.W + (size_t)w_lo * 32;
         if (w_bytes) {
             if (in.device) G16_CUDA(cudaMemcpyPeerAsync(dst, c->device, srcp, dev0, w_bytes, st));
-            else G16_CUDA(cudaMemcpyAsync(dst, srcp, w_bytes, cudaMemcpyHostToDevice, st));
+            else h2d_caller(c, dst, srcp, w_bytes, st, mg.n);
         }
         W_ptr = c->stage[3].as<Fr::T>();
         R.st.h2d_bytes += in.device ? 0 : w_bytes;
@@ -473,7 +393,7 @@ void rank_prove(const ProveJob& J, int r) {
         G16_LAUNCH_CHECK();
     } else {
         const void* srcs[3] = {in.a, in.b, in.c};
-        for (int i = 0; i < 3; i++) load_host_rows(A + i * n_local, srcs[i], in.n_constraints, n, n_local, rb, g, (uint32_t)r, hs);
+        for (int i = 0; i < 3; i++) load_host_rows(c, mg.n, A + i * n_local, srcs[i], in.n_constraints, n, n_local, rb, g, (uint32_t)r, hs);
         uint64_t mine = 0;   // elements of one array that exist on this rank
         for (uint64_t hi = 0; hi < (n_local >> rb); hi++) {
             const uint64_t s = (hi << (rb + g)) + ((uint64_t)r << rb);

@@ -57,6 +57,13 @@ def WithDevice(device, shard_index=0, shard_count=1):
     return opt
 
 
+def WithDevices(devices):
+    """2, 4 or 8 GPU ordinals: one multi-GPU context behind the same Prove call (g16_ctx_create over several devices)."""
+    def opt(cfg):
+        cfg.device, cfg.shard_index, cfg.shard_count = list(devices), 0, 1
+    return opt
+
+
 def NewProverConfig(*opts):
     cfg = ProverConfig()
     for o in opts:
@@ -217,6 +224,10 @@ def Prove(r1cs, pk, full_witness, *opts):
     if cfg.accelerator != "icicle":
         raise _lib.G16Error("accelerator option missing: pass WithIcicleAcceleration() "
                             "(the CPU prover lives in gnark, not in this package)")
+    if cfg.shard_count > 1:
+        # one shard's MSM points are partial sums: assembling them would give a proof that can never verify
+        raise _lib.G16Error("Prove needs the whole key: WithDevice(dev, i, n) with n > 1 uploads one shard only. Use a "
+                            "multi-GPU context (WithDevices([...])), or prove_msms per shard + combine_shards + assemble")
     info = list(getattr(r1cs, "commitment_info", None) or [])
     if info or pk.commitment_keys:
         return _prove_with_commitments(r1cs, pk, full_witness, info, cfg)

@@ -82,7 +82,7 @@ class R1csDesc(ctypes.Structure):
 
 # every symbol include/g16b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
-    "g16_ctx_create", "g16_ctx_destroy", "g16_last_error", "g16_ctx_set", "g16_kernel_launch_count",
+    "g16_ctx_create", "g16_device_count", "g16_ctx_destroy", "g16_last_error", "g16_ctx_set", "g16_kernel_launch_count",
     "g16_pk_upload", "g16_pk_upload_from_file", "g16_pk_free", "g16_pk_wire_range", "g16_pk_placement", "g16_prove_bn254", "g16_prove_bn254_dev", "g16_assemble_proof_bn254",
     "g16_r1cs_upload", "g16_r1cs_free", "g16_r1cs_eval_dev", "g16_prove_bn254_wires",
     "g16_bases_upload", "g16_bases_free", "g16_msm_resident_dev", "g16_msm_resident",
@@ -448,6 +448,10 @@ def _pipe_rates(self):
 
 
 Context.pipe_rates = _pipe_rates
+
+
+def device_count(curve="bn254"):
+    return int(load(curve).g16_device_count())
 
 
 def kernel_launch_count(curve="bn254"):

@@ -94,10 +94,9 @@ func (pk *ProvingKey) ReadDumpToDevice(f *os.File, kIndex []uint32) error {
 		pk.CommitmentKeys = append(pk.CommitmentKeys, ck)
 	}
 
-	var ctx ctxHandle
-	dev := C.int(0)
-	if rc := C.g16_ctx_create(&ctx, C.G16_CURVE_BN254, &dev, 1); rc != 0 {
-		return fmt.Errorf("g16_ctx_create: status %d", int(rc))
+	ctx, err := newContext()
+	if err != nil {
+		return err
 	}
 	infA, infB := boolBytes(pk.InfinityA), boolBytes(pk.InfinityB)
 	var pin runtime.Pinner
@@ -119,6 +118,11 @@ func (pk *ProvingKey) ReadDumpToDevice(f *os.File, kIndex []uint32) error {
 		C.g16_ctx_destroy(ctx)
 		return err
 	}
-	pk.deviceInfo = &deviceInfo{ctx: ctx, handle: uint64(h)}
-	return pk.uploadCommitmentKeys()
+	info := &deviceInfo{ctx: ctx, handle: uint64(h)}
+	if err := info.uploadCommitmentKeys(&pk.ProvingKey); err != nil {
+		C.g16_ctx_destroy(ctx)
+		return err
+	}
+	pk.deviceInfo = info
+	return nil
 }

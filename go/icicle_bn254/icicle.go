@@ -13,7 +13,9 @@ import "C"
 import (
 	"fmt"
 	"math/big"
+	"os"
 	"runtime"
+	"strconv"
 	"time"
 	"unsafe"
 
@@ -88,10 +90,9 @@ func (pk *ProvingKey) setupDevicePointers(nbPublic int, commitmentInfo constrain
 			return fmt.Errorf("commitment info leaves %d private wires, pk.G1.K has %d", len(kIndex), len(pk.G1.K))
 		}
 	}
-	var ctx ctxHandle
-	dev := C.int(0)
-	if rc := C.g16_ctx_create(&ctx, C.G16_CURVE_BN254, &dev, 1); rc != 0 {
-		return fmt.Errorf("g16_ctx_create: status %d (no CUDA device? this backend has no CPU fallback)", int(rc))
+	ctx, err := newContext()
+	if err != nil {
+		return err
 	}
 	infA, infB := boolBytes(pk.InfinityA), boolBytes(pk.InfinityB)
 	var pin runtime.Pinner
@@ -118,19 +119,52 @@ func (pk *ProvingKey) setupDevicePointers(nbPublic int, commitmentInfo constrain
 		C.g16_ctx_destroy(ctx)
 		return err
 	}
-	pk.deviceInfo = &deviceInfo{ctx: ctx, handle: uint64(h)}
-	return pk.uploadCommitmentKeys()
+	// the key becomes visible to Prove only once everything it needs is resident: a failed commitment-key upload
+	// leaves pk.deviceInfo nil (the next Prove retries) instead of a half-initialised device state
+	info := &deviceInfo{ctx: ctx, handle: uint64(h)}
+	if err := info.uploadCommitmentKeys(&pk.ProvingKey); err != nil {
+		C.g16_ctx_destroy(ctx)
+		return err
+	}
+	pk.deviceInfo = info
+	return nil
+}
+
+// newContext creates the library context over every visible GPU the library can group (1, 2, 4 or 8: the largest
+// power of two not above the device count; G16_DEVICES=n caps it).  With more than one GPU the key is placed across
+// them by g16_pk_upload and a single g16_prove_bn254 call uses them all (include/g16b200.h, g16_ctx_create).
+func newContext() (ctxHandle, error) {
+	n := int(C.g16_device_count())
+	if n < 1 {
+		return nil, fmt.Errorf("g16b200: no CUDA device (this backend has no CPU fallback)")
+	}
+	if v, err := strconv.Atoi(os.Getenv("G16_DEVICES")); err == nil && v >= 1 && v < n {
+		n = v
+	}
+	world := 1
+	for world*2 <= n && world < 8 {
+		world *= 2
+	}
+	ids := make([]C.int, world)
+	for i := range ids {
+		ids[i] = C.int(i)
+	}
+	var ctx ctxHandle
+	if rc := C.g16_ctx_create(&ctx, C.G16_CURVE_BN254, &ids[0], C.int(world)); rc != 0 {
+		return nil, fmt.Errorf("g16_ctx_create over %d GPU(s): status %d", world, int(rc))
+	}
+	return ctx, nil
 }
 
 // BSB22 commitment keys (pedersen.ProvingKey{Basis, BasisExpSigma}) stay resident next to the key.
-func (pk *ProvingKey) uploadCommitmentKeys() error {
+func (d *deviceInfo) uploadCommitmentKeys(pk *groth16_bn254.ProvingKey) error {
 	for i := range pk.CommitmentKeys {
 		ck := &pk.CommitmentKeys[i]
 		var kh C.uint64_t
-		if rc := C.g16_commitment_key_upload(pk.ctx, ptrOf(ck.Basis), ptrOf(ck.BasisExpSigma), C.uint64_t(len(ck.Basis)), &kh); rc != 0 {
-			return lastError(pk.ctx, "g16_commitment_key_upload")
+		if rc := C.g16_commitment_key_upload(d.ctx, ptrOf(ck.Basis), ptrOf(ck.BasisExpSigma), C.uint64_t(len(ck.Basis)), &kh); rc != 0 {
+			return lastError(d.ctx, "g16_commitment_key_upload")
 		}
-		pk.commitKeys = append(pk.commitKeys, uint64(kh))
+		d.commitKeys = append(d.commitKeys, uint64(kh))
 	}
 	return nil
 }
@@ -173,8 +207,12 @@ func Prove(r1cs *cs.R1CS, pk *ProvingKey, fullWitness witness.Witness, opts ...b
 		if len(values) != 0 {
 			pin.Pin(&values[0])
 		}
+		// one call in flight per library context: hints may run on several solver goroutines, and other goroutines may
+		// be proving with the same key
+		pk.mu.Lock()
 		rc := C.g16_commit(pk.ctx, C.uint64_t(pk.commitKeys[i]), ptrOf(values), C.uint64_t(len(values)),
 			unsafe.Pointer(&proof.Commitments[i]), unsafe.Pointer(&poks[i]))
+		pk.mu.Unlock()
 		pin.Unpin()
 		if rc != 0 {
 			return lastError(pk.ctx, "g16_commit")
@@ -214,26 +252,31 @@ func Prove(r1cs *cs.R1CS, pk *ProvingKey, fullWitness witness.Witness, opts ...b
 		}
 	}
 
-	var out [C.G16_PROVE_OUT_BYTES]byte
+	// uint64 backing store: the block is reinterpreted as G1Affine / G2Affine below, which need 8-byte alignment
+	var out [C.G16_PROVE_OUT_BYTES / 8]uint64
 	var stats C.g16_stats
 	var pin runtime.Pinner
 	pin.Pin(&solution.W[0])
 	pin.Pin(&solution.A[0])
 	pin.Pin(&solution.B[0])
 	pin.Pin(&solution.C[0])
+	// The slices are ordinary (pageable) Go heap memory: the library stages them through its pinned ring with its own
+	// copier threads ("stage_threads"), W first so that the MSMs over W run while a, b, c are still being staged.
+	pk.mu.Lock()
 	rc := C.g16_prove_bn254(pk.ctx, C.uint64_t(pk.handle), unsafe.Pointer(&solution.W[0]), C.uint64_t(len(solution.W)),
 		unsafe.Pointer(&solution.A[0]), unsafe.Pointer(&solution.B[0]), unsafe.Pointer(&solution.C[0]),
 		C.uint64_t(len(solution.A)), unsafe.Pointer(&out[0]), &stats)
+	pk.mu.Unlock()
 	pin.Unpin()
 	if rc != 0 {
 		return nil, lastError(pk.ctx, "g16_prove_bn254")
 	}
 	// the five raw MSM results are gnark memory images
 	arMsm := *(*curve.G1Affine)(unsafe.Pointer(&out[0]))
-	bs1Msm := *(*curve.G1Affine)(unsafe.Pointer(&out[64]))
-	krsK := *(*curve.G1Affine)(unsafe.Pointer(&out[128]))
-	krsHZ := *(*curve.G1Affine)(unsafe.Pointer(&out[192]))
-	bs2Msm := *(*curve.G2Affine)(unsafe.Pointer(&out[256]))
+	bs1Msm := *(*curve.G1Affine)(unsafe.Pointer(&out[8]))
+	krsK := *(*curve.G1Affine)(unsafe.Pointer(&out[16]))
+	krsHZ := *(*curve.G1Affine)(unsafe.Pointer(&out[24]))
+	bs2Msm := *(*curve.G2Affine)(unsafe.Pointer(&out[32]))
 
 	// epilogue: r, s, kr = -r*s; deltas = [r, s, kr] * delta
 	var _r, _s, _kr fr.Element

@@ -1,6 +1,8 @@
 package icicle_bn254
 
 import (
+	"sync"
+
 	groth16_bn254 "github.com/consensys/gnark/backend/groth16/bn254"
 	cs "github.com/consensys/gnark/constraint/bn254"
 )
@@ -9,6 +11,7 @@ import (
 // uploaded key (bases in Montgomery affine form, index maps, domain twiddles).  It is never serialised, so a key
 // read back with ReadFrom re-uploads lazily on its next Prove.
 type deviceInfo struct {
+	mu         sync.Mutex // the library context is thread-compatible (one call in flight): Prove and the bsb22 hint hold it
 	ctx        ctxHandle
 	handle     uint64
 	commitKeys []uint64 // one resident pedersen.ProvingKey per BSB22 commitment

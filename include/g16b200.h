@@ -64,6 +64,8 @@ typedef struct {
  * device_ids[0].  The devices must be peer-accessible.  The same ordinal may be listed more than once: the ranks then
  * share that GPU (functional emulation for tests; no speed-up). */
 int g16_ctx_create(g16_ctx** out, int curve_id, const int* device_ids, int n_devices);
+/* CUDA devices visible to this process (0 when there is none or the driver cannot be initialised) */
+int g16_device_count(void);
 void g16_ctx_destroy(g16_ctx* ctx);
 const char* g16_last_error(const g16_ctx* ctx);
 /* tunables: "msm_c" (0 = auto, 8..16), "msm_waves" (accumulate waves, default 4),
@@ -72,7 +74,10 @@ const char* g16_last_error(const g16_ctx* ctx);
  * analogue of icicle's precompute_factor -- so that all windows of a prove MSM share one bucket set and the window
  * can grow to 20 bits; costs 13x the key in HBM and is skipped when that exceeds half of the free memory; set 0
  * before the upload to skip the tables, or after it to run the classic per-window path on the same key),
- * "msm_pre_c" (window bits, 16..21, of the tables built by later uploads; 0 = chosen from the array size) */
+ * "msm_pre_c" (window bits, 16..21, of the tables built by later uploads; 0 = chosen from the array size),
+ * "stage_threads" (copier threads that stage PAGEABLE caller memory -- e.g. Go heap slices -- into the context's pinned
+ * ring; 0 = half of the host cores divided by the GPU count, between 2 and 8; page-locked buffers are DMA'd directly),
+ * "g2_weight" (multi-GPU key placement: cost of a G2 point in hundredths of a G1 point, default 340; before the upload) */
 int g16_ctx_set(g16_ctx* ctx, const char* key, int64_t value);
 /* total kernels launched by this library in this process (bench.py's gpu_launches evidence) */
 uint64_t g16_kernel_launch_count(void);

@@ -137,3 +137,18 @@ def test_sharded_key_with_wires_only_entry_point(ctx, case):
         ctx.pk_free(h)
     ctx.r1cs_free(r1)
     assert_limbs_equal(g16.combine_shards(blocks), case.want, "3-way sharded wires-only prove")
+
+
+def test_prove_surface_over_a_group_and_shard_rejection(case):
+    """gnark_icicle_b200.Prove (the mirror of icicle_bn254.Prove) over a multi-GPU context gives the proof the
+    single-GPU context gives; a single shard of the key is refused instead of yielding a proof that cannot verify."""
+    sol = g16.R1CSSolution(W=case.W, A=case.a, B=case.b, C=case.c)
+    opts = (g16.WithIcicleAcceleration(), g16.WithRandomness(case.r, case.s))
+    one = g16.Prove(None, case.pk, sol, *opts)
+    case.pk.free_device()
+    grp = g16.Prove(None, case.pk, sol, g16.WithDevices(_devices(4)), *opts)
+    case.pk.free_device()
+    assert grp.raw() == one.raw()
+    assert grp.raw() == g16.assemble(case.pk, case.want, case.r, case.s).raw()
+    with pytest.raises(lib.G16Error, match="needs the whole key"):
+        g16.Prove(None, case.pk, sol, g16.WithDevice(0, 0, 2), *opts)
