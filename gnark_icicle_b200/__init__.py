@@ -5,8 +5,9 @@
   groth16.py   mirror of package icicle_bn254 (Prove, ProvingKey, WithIcicleAcceleration)
   bsb22.py     BSB22 commitments on that path (hint override, commitment keys on the device, folded PoK)
   dump.py      ProvingKey.WriteDump / ReadDump and the direct file -> device key load
-  marshal.py   Proof.WriteTo / WriteRawTo / ReadFrom (compressed and raw point encodings, BN254)
+  marshal.py   Proof / VerifyingKey / ProvingKey WriteTo, WriteRawTo, ReadFrom (compressed and raw encodings, BN254)
   witness.py   witness.Witness binary protocol
+  kzg.py       kzg.Commit (PLONK prover) and the MPC-setup linear combinations on the same MSM kernels
 
 The directory ``gnark-icicle_b200`` at the repo root is a link to this package (a hyphen is not importable).
 """
@@ -14,8 +15,8 @@ from . import lib, bsb22
 from .groth16 import (HasIcicle, Prove, ProvingKey, Proof, R1CSSolution, WithIcicleAcceleration, WithRandomness,
                       WithDevice, WithDevices, NewProverConfig, prove_msms, assemble, combine_shards, ConstraintSystem,
                       prove_msms_wires)
-from . import dump, marshal, witness
+from . import dump, marshal, witness, kzg
 
-__all__ = ["lib", "bsb22", "dump", "marshal", "witness", "HasIcicle", "Prove", "ProvingKey", "Proof", "R1CSSolution", "WithIcicleAcceleration",
+__all__ = ["lib", "bsb22", "dump", "marshal", "witness", "kzg", "HasIcicle", "Prove", "ProvingKey", "Proof", "R1CSSolution", "WithIcicleAcceleration",
            "WithRandomness", "WithDevice", "WithDevices", "NewProverConfig", "prove_msms", "assemble", "combine_shards",
            "ConstraintSystem", "prove_msms_wires"]

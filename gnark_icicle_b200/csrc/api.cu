@@ -441,7 +441,7 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
         G16_CUDA(cudaEventElapsedTime(&stats->ms_total, ev[0], ev[14]));
         stats->ms_host = std::chrono::duration<float, std::milli>(t1 - t0).count();
         stats->d2h_bytes = 0;
-        for (int i = 0; i < 5; i++) stats->d2h_bytes += (uint64_t)2 * plan[i].W * (i == 4 ? sizeof(G2::Xyzz) : sizeof(G1::Xyzz));
+        for (int i = 0; i < 5; i++) stats->d2h_bytes += (uint64_t)(1 + plan[i].nfold) * plan[i].W * (i == 4 ? sizeof(G2::Xyzz) : sizeof(G1::Xyzz));
         stats->kernel_launches = (uint32_t)(launch_counter().load() - launches0);
     }
     static const bool timeline = getenv("G16_TIMELINE") != nullptr;   // diagnostic: event offsets from the start of the prove

@@ -45,8 +45,11 @@ struct MsmPlan {
     int c, W;          // window bits; number of bucket SETS (= windows; 1 with precomputed multiples)
     uint32_t B;        // buckets per set = 2^(c-1)
     uint32_t NB;       // W * B
-    int red_m, red_rb; // bucket-reduce level 2 (over the level-1 sums): sums per thread, CTAs per set
-    int fold_m, fold_rb; // bucket-reduce level 1: buckets per thread (power of two), CTAs per set
+    // bucket reduction: nfold fold levels (k_bucket_fold: fold_m[k] consecutive elements per thread, fold_n[k] elements
+    // enter level k, fold_n[0] = B), then k_bucket_reduce over the fold_n[nfold] remaining sums (red_m per thread, red_rb CTAs)
+    int nfold, fold_m[2];
+    uint32_t fold_n[3];
+    int red_m, red_rb;
     int Wd;            // digits (bucket entries) per scalar: = W, or the window count when W == 1 (precomputed mode)
     bool pre;          // bases are a table [Wd][n] of 2^(c j) P_i: every window feeds the same bucket set
 };
@@ -108,19 +111,30 @@ inline MsmPlan msm_plan_pre(int c) {
     p.pre = true;
     return p;
 }
-// Two-level reduction of a bucket set: level 1 folds fold_m consecutive buckets per thread (no scalar multiplication),
-// level 2 is the weighted sum of the B / fold_m level-1 sums (k_bucket_reduce).  B >= 128 (c >= 8).
+// Reduction of a bucket set in up to three levels.  A fold level turns n elements into n / m sums (k_bucket_fold, m
+// consecutive elements per thread, no scalar multiplication); the last level is the weighted sum of what remains
+// (k_bucket_reduce).  Sets of >= 8192 buckets fold until fewer than 8192 sums remain (c = 20: 2^19 -> 2^15 -> 2^12): the
+// dependent chain of the last level shrinks from ~86 group additions (one fold of 16, then 16 sums per thread and an
+// 11-bit double-and-add) to ~28, and its thread count stays at 2048.  B >= 128 (c >= 8).
 inline void msm_plan_reduce(MsmPlan& p) {
-    uint32_t fm = p.B / MSM_RED_THREADS;
-    if (fm > 16) fm = 16;
-    p.fold_m = (int)fm;
-    p.fold_rb = (int)(p.B / (MSM_RED_THREADS * fm));
-    const uint32_t nt = p.B / fm;                        // level-1 sums per set, a multiple of 64
-    uint32_t m = nt / (MSM_RED_THREADS * 32);
+    uint32_t cur = p.B;
+    p.nfold = 0;
+    p.fold_n[0] = cur;
+    if (cur >= 8192) {
+        // first level by 16 when that still leaves >= 2048 sums (measured at c = 20: 0.38 ms by 16 against 0.48 ms by 8 -- twice
+        // the CTAs, each with its own shared-memory tree, and a ragged second wave), the second level by 8
+        while (p.nfold < 2 && cur >= 8192) { const uint32_t m = (p.nfold == 0 && cur >= 32768) ? 16 : 8; p.fold_m[p.nfold] = (int)m; cur /= m; p.fold_n[++p.nfold] = cur; }
+    } else {
+        uint32_t fm = cur / MSM_RED_THREADS;
+        if (fm > 16) fm = 16;
+        p.fold_m[0] = (int)fm; cur /= fm; p.nfold = 1; p.fold_n[1] = cur;
+    }
+    uint32_t m = cur / (MSM_RED_THREADS * 32);           // cur is a multiple of 64
     if (m < 1) m = 1;
     p.red_m = (int)m;
-    p.red_rb = (int)(nt / (MSM_RED_THREADS * m));
+    p.red_rb = (int)(cur / (MSM_RED_THREADS * m));
 }
+inline uint32_t msm_fold_ctas(const MsmPlan& p, int k) { return p.fold_n[k] / (uint32_t)p.fold_m[k] / MSM_RED_THREADS; }
 
 // ------------------------------------------------------------------ digits
 static __global__ void k_digits(const Fr::T* __restrict__ scalars, const uint32_t* __restrict__ map, uint64_t n,
@@ -622,9 +636,10 @@ k_fixup_heavy(const uint32_t* __restrict__ offsets, uint32_t nb, uint32_t nthrea
 // The weighted sum  sum_k (k+1) B_k  of a bucket set in two levels.  With k = t*m + j (thread t, j < m):
 //   (k+1) = (t+1)*m - (m-1-j)   =>   total = m * sum_t (t+1) S_t  -  sum_t T_t,
 //   S_t = sum_j B_{tm+j},  T_t = sum_j (m-1-j) B_{tm+j}  -- both from one forward running sum, no scalar multiplication.
-// Level 1 (k_bucket_fold): S_t -> fold[w][t], T_t tree-summed per CTA -> partialT.  Level 2: k_bucket_reduce on the
-// S_t as a bucket set of B/m entries.  The host finishes with log2(m) doublings and one subtraction per set.
-// grid (fold_rb, W)
+// A fold level (k_bucket_fold): S_t -> fold[w][t], T_t tree-summed per CTA -> partialT; the S_t form a bucket set of
+// B/m entries that is folded again or goes to k_bucket_reduce.  The host finishes with log2(m) doublings and one
+// subtraction per level and set.
+// grid (B / m / 64, W)
 template <class C>
 __global__ void __launch_bounds__(MSM_RED_THREADS)
 k_bucket_fold(const typename C::Xyzz* __restrict__ buckets, uint32_t B, int m, typename C::Xyzz* __restrict__ fold,
@@ -682,21 +697,26 @@ k_bucket_reduce(const typename C::Xyzz* __restrict__ buckets, uint32_t B, int m,
     if (threadIdx.x == 0) store_xyzz<C>(partial + (uint64_t)w * gridDim.x + blockIdx.x, sm[0]);
 }
 
-// grid W, 32 threads: sum the rb partials of a window (rb > 32 in precomputed mode: strided first)
+// grid (W, segments), 128 threads: segment y sums its cnt[y] partials of window x (partial + off[y] + x * cnt[y])
+constexpr int MSM_WSUM_THREADS = 128;
+struct WsumArgs { uint32_t off[3], cnt[3]; };
 template <class C>
-__global__ void __launch_bounds__(32) k_window_sum(const typename C::Xyzz* __restrict__ partial, int rb, typename C::Xyzz* __restrict__ wsum) {
+__global__ void __launch_bounds__(MSM_WSUM_THREADS) k_window_sum(const typename C::Xyzz* __restrict__ partial, WsumArgs a, typename C::Xyzz* __restrict__ wsum) {
     typedef typename C::Xyzz Xyzz;
-    __shared__ Xyzz sm[32];
-    const int w = blockIdx.x;
+    extern __shared__ uint4 wsum_sm[];
+    Xyzz* sm = reinterpret_cast<Xyzz*>(wsum_sm);
+    const int w = blockIdx.x, seg = blockIdx.y;
+    const uint32_t rb = a.cnt[seg];
+    const Xyzz* src = partial + a.off[seg] + (uint64_t)w * rb;
     Xyzz mine = C::inf();
-    for (int i = threadIdx.x; i < rb; i += 32) C::add(mine, load_xyzz<C>(partial + (uint64_t)w * rb + i));
+    for (uint32_t i = threadIdx.x; i < rb; i += MSM_WSUM_THREADS) C::add(mine, load_xyzz<C>(src + i));
     sm[threadIdx.x] = mine;
-    __syncwarp();
-    for (int stride = 16; stride >= 1; stride >>= 1) {
-        if ((int)threadIdx.x < stride) { Xyzz a = sm[threadIdx.x]; C::add(a, sm[threadIdx.x + stride]); sm[threadIdx.x] = a; }
-        __syncwarp();
+    __syncthreads();
+    for (int stride = MSM_WSUM_THREADS / 2; stride >= 1; stride >>= 1) {
+        if ((int)threadIdx.x < stride) { Xyzz x = sm[threadIdx.x]; C::add(x, sm[threadIdx.x + stride]); sm[threadIdx.x] = x; }
+        __syncthreads();
     }
-    if (threadIdx.x == 0) store_xyzz<C>(wsum + w, sm[0]);
+    if (threadIdx.x == 0) store_xyzz<C>(wsum + (uint64_t)seg * gridDim.x + w, sm[0]);
 }
 
 // ------------------------------------------------------------------ host driver
@@ -746,10 +766,14 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
     ws.buckets.reserve((size_t)pl.NB * sizeof(Xyzz));
     ws.head.reserve((size_t)nthreads * sizeof(Xyzz));
     ws.tail.reserve((size_t)nthreads * sizeof(Xyzz));
-    ws.fold.reserve((size_t)pl.W * (pl.B / pl.fold_m) * sizeof(Xyzz));
-    ws.partial.reserve((size_t)pl.W * (pl.red_rb + pl.fold_rb) * sizeof(Xyzz));
-    ws.wsum.reserve((size_t)2 * pl.W * sizeof(Xyzz));
-    ws.host_wsum.reserve((size_t)2 * pl.W * sizeof(Xyzz));
+    {
+        size_t fold_elems = 0, partials = pl.red_rb;
+        for (int k = 0; k < pl.nfold; k++) { fold_elems += pl.fold_n[k + 1]; partials += msm_fold_ctas(pl, k); }
+        ws.fold.reserve((size_t)pl.W * fold_elems * sizeof(Xyzz));
+        ws.partial.reserve((size_t)pl.W * partials * sizeof(Xyzz));
+    }
+    ws.wsum.reserve((size_t)3 * pl.W * sizeof(Xyzz));
+    ws.host_wsum.reserve((size_t)3 * pl.W * sizeof(Xyzz));
 
     uint32_t* sorted = ws.sorted.as<uint32_t>();
     uint32_t* counts = ws.counts.as<uint32_t>();
@@ -850,20 +874,34 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
         G16_LAUNCH_CHECK();
     }
     {
-        Xyzz* partialU = ws.partial.as<Xyzz>();
-        Xyzz* partialT = partialU + (size_t)pl.W * pl.red_rb;
-        Xyzz* wsum = ws.wsum.as<Xyzz>();                 // [0, W): U_w = sum_t (t+1) S_t, [W, 2W): T_w
-        dim3 fgrid(pl.fold_rb, pl.W), rgrid(pl.red_rb, pl.W);
-        k_bucket_fold<C><<<fgrid, MSM_RED_THREADS, 0, st>>>(buckets, pl.B, pl.fold_m, ws.fold.as<Xyzz>(), partialT);
+        // partial: [U: W x red_rb][T of fold level 0: W x ctas_0][T of level 1: W x ctas_1];  wsum: [U_w][T0_w][T1_w]
+        Xyzz* partial = ws.partial.as<Xyzz>();
+        Xyzz* wsum = ws.wsum.as<Xyzz>();
+        WsumArgs wa = {};
+        wa.off[0] = 0; wa.cnt[0] = (uint32_t)pl.red_rb;
+        uint32_t poff = (uint32_t)pl.W * pl.red_rb;
+        const Xyzz* level_in = buckets;
+        Xyzz* level_out = ws.fold.as<Xyzz>();
+        for (int k = 0; k < pl.nfold; k++) {
+            const uint32_t ctas = msm_fold_ctas(pl, k);
+            dim3 fgrid(ctas, pl.W);
+            k_bucket_fold<C><<<fgrid, MSM_RED_THREADS, 0, st>>>(level_in, pl.fold_n[k], pl.fold_m[k], level_out, partial + poff);
+            G16_LAUNCH_CHECK();
+            wa.off[1 + k] = poff; wa.cnt[1 + k] = ctas;
+            poff += (uint32_t)pl.W * ctas;
+            level_in = level_out;
+            level_out += (size_t)pl.W * pl.fold_n[k + 1];
+        }
+        dim3 rgrid(pl.red_rb, pl.W);
+        k_bucket_reduce<C><<<rgrid, MSM_RED_THREADS, 0, st>>>(level_in, pl.fold_n[pl.nfold], pl.red_m, partial);
         G16_LAUNCH_CHECK();
-        k_bucket_reduce<C><<<rgrid, MSM_RED_THREADS, 0, st>>>(ws.fold.as<Xyzz>(), pl.B / pl.fold_m, pl.red_m, partialU);
-        G16_LAUNCH_CHECK();
-        k_window_sum<C><<<pl.W, 32, 0, st>>>(partialU, pl.red_rb, wsum);
-        G16_LAUNCH_CHECK();
-        k_window_sum<C><<<pl.W, 32, 0, st>>>(partialT, pl.fold_rb, wsum + pl.W);
+        const size_t wsm = (size_t)MSM_WSUM_THREADS * sizeof(Xyzz);
+        if (wsm > 48 * 1024) G16_CUDA(cudaFuncSetAttribute(k_window_sum<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsm));
+        dim3 wgrid(pl.W, 1 + pl.nfold);
+        k_window_sum<C><<<wgrid, MSM_WSUM_THREADS, wsm, st>>>(partial, wa, wsum);
         G16_LAUNCH_CHECK();
     }
-    G16_CUDA(cudaMemcpyAsync(ws.host_wsum.p, ws.wsum.p, (size_t)2 * pl.W * sizeof(Xyzz), cudaMemcpyDeviceToHost, st));
+    G16_CUDA(cudaMemcpyAsync(ws.host_wsum.p, ws.wsum.p, (size_t)(1 + pl.nfold) * pl.W * sizeof(Xyzz), cudaMemcpyDeviceToHost, st));
     if (st != main_st) {   // the MSM's own stream completes when its tail does
         G16_CUDA(cudaEventRecord(ws.tail_done, st));
         G16_CUDA(cudaStreamWaitEvent(main_st, ws.tail_done, 0));
@@ -879,9 +917,11 @@ typename C::Xyzz msm_finish_xyzz(const MsmWorkspace& ws, const MsmPlan& pl) {
     Xyzz acc = C::inf();
     for (int w = pl.W - 1; w >= 0; w--) {
         for (int i = 0; i < pl.c; i++) acc = C::dbl(acc);
-        Xyzz u = wsum[w];                                  // set total = fold_m * U_w - T_w
-        for (int m = pl.fold_m; m > 1; m >>= 1) u = C::dbl(u);
-        C::add(u, C::neg(wsum[pl.W + w]));
+        Xyzz u = wsum[w];                                  // set total R_0, R_k = fold_m[k] * R_(k+1) - T_k, R_nfold = U_w
+        for (int k = pl.nfold - 1; k >= 0; k--) {
+            for (int m = pl.fold_m[k]; m > 1; m >>= 1) u = C::dbl(u);
+            C::add(u, C::neg(wsum[(size_t)(1 + k) * pl.W + w]));
+        }
         C::add(acc, u);
     }
     return acc;

@@ -203,3 +203,169 @@ def proof_read_from(buf):
     commitments = [g1() for _ in range(count)]
     pok = g1()
     return Proof(Ar=ar, Bs=bs, Krs=krs, Commitments=commitments, CommitmentPok=pok), off
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# VerifyingKey / ProvingKey WriteTo, WriteRawTo, ReadFrom (backend/groth16/bn254/marshal.go:99-236, :242-385).
+# Container conventions of gnark-crypto's curve.Encoder, restated [recollection] like the point encodings above:
+# uint32 / uint64 big-endian; a point slice is a uint32 count followed by the points; [][]uint64 is a uint32 count of
+# rows, each row a uint32 count followed by its uint64s; []bool is a uint32 count followed by the bits packed LSB-first
+# (the convention dump.py uses for the same fields); fft.Domain.WriteTo as in dump.py; pedersen.VerifyingKey = G,
+# GSigmaNeg (G2), pedersen.ProvingKey = Basis, BasisExpSigma (G1 slices).
+from dataclasses import dataclass, field as _field
+
+
+@dataclass
+class PedersenVerifyingKey:
+    """pedersen.VerifyingKey (verify.go:107-115 consumes it)."""
+    G: np.ndarray            # (16,) G2Affine
+    GSigmaNeg: np.ndarray    # (16,)
+
+
+@dataclass
+class VerifyingKey:
+    """setup.go:60-83 fields that go on the wire (vk.e and the negated points are recomputed by Precompute)."""
+    g1_alpha: np.ndarray
+    g1_beta: np.ndarray
+    g2_beta: np.ndarray
+    g2_gamma: np.ndarray
+    g1_delta: np.ndarray
+    g2_delta: np.ndarray
+    g1_k: np.ndarray                                     # (nbPublic + nbCommitments, 8)
+    public_and_commitment_committed: list = _field(default_factory=list)
+    commitment_keys: list = _field(default_factory=list)   # []PedersenVerifyingKey
+
+
+def _g1_slice(arr, raw):
+    arr = np.asarray(arr, dtype=np.uint64).reshape(-1, 8)
+    return struct.pack(">I", len(arr)) + b"".join(g1_encode(p, raw) for p in arr)
+
+
+def _g2_slice(arr, raw):
+    arr = np.asarray(arr, dtype=np.uint64).reshape(-1, 16)
+    return struct.pack(">I", len(arr)) + b"".join(g2_encode(p, raw) for p in arr)
+
+
+def _bools(b):
+    b = np.asarray(b, dtype=np.uint8)
+    return struct.pack(">I", len(b)) + np.packbits(b, bitorder="little").tobytes()
+
+
+def vk_write_to(vk, raw=False):
+    """VerifyingKey.WriteTo (compressed) / WriteRawTo: [alpha]1,[beta]1,[beta]2,[gamma]2,[delta]1,[delta]2,
+    uint32(len(Kvk)),[Kvk]1, PublicAndCommitmentCommitted, uint32(len(CommitmentKeys)), the Pedersen keys."""
+    out = [g1_encode(vk.g1_alpha, raw), g1_encode(vk.g1_beta, raw), g2_encode(vk.g2_beta, raw), g2_encode(vk.g2_gamma, raw),
+           g1_encode(vk.g1_delta, raw), g2_encode(vk.g2_delta, raw), _g1_slice(vk.g1_k, raw)]
+    rows = vk.public_and_commitment_committed or []
+    out.append(struct.pack(">I", len(rows)))
+    for row in rows:
+        out.append(struct.pack(">I", len(row)) + b"".join(struct.pack(">Q", int(v)) for v in row))
+    out.append(struct.pack(">I", len(vk.commitment_keys)))
+    for k in vk.commitment_keys:
+        out += [g2_encode(k.G, raw), g2_encode(k.GSigmaNeg, raw)]
+    return b"".join(out)
+
+
+class _Reader:
+    def __init__(self, buf, off=0):
+        self.buf, self.off = buf, off
+        self.raw = None            # decided by the first point met
+
+    def u32(self):
+        (v,) = struct.unpack(">I", self.buf[self.off:self.off + 4])
+        self.off += 4
+        return v
+
+    def u64(self):
+        (v,) = struct.unpack(">Q", self.buf[self.off:self.off + 8])
+        self.off += 8
+        return v
+
+    def _point(self, words, decode):
+        flag = self.buf[self.off] & M_MASK
+        if self.raw is None:
+            # uniform over a key; an infinity flag says nothing, so a leading infinity leaves the question open
+            if flag != M_INFINITY:
+                self.raw = flag == M_UNCOMPRESSED
+        if flag == M_INFINITY:
+            if self.raw is None:
+                raise ValueError("cannot tell the encoding from a leading point at infinity")
+            self.off += (8 * words) if self.raw else (4 * words)
+            return np.zeros(words, dtype=np.uint64)
+        pt, n = decode(self.buf, self.off)
+        self.off += n
+        return pt
+
+    def g1(self):
+        return self._point(8, g1_decode)
+
+    def g2(self):
+        return self._point(16, g2_decode)
+
+    def g1_slice(self):
+        n = self.u32()
+        return np.array([self.g1() for _ in range(n)], dtype=np.uint64).reshape(n, 8)
+
+    def g2_slice(self):
+        n = self.u32()
+        return np.array([self.g2() for _ in range(n)], dtype=np.uint64).reshape(n, 16)
+
+    def bools(self):
+        n = self.u32()
+        rawb = np.frombuffer(self.buf[self.off:self.off + (n + 7) // 8], dtype=np.uint8)
+        self.off += (n + 7) // 8
+        return np.unpackbits(rawb, bitorder="little")[:n].astype(np.uint8)
+
+
+def vk_read_from(buf):
+    """VerifyingKey.ReadFrom: either encoding; returns (VerifyingKey, bytes read)."""
+    r = _Reader(buf)
+    alpha, beta1, beta2, gamma2, delta1, delta2 = r.g1(), r.g1(), r.g2(), r.g2(), r.g1(), r.g2()
+    k = r.g1_slice()
+    rows = [[r.u64() for _ in range(r.u32())] for _ in range(r.u32())]
+    keys = [PedersenVerifyingKey(r.g2(), r.g2()) for _ in range(r.u32())]
+    return VerifyingKey(alpha, beta1, beta2, gamma2, delta1, delta2, k, rows, keys), r.off
+
+
+def pk_write_to(pk, raw=False):
+    """ProvingKey.WriteTo / WriteRawTo (marshal.go:242-312): Domain, [alpha]1,[beta]1,[delta]1, A, B, Z, K, [beta]2,
+    [delta]2, B2, nbWires, NbInfinityA, NbInfinityB, InfinityA, InfinityB, uint32(len(CommitmentKeys)), the keys."""
+    from .dump import _domain_bytes
+    if pk.curve != "bn254":
+        raise ValueError("key wire format is implemented for BN254")
+    ia, ib = np.asarray(pk.infinity_a, dtype=np.uint8), np.asarray(pk.infinity_b, dtype=np.uint8)
+    out = [_domain_bytes(pk.domain_n, pk.curve),
+           g1_encode(pk.g1_alpha, raw), g1_encode(pk.g1_beta, raw), g1_encode(pk.g1_delta, raw),
+           _g1_slice(pk.g1_a, raw), _g1_slice(pk.g1_b, raw), _g1_slice(pk.g1_z, raw), _g1_slice(pk.g1_k, raw),
+           g2_encode(pk.g2_beta, raw), g2_encode(pk.g2_delta, raw), _g2_slice(pk.g2_b, raw),
+           struct.pack(">QQQ", len(ia), int(ia.sum()), int(ib.sum())), _bools(ia), _bools(ib),
+           struct.pack(">I", len(pk.commitment_keys))]
+    for k in pk.commitment_keys:
+        out += [_g1_slice(k.basis, raw), _g1_slice(k.basis_exp_sigma, raw)]
+    return b"".join(out)
+
+
+def pk_read_from(buf, nb_public=0):
+    """ProvingKey.ReadFrom: either encoding; returns (gnark_icicle_b200.ProvingKey, bytes read).  nb_public is not on
+    the wire (the reference takes it from the constraint system at prove time)."""
+    from .bsb22 import CommitmentKey
+    from .dump import _domain_bytes
+    from .groth16 import ProvingKey
+    (n,) = struct.unpack(">Q", buf[:8])
+    dom = _domain_bytes(n, "bn254")
+    if bytes(buf[:len(dom)]) != dom:
+        raise ValueError("unexpected fft.Domain encoding")
+    r = _Reader(buf, len(dom))
+    alpha, beta, delta = r.g1(), r.g1(), r.g1()
+    a, b, z, k = r.g1_slice(), r.g1_slice(), r.g1_slice(), r.g1_slice()
+    beta2, delta2 = r.g2(), r.g2()
+    b2 = r.g2_slice()
+    nb_wires, nia, nib = r.u64(), r.u64(), r.u64()
+    ia, ib = r.bools(), r.bools()
+    if len(ia) != nb_wires or len(ib) != nb_wires or int(ia.sum()) != nia or int(ib.sum()) != nib:
+        raise ValueError("infinity masks do not match their counts")
+    keys = [CommitmentKey(r.g1_slice(), r.g1_slice()) for _ in range(r.u32())]
+    pk = ProvingKey(domain_n=n, g1_alpha=alpha, g1_beta=beta, g1_delta=delta, g1_a=a, g1_b=b, g1_z=z, g1_k=k,
+                    g2_beta=beta2, g2_delta=delta2, g2_b=b2, infinity_a=ia, infinity_b=ib, nb_wires=int(nb_wires),
+                    nb_public=nb_public, commitment_keys=keys)
+    return pk, r.off
