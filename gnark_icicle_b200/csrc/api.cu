@@ -520,39 +520,55 @@ extern "C" int g16_prove_bn254(g16_ctx* ctx, uint64_t pk_handle, const void* W, 
 }
 
 // =================================================================== resident bases
-extern "C" int g16_bases_upload(g16_ctx* ctx, const void* bases, uint64_t n, int g2, int from_device, uint64_t* handle) {
-    return guarded(ctx, [&] {
-        if (!handle || (n && !bases)) throw std::runtime_error("null argument");
-        g16_ctx::Bases b;
-        b.n = n; b.g2 = g2 != 0;
-        cudaStream_t st = ctx->stream;
-        const void* src = bases;
-        if (from_device && n) {   // upload_bases copies host -> device; for a device source copy into row 0 afterwards
+namespace g16 {
+void bases_upload_one(g16_ctx* ctx, const void* bases, uint64_t n, bool g2, bool from_device, int src_device, uint64_t handle) {
+    g16_ctx::Bases b;
+    b.n = n; b.g2 = g2;
+    cudaStream_t st = ctx->stream;
+    try {
+        if (from_device && n) {   // upload_bases copies host -> device; a device source is copied into row 0 here
             int pre_c = 0;
             const size_t row = (size_t)n * (g2 ? G2SZ : G1SZ);
             if (ctx->msm_precompute && n >= PRECOMPUTE_MIN_POINTS) {
-                const int c = msm_pre_choose_c(n, g2 != 0, ctx->msm_pre_c);
+                const int c = msm_pre_choose_c(n, g2, ctx->msm_pre_c);
                 size_t free_b = 0, total_b = 0;
                 G16_CUDA(cudaMemGetInfo(&free_b, &total_b));
                 if (row * (size_t)(255 / c + 1) <= free_b / 2) pre_c = c;
             }
             b.table.reserve(pre_c ? row * (size_t)(255 / pre_c + 1) : row);
-            G16_CUDA(cudaMemcpyAsync(b.table.p, src, row, cudaMemcpyDeviceToDevice, st));
+            if (src_device == ctx->device) G16_CUDA(cudaMemcpyAsync(b.table.p, bases, row, cudaMemcpyDeviceToDevice, st));
+            else G16_CUDA(cudaMemcpyPeerAsync(b.table.p, ctx->device, bases, src_device, row, st));
             if (pre_c) { if (g2) msm_g2_precompute(b.table.as<G2::Aff>(), n, pre_c, st); else msm_g1_precompute(b.table.as<G1::Aff>(), n, pre_c, st); }
             b.pre_c = pre_c;
         } else if (g2) {
-            upload_bases<G2>(ctx, b.table, src, n, b.pre_c, st);
+            upload_bases<G2>(ctx, b.table, bases, n, b.pre_c, st);
         } else {
-            upload_bases<G1>(ctx, b.table, src, n, b.pre_c, st);
+            upload_bases<G1>(ctx, b.table, bases, n, b.pre_c, st);
         }
         G16_CUDA(cudaStreamSynchronize(st));
-        uint64_t h = ctx->next_pk++;
-        ctx->bases[h] = b;
+    } catch (...) {
+        b.table.release();
+        throw;
+    }
+    ctx->bases[handle] = b;
+}
+}  // namespace g16
+
+// a group context shards arrays of at least this many points per GPU over its ranks; smaller ones stay on the first GPU
+static constexpr uint64_t GROUP_MIN_POINTS_PER_RANK = 1 << 16;
+
+extern "C" int g16_bases_upload(g16_ctx* ctx, const void* bases, uint64_t n, int g2, int from_device, uint64_t* handle) {
+    return guarded(ctx, [&] {
+        if (!handle || (n && !bases)) throw std::runtime_error("null argument");
+        if (ctx->multi && n >= GROUP_MIN_POINTS_PER_RANK * 8) { multi_bases_upload(ctx, bases, n, g2, from_device, handle); return; }
+        const uint64_t h = ctx->next_pk++;
+        bases_upload_one(ctx, bases, n, g2 != 0, from_device != 0, ctx->device, h);
         *handle = h;
     });
 }
 extern "C" int g16_bases_free(g16_ctx* ctx, uint64_t handle) {
     return guarded(ctx, [&] {
+        if (multi_has_bases(ctx, handle)) { multi_bases_free(ctx, handle); return; }
         auto it = ctx->bases.find(handle);
         if (it == ctx->bases.end()) throw std::runtime_error("unknown bases handle");
         G16_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -562,6 +578,7 @@ extern "C" int g16_bases_free(g16_ctx* ctx, uint64_t handle) {
 }
 extern "C" int g16_msm_resident_dev(g16_ctx* ctx, uint64_t handle, const void* scalars_d, void* out) {
     return guarded(ctx, [&] {
+        if (multi_has_bases(ctx, handle)) { if (!out) throw std::runtime_error("null argument"); multi_msm_resident(ctx, handle, scalars_d, true, out); return; }
         auto it = ctx->bases.find(handle);
         if (it == ctx->bases.end()) throw std::runtime_error("unknown bases handle");
         if (!out || (it->second.n && !scalars_d)) throw std::runtime_error("null argument");
@@ -583,6 +600,7 @@ extern "C" int g16_msm_resident_dev(g16_ctx* ctx, uint64_t handle, const void* s
 extern "C" int g16_msm_resident(g16_ctx* ctx, uint64_t handle, const void* scalars, void* out) {
     // host-scalar form of g16_msm_resident_dev: one staged H2D copy, then the same path
     if (!ctx) return 1;
+    if (multi_has_bases(ctx, handle)) return guarded(ctx, [&] { if (!out) throw std::runtime_error("null argument"); multi_msm_resident(ctx, handle, scalars, false, out); });
     uint64_t n = 0;
     int rc = guarded(ctx, [&] {
         auto it = ctx->bases.find(handle);
@@ -841,6 +859,8 @@ int g16_msm_g2(g16_ctx* ctx, const void* scalars, const void* bases, uint64_t n,
 
 int g16_ntt_dev(g16_ctx* ctx, void* data_d, uint64_t n, int inverse, int coset, int decimation) {
     return guarded(ctx, [&] {
+        // a group context distributes the transform shapes computeH is made of (one exchange); the rest runs on its first GPU
+        if (multi_can_distribute(ctx, n) && n >= GROUP_MIN_POINTS_PER_RANK * 8 && multi_ntt_dev(ctx, data_d, n, inverse, coset, decimation)) return;
         ntt_dev_impl(ctx, (Fr::T*)data_d, n, inverse, coset, decimation);
         G16_CUDA(cudaStreamSynchronize(ctx->stream));
     });
@@ -857,6 +877,7 @@ int g16_ntt(g16_ctx* ctx, void* data, uint64_t n, int inverse, int coset, int de
 int g16_compute_h_dev(g16_ctx* ctx, void* a_d, void* b_d, void* c_d, uint64_t domain_n) {
     return guarded(ctx, [&] {
         if (!is_pow2(domain_n)) throw std::runtime_error("domain_n must be a power of two");
+        if (multi_can_distribute(ctx, domain_n) && domain_n >= GROUP_MIN_POINTS_PER_RANK * 8) { multi_compute_h_dev(ctx, a_d, b_d, c_d, domain_n); return; }
         compute_h_device(ctx->domain(ilog2_ceil(domain_n)), (Fr::T*)a_d, (Fr::T*)b_d, (Fr::T*)c_d, ctx->stream);
         G16_CUDA(cudaStreamSynchronize(ctx->stream));
     });

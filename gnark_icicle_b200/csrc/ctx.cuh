@@ -239,5 +239,15 @@ struct MultiIn {
     uint64_t r1cs = 0;          // non-zero: a, b, c are evaluated on the device from this resident constraint system
 };
 void multi_prove(g16_ctx* ctx, uint64_t pk_handle, const MultiIn& in, void* out_points, g16_stats* stats);
+// group primitives (configs 2 and 3 on N GPUs); arrays named _d live on rank 0's GPU
+bool multi_can_distribute(g16_ctx* ctx, uint64_t n);
+void multi_compute_h_dev(g16_ctx* ctx, void* a_d, void* b_d, void* c_d, uint64_t n);
+bool multi_ntt_dev(g16_ctx* ctx, void* data_d, uint64_t n, int inverse, int coset, int decimation);
+void multi_bases_upload(g16_ctx* ctx, const void* bases, uint64_t n, int g2, int from_device, uint64_t* handle);
+bool multi_has_bases(g16_ctx* ctx, uint64_t handle);
+void multi_bases_free(g16_ctx* ctx, uint64_t handle);
+void multi_msm_resident(g16_ctx* ctx, uint64_t handle, const void* scalars, bool on_device, void* out);
+// api.cu: bases (n points, host memory or -- from_device -- memory of GPU src_device) resident on ctx under `handle`
+void bases_upload_one(g16_ctx* ctx, const void* bases, uint64_t n, bool g2, bool from_device, int src_device, uint64_t handle);
 
 }  // namespace g16

@@ -44,12 +44,15 @@ struct GroupPk {
 
 }  // namespace
 
+struct GroupBases { uint64_t n = 0; bool g2 = false; };
+
 struct MultiGpu {
     int n = 0, g = 0;
     std::vector<RankState> rk;
     Team team;
     HostBarrier bar;
     std::map<uint64_t, GroupPk> pks;
+    std::map<uint64_t, GroupBases> bases;
 };
 
 namespace {
@@ -328,6 +331,42 @@ struct ProveJob {
     uint64_t launches0;
 };
 
+// exchange k of the call in flight: this rank's arrays at `src` go, element by element, to their owners in the other
+// distribution (buffer `target` of every rank); returns once this rank's stream waits for everybody's stores
+void dist_exchange(const ProveJob& J, int r, int k, const Fr::T* src, int target, int count, int to_block) {
+    MultiGpu& mg = *J.mg;
+    RankState& R = mg.rk[r];
+    DistExchange a;
+    for (int p = 0; p < 8; p++) a.dst[p] = p < mg.n ? mg.rk[p].buf[target].as<Fr::T>() : nullptr;
+    a.src = src; a.count = count; a.n_local = J.n_local; a.g = J.g; a.L = J.L; a.rb = J.rb; a.rank = (uint32_t)r; a.to_block = to_block;
+    ntt_dist_exchange(a, R.hs);
+    G16_CUDA(cudaEventRecord(R.ev_x[k], R.hs));
+    if (!mg.bar.wait()) throw std::runtime_error("another rank failed");        // every rank has recorded its event
+    for (int p = 0; p < mg.n; p++) G16_CUDA(cudaStreamWaitEvent(R.hs, mg.rk[p].ev_x[k], 0));
+}
+NttBatch dist_batch(Fr::T* p, int count, uint64_t n_local) { return NttBatch{{p, p + (count > 1 ? n_local : 0), p + (count > 2 ? 2 * n_local : 0)}, count}; }
+
+// a, b, c of this rank in D(rb) in buf[0]  ->  this rank's block of h (bit-reversed order) in buf[1]; on R.hs
+void dist_compute_h(const ProveJob& J, int r) {
+    RankState& R = J.mg->rk[r];
+    cudaStream_t hs = R.hs;
+    NttDomain& dom = R.ctx->domain(J.L);
+    Fr::T* A = R.buf[0].as<Fr::T>();
+    Fr::T* B = R.buf[1].as<Fr::T>();
+    const int g = J.g, X = J.X, rb = J.rb;
+    const uint64_t nl = J.n_local;
+    ntt_dist_stages(dom, dist_batch(A, 3, nl), TW_INV, true, g, (uint32_t)r, true, X, hs, rb);          // 3 x iNTT, upper stages
+    dist_exchange(J, r, 0, A, 1, 3, 1);
+    ntt_dist_stages(dom, dist_batch(B, 3, nl), TW_INV, true, g, (uint32_t)r, false, X, hs);             //           lower stages
+    ntt_dist_stages(dom, dist_batch(B, 3, nl), TW_COSET_FWD, false, g, (uint32_t)r, false, X, hs);      // 3 x coset NTT, lower stages
+    dist_exchange(J, r, 1, B, 0, 3, 0);
+    ntt_dist_stages(dom, dist_batch(A, 3, nl), TW_COSET_FWD, false, g, (uint32_t)r, true, X, hs, rb);   //               upper stages
+    fr_pointwise_h(A, A + nl, A + 2 * nl, nl, dom.h_c1, dom.h_c2, hs);
+    ntt_dist_stages(dom, dist_batch(A, 1, nl), TW_COSET_INV, true, g, (uint32_t)r, true, X, hs, rb);    // coset iNTT, upper stages
+    dist_exchange(J, r, 2, A, 1, 1, 1);
+    ntt_dist_stages(dom, dist_batch(B, 1, nl), TW_COSET_INV, true, g, (uint32_t)r, false, X, hs);       //            lower stages
+}
+
 void rank_prove(const ProveJob& J, int r) {
     MultiGpu& mg = *J.mg;
     RankState& R = mg.rk[r];
@@ -405,28 +444,8 @@ void rank_prove(const ProveJob& J, int r) {
     G16_CUDA(cudaEventRecord(c->ev[27], hs));
 
     // ---- distributed computeH (prove.go:356-399): 3 exchanges
-    NttDomain& dom = c->domain(J.L);
-    auto batch = [&](Fr::T* p, int count) { return NttBatch{{p, p + (count > 1 ? n_local : 0), p + (count > 2 ? 2 * n_local : 0)}, count}; };
-    auto exchange = [&](int k, const Fr::T* src, int target, int count, int to_block) {
-        DistExchange a;
-        for (int p = 0; p < 8; p++) a.dst[p] = p < mg.n ? mg.rk[p].buf[target].as<Fr::T>() : nullptr;
-        a.src = src; a.count = count; a.n_local = n_local; a.g = g; a.L = J.L; a.rb = rb; a.rank = (uint32_t)r; a.to_block = to_block;
-        ntt_dist_exchange(a, hs);
-        G16_CUDA(cudaEventRecord(R.ev_x[k], hs));
-        if (!mg.bar.wait()) throw std::runtime_error("another rank failed");        // every rank has recorded its event
-        for (int p = 0; p < mg.n; p++) G16_CUDA(cudaStreamWaitEvent(hs, mg.rk[p].ev_x[k], 0));
-    };
     G16_CUDA(cudaEventRecord(c->ev[30], hs));
-    ntt_dist_stages(dom, batch(A, 3), TW_INV, true, g, (uint32_t)r, true, X, hs, rb);          // 3 x iNTT, upper stages
-    exchange(0, A, 1, 3, 1);
-    ntt_dist_stages(dom, batch(B, 3), TW_INV, true, g, (uint32_t)r, false, X, hs);             //           lower stages
-    ntt_dist_stages(dom, batch(B, 3), TW_COSET_FWD, false, g, (uint32_t)r, false, X, hs);      // 3 x coset NTT, lower stages
-    exchange(1, B, 0, 3, 0);
-    ntt_dist_stages(dom, batch(A, 3), TW_COSET_FWD, false, g, (uint32_t)r, true, X, hs, rb);   //               upper stages
-    fr_pointwise_h(A, A + n_local, A + 2 * n_local, n_local, dom.h_c1, dom.h_c2, hs);
-    ntt_dist_stages(dom, batch(A, 1), TW_COSET_INV, true, g, (uint32_t)r, true, X, hs, rb);    // coset iNTT, upper stages
-    exchange(2, A, 1, 1, 1);
-    ntt_dist_stages(dom, batch(B, 1), TW_COSET_INV, true, g, (uint32_t)r, false, X, hs);       //            lower stages
+    dist_compute_h(J, r);
     G16_CUDA(cudaEventRecord(R.ev_x[3], hs));   // this rank's block of h (bit-reversed order) is final in buf[1]
     G16_CUDA(cudaEventRecord(c->ev[31], hs));
     // ---- the MSMs over W, on their own streams.  Their sorts (short CTAs) run beside computeH; their accumulations --
@@ -533,6 +552,219 @@ void multi_prove(g16_ctx* ctx, uint64_t pk_handle, const MultiIn& in, void* out_
         stats->ms_host += std::chrono::duration<float, std::milli>(t2 - t1).count();
         stats->kernel_launches = (uint32_t)(launch_counter().load() - J.launches0);
         stats->ms_wall = std::chrono::duration<float, std::milli>(t2 - t0).count();   // wall clock of the group call
+    }
+}
+
+// =================================================================== group primitives (BASELINE configs 2 and 3 on N GPUs)
+namespace {
+
+void launch_pull(const void* a, const void* b, const void* c, Fr::T* dst, int count, const ProveJob& J, int r, cudaStream_t st) {
+    PullArgs pa;
+    pa.src[0] = (const Fr::T*)a; pa.src[1] = (const Fr::T*)b; pa.src[2] = (const Fr::T*)c;
+    pa.dst = dst; pa.n_local = J.n_local; pa.count = count; pa.rb = J.rb; pa.g = J.g; pa.rank = (uint32_t)r;
+    unsigned blocks = (unsigned)(((uint64_t)count * J.n_local + 255) / 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    k_dist_pull<<<blocks, 256, 0, st>>>(pa);
+    G16_LAUNCH_CHECK();
+}
+
+// dst[i(q)] = src[q]: this rank's D(rb) positions back into a whole array on another (or the same) GPU
+__global__ void __launch_bounds__(256) k_dist_push(const Fr::T* __restrict__ src, Fr::T* __restrict__ dst, uint64_t n_local, int rb, int g, uint32_t rank) {
+    const uint64_t rmask = (1ull << rb) - 1;
+    for (uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n_local; q += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t i = ((q >> rb) << (rb + g)) | ((uint64_t)rank << rb) | (q & rmask);
+        const uint4* s = reinterpret_cast<const uint4*>(src + q);
+        uint4* d = reinterpret_cast<uint4*>(dst + i);
+        const uint4 lo = s[0], hi = s[1];
+        d[0] = lo; d[1] = hi;
+    }
+}
+
+ProveJob geometry(MultiGpu& mg, uint64_t n) {
+    ProveJob J;
+    J.mg = &mg; J.handle = 0; J.in = nullptr; J.launches0 = 0;
+    J.n = n; J.L = ilog2_ceil(n); J.g = mg.g; J.X = split_stage(J.L, J.g); J.rb = J.X - J.g;
+    J.n_local = n >> mg.g;
+    return J;
+}
+
+template <class F>
+void run_ranks(g16_ctx* ctx, F&& body) {
+    MultiGpu& mg = *ctx->multi;
+    mg.bar.reset(mg.n);
+    try {
+        mg.team.run([&](int r) {
+            try { set_device(mg.rk[r]); body(r); }
+            catch (...) { mg.bar.fail(); cudaDeviceSynchronize(); cudaGetLastError(); throw; }
+        });
+    } catch (...) {
+        cudaSetDevice(ctx->device);
+        throw;
+    }
+    G16_CUDA(cudaSetDevice(ctx->device));
+}
+
+}  // namespace
+
+bool multi_can_distribute(g16_ctx* ctx, uint64_t n) { return ctx->multi && is_pow2(n) && ilog2_ceil(n) >= 2 * ctx->multi->g + 4; }
+
+// computeH with a_d, b_d, c_d (n elements each) on rank 0's GPU; h (bit-reversed order) is written back into a_d
+void multi_compute_h_dev(g16_ctx* ctx, void* a_d, void* b_d, void* c_d, uint64_t n) {
+    MultiGpu& mg = *ctx->multi;
+    ProveJob J = geometry(mg, n);
+    G16_CUDA(cudaEventRecord(mg.rk[0].ev_in, ctx->stream));
+    run_ranks(ctx, [&](int r) {
+        RankState& R = mg.rk[r];
+        R.buf[0].reserve((size_t)3 * J.n_local * sizeof(Fr::T));
+        R.buf[1].reserve((size_t)3 * J.n_local * sizeof(Fr::T));
+        R.ctx->domain(J.L).table(TW_INV, R.hs); R.ctx->domain(J.L).table(TW_COSET_FWD, R.hs); R.ctx->domain(J.L).table(TW_COSET_INV, R.hs);
+        if (!mg.bar.wait()) throw std::runtime_error("another rank failed");
+        G16_CUDA(cudaStreamWaitEvent(R.hs, mg.rk[0].ev_in, 0));
+        launch_pull(a_d, b_d, c_d, R.buf[0].as<Fr::T>(), 3, J, r, R.hs);
+        G16_CUDA(cudaEventRecord(R.ev_x[3], R.hs));
+        if (!mg.bar.wait()) throw std::runtime_error("another rank failed");
+        for (int p = 0; p < mg.n; p++) G16_CUDA(cudaStreamWaitEvent(R.hs, mg.rk[p].ev_x[3], 0));   // everybody has read a_d before h lands in it
+        dist_compute_h(J, r);
+        G16_CUDA(cudaMemcpyPeerAsync((Fr::T*)a_d + (uint64_t)r * J.n_local, mg.rk[0].ctx->device, R.buf[1].p, R.ctx->device, (size_t)J.n_local * sizeof(Fr::T), R.hs));
+        G16_CUDA(cudaStreamSynchronize(R.hs));
+    });
+}
+
+// one transform of fft.Domain on an array that lives on rank 0's GPU, in place: FFTInverse(DIF) and FFT(DIT), with or
+// without the coset (the shapes computeH is made of); returns false for the shapes that are not distributed
+bool multi_ntt_dev(g16_ctx* ctx, void* data_d, uint64_t n, int inverse, int coset, int decimation) {
+    const bool inv_dif = inverse && decimation == G16_DIF, fwd_dit = !inverse && decimation == G16_DIT;
+    if (!inv_dif && !fwd_dit) return false;
+    MultiGpu& mg = *ctx->multi;
+    ProveJob J = geometry(mg, n);
+    const NttTable tab = inverse ? (coset ? TW_COSET_INV : TW_INV) : (coset ? TW_COSET_FWD : TW_FWD);
+    G16_CUDA(cudaEventRecord(mg.rk[0].ev_in, ctx->stream));
+    run_ranks(ctx, [&](int r) {
+        RankState& R = mg.rk[r];
+        cudaStream_t hs = R.hs;
+        R.buf[0].reserve((size_t)3 * J.n_local * sizeof(Fr::T));
+        R.buf[1].reserve((size_t)3 * J.n_local * sizeof(Fr::T));
+        NttDomain& dom = R.ctx->domain(J.L);
+        dom.table(tab, hs);
+        if (!mg.bar.wait()) throw std::runtime_error("another rank failed");
+        G16_CUDA(cudaStreamWaitEvent(hs, mg.rk[0].ev_in, 0));
+        Fr::T* A = R.buf[0].as<Fr::T>();
+        Fr::T* B = R.buf[1].as<Fr::T>();
+        Fr::T* whole = (Fr::T*)data_d;
+        const int dev0 = mg.rk[0].ctx->device;
+        if (inv_dif) {
+            launch_pull(whole, whole, whole, A, 1, J, r, hs);
+            G16_CUDA(cudaEventRecord(R.ev_x[3], hs));
+            if (!mg.bar.wait()) throw std::runtime_error("another rank failed");
+            for (int p = 0; p < mg.n; p++) G16_CUDA(cudaStreamWaitEvent(hs, mg.rk[p].ev_x[3], 0));   // all reads of the array precede the write-back
+            ntt_dist_stages(dom, dist_batch(A, 1, J.n_local), tab, true, J.g, (uint32_t)r, true, J.X, hs, J.rb);
+            dist_exchange(J, r, 0, A, 1, 1, 1);
+            ntt_dist_stages(dom, dist_batch(B, 1, J.n_local), tab, true, J.g, (uint32_t)r, false, J.X, hs);
+            fr_scale_powers(B, J.n_local, J.L - J.g, dom.n_inv, Fr::one(), 0, 0, hs);
+            G16_CUDA(cudaMemcpyPeerAsync(whole + (uint64_t)r * J.n_local, dev0, B, R.ctx->device, (size_t)J.n_local * sizeof(Fr::T), hs));
+        } else {
+            G16_CUDA(cudaMemcpyPeerAsync(B, R.ctx->device, whole + (uint64_t)r * J.n_local, dev0, (size_t)J.n_local * sizeof(Fr::T), hs));
+            G16_CUDA(cudaEventRecord(R.ev_x[3], hs));
+            if (!mg.bar.wait()) throw std::runtime_error("another rank failed");
+            for (int p = 0; p < mg.n; p++) G16_CUDA(cudaStreamWaitEvent(hs, mg.rk[p].ev_x[3], 0));
+            ntt_dist_stages(dom, dist_batch(B, 1, J.n_local), tab, false, J.g, (uint32_t)r, false, J.X, hs);
+            dist_exchange(J, r, 0, B, 0, 1, 0);
+            ntt_dist_stages(dom, dist_batch(A, 1, J.n_local), tab, false, J.g, (uint32_t)r, true, J.X, hs, J.rb);
+            unsigned blocks = (unsigned)((J.n_local + 255) / 256);
+            if (blocks > 148 * 16) blocks = 148 * 16;
+            k_dist_push<<<blocks, 256, 0, hs>>>(A, whole, J.n_local, J.rb, J.g, (uint32_t)r);
+            G16_LAUNCH_CHECK();
+        }
+        G16_CUDA(cudaStreamSynchronize(hs));
+    });
+    return true;
+}
+
+// resident bases sharded by point range over the ranks (SURVEY.md 8(e) level 2), each slice with its own table
+void multi_bases_upload(g16_ctx* ctx, const void* bases, uint64_t n, int g2, int from_device, uint64_t* handle) {
+    MultiGpu& mg = *ctx->multi;
+    const uint64_t h = ctx->next_pk++;
+    const size_t sz = g2 ? G2SZ : G1SZ;
+    try {
+        run_ranks(ctx, [&](int r) {
+            uint64_t lo, hi;
+            slice(n, (uint32_t)r, (uint32_t)mg.n, lo, hi);
+            bases_upload_one(mg.rk[r].ctx, (const char*)bases + lo * sz, hi - lo, g2 != 0, from_device != 0, mg.rk[0].ctx->device, h);
+        });
+    } catch (...) {
+        for (int r = 0; r < mg.n; r++) {
+            g16_ctx* c = mg.rk[r].ctx;
+            auto it = c->bases.find(h);
+            if (it != c->bases.end()) { cudaSetDevice(c->device); cudaDeviceSynchronize(); it->second.table.release(); c->bases.erase(it); }
+        }
+        cudaSetDevice(ctx->device);
+        throw;
+    }
+    GroupBases gb; gb.n = n; gb.g2 = g2 != 0;
+    mg.bases[h] = gb;
+    *handle = h;
+}
+
+bool multi_has_bases(g16_ctx* ctx, uint64_t handle) { return ctx->multi && ctx->multi->bases.count(handle); }
+
+void multi_bases_free(g16_ctx* ctx, uint64_t handle) {
+    MultiGpu& mg = *ctx->multi;
+    for (int r = 0; r < mg.n; r++) {
+        g16_ctx* c = mg.rk[r].ctx;
+        auto it = c->bases.find(handle);
+        if (it == c->bases.end()) continue;
+        cudaSetDevice(c->device);
+        cudaDeviceSynchronize();
+        it->second.table.release();
+        c->bases.erase(it);
+    }
+    cudaSetDevice(ctx->device);
+    mg.bases.erase(handle);
+}
+
+// scalars: n Fr on rank 0's GPU (on_device) or in host memory; every rank runs the MSM over its slice, the host adds
+void multi_msm_resident(g16_ctx* ctx, uint64_t handle, const void* scalars, bool on_device, void* out) {
+    MultiGpu& mg = *ctx->multi;
+    const GroupBases& gb = mg.bases.at(handle);
+    if (gb.n && !scalars) throw std::runtime_error("null argument");
+    if (on_device) G16_CUDA(cudaEventRecord(mg.rk[0].ev_in, ctx->stream));
+    run_ranks(ctx, [&](int r) {
+        RankState& R = mg.rk[r];
+        g16_ctx* c = R.ctx;
+        const g16_ctx::Bases& b = c->bases.at(handle);
+        uint64_t lo, hi;
+        slice(gb.n, (uint32_t)r, (uint32_t)mg.n, lo, hi);
+        cudaStream_t st = c->stream;
+        const Fr::T* s_ptr = nullptr;
+        if (b.n) {
+            const char* src = (const char*)scalars + lo * 32;
+            if (on_device) G16_CUDA(cudaStreamWaitEvent(st, mg.rk[0].ev_in, 0));
+            if (on_device && c->device == mg.rk[0].ctx->device) s_ptr = (const Fr::T*)src;
+            else {
+                c->stage[3].reserve((size_t)b.n * 32);
+                if (on_device) G16_CUDA(cudaMemcpyPeerAsync(c->stage[3].p, c->device, src, mg.rk[0].ctx->device, (size_t)b.n * 32, st));
+                else h2d_caller(c, c->stage[3].p, src, (size_t)b.n * 32, st, mg.n);
+                s_ptr = c->stage[3].as<Fr::T>();
+            }
+        }
+        const int pre_c = (c->msm_c == 0 && c->msm_precompute) ? b.pre_c : 0;
+        MsmPlan pl;
+        if (gb.g2) {
+            if (b.n) { msm_g2_enqueue(c->ws[4], s_ptr, nullptr, b.table.as<G2::Aff>(), b.n, c->msm_c, c->msm_waves, st, pl, nullptr, nullptr, pre_c); G16_CUDA(cudaStreamSynchronize(st)); }
+            R.part.g2 = b.n ? msm_g2_finish_xyzz(c->ws[4], pl) : G2::inf();
+        } else {
+            if (b.n) { msm_g1_enqueue(c->ws[0], s_ptr, nullptr, b.table.as<G1::Aff>(), b.n, c->msm_c, c->msm_waves, st, pl, nullptr, nullptr, pre_c); G16_CUDA(cudaStreamSynchronize(st)); }
+            R.part.g1[0] = b.n ? msm_g1_finish_xyzz(c->ws[0], pl) : G1::inf();
+        }
+    });
+    if (gb.g2) {
+        G2::Xyzz acc = mg.rk[0].part.g2;
+        for (int r = 1; r < mg.n; r++) G2::add(acc, mg.rk[r].part.g2);
+        copy_out(out, G2::to_aff(acc));
+    } else {
+        G1::Xyzz acc = mg.rk[0].part.g1[0];
+        for (int r = 1; r < mg.n; r++) G1::add(acc, mg.rk[r].part.g1[0]);
+        copy_out(out, G1::to_aff(acc));
     }
 }
 

@@ -152,3 +152,74 @@ def test_prove_surface_over_a_group_and_shard_rejection(case):
     assert grp.raw() == g16.assemble(case.pk, case.want, case.r, case.s).raw()
     with pytest.raises(lib.G16Error, match="needs the whole key"):
         g16.Prove(None, case.pk, sol, g16.WithDevice(0, 0, 2), *opts)
+
+
+# ---------------------------------------------------------------- group primitives (BASELINE configs 2 and 3 on N GPUs)
+FR_TOP_MASK = 0x0FFFFFFFFFFFFFFF
+
+
+def _rand_fr(torch, n, gen):
+    x = torch.randint(-(2 ** 63), 2 ** 63 - 1, (n, 4), dtype=torch.int64, device="cuda:0", generator=gen)
+    x[:, 3] &= FR_TOP_MASK
+    return x
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_group_transforms_and_compute_h_equal_single_gpu(ctx, world):
+    """g16_ntt_dev / g16_compute_h_dev on a group context: one exchange per transform between the D(rb) and the block
+    distribution, arrays on the group's first GPU -- bit-identical to the single-GPU context (itself checked against
+    oracle/c up to 2^26 in test_gpu_large.py)."""
+    import torch
+    logn = 20
+    n = 1 << logn
+    gen = torch.Generator(device="cuda:0")
+    gen.manual_seed(7100 + world)
+    grp = lib.Context(_devices(world))
+    try:
+        x = _rand_fr(torch, n, gen)
+        for kw in (dict(inverse=True, coset=False, decimation=lib.DIF), dict(inverse=True, coset=True, decimation=lib.DIF),
+                   dict(inverse=False, coset=True, decimation=lib.DIT), dict(inverse=False, coset=False, decimation=lib.DIT),
+                   dict(inverse=False, coset=True, decimation=lib.DIF)):      # the last shape is not distributed: first GPU alone
+            a, b = x.clone(), x.clone()
+            torch.cuda.synchronize()
+            ctx.ntt_dev(a.data_ptr(), n, **kw)
+            grp.ntt_dev(b.data_ptr(), n, **kw)
+            torch.cuda.synchronize()
+            assert torch.equal(a, b), kw
+        abc = torch.stack([_rand_fr(torch, n, gen) for _ in range(3)])
+        one, many = abc.clone(), abc.clone()
+        torch.cuda.synchronize()
+        ctx.compute_h_dev(one[0].data_ptr(), one[1].data_ptr(), one[2].data_ptr(), n)
+        grp.compute_h_dev(many[0].data_ptr(), many[1].data_ptr(), many[2].data_ptr(), n)
+        torch.cuda.synchronize()
+        assert torch.equal(one[0], many[0]), "distributed computeH differs from the single-GPU h"
+    finally:
+        grp.close()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_group_resident_msm_equals_trapdoor(ctx, world):
+    """g16_bases_upload on a group context shards the points by range (every slice with its own table of multiples);
+    g16_msm_resident(_dev) adds the ranks' partial sums.  Expected value from the exponent side."""
+    import torch
+    from helpers import g1_gen_arr
+    n = 1 << 19
+    gen = torch.Generator(device="cuda:0")
+    gen.manual_seed(7200 + world)
+    k, s = _rand_fr(torch, n, gen), _rand_fr(torch, n, gen)
+    bases = torch.empty((n, 8), dtype=torch.int64, device="cuda:0")
+    torch.cuda.synchronize()
+    ctx.g1_fixed_base_mul_dev(k.data_ptr(), n, bases.data_ptr())
+    kh, sh = k.cpu().numpy().view(np.uint64), s.cpu().numpy().view(np.uint64)
+    want = ocpu.g1_mul(g1_gen_arr(), ocpu.fr_dot(sh, kh))
+    grp = lib.Context(_devices(world))
+    try:
+        h = grp.bases_upload_dev(bases.data_ptr(), n)
+        assert_limbs_equal(grp.msm_resident_dev(h, s.data_ptr()), want, "group resident MSM, device scalars")
+        assert_limbs_equal(grp.msm_resident(h, sh), want, "group resident MSM, host scalars")
+        grp.bases_free(h)
+        h = grp.bases_upload(bases.cpu().numpy().view(np.uint64))
+        assert_limbs_equal(grp.msm_resident_dev(h, s.data_ptr()), want, "group resident MSM, bases from the host")
+        grp.bases_free(h)
+    finally:
+        grp.close()
