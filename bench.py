@@ -325,6 +325,7 @@ def run_ours(args):
     devices = list(range(world))
     ctx = lib.Context(devices if world > 1 else 0)
     ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
+    ctx.set("msm_ba_rounds", args.ba_rounds)
     nc = 1 << args.log_n
     case = chain_case(nc, g1_mul=ctx.g1_fixed_base_mul, g2_mul=ctx.g2_fixed_base_mul)
     n, nw, pk = case.n, case.nw, case.pk
@@ -410,8 +411,16 @@ def run_ours(args):
     g2_ms = st["ms_accumulate"][4]
     peak = imad * world
     ach = g1_ops / (g1_ms * 1e-3) / 1e12
-    roof = {"bound": "int32-imad", "kernel": "k_accumulate<G1> (4 launches/step)", "achieved": ach, "peak": peak / 1e12,
+    # what the stage EXECUTES since the batch-affine rounds (csrc/msm_ba.cuh): an affine pair addition is 6 multiplications
+    # (3 for the shared inversion), R rounds leave 1/2^R of the entries to the 10-multiplication XYZZ addition
+    ba_r = args.ba_rounds
+    mults_exec = (1 - 0.5 ** ba_r) * 6 + 0.5 ** ba_r * 10 if ba_r > 0 else 10.0
+    roof = {"bound": "int32-imad", "kernel": "bucket accumulation of the four G1 MSMs: k_ba_fwd / k_ba_bwd rounds + k_accumulate<G1>",
+            "achieved": ach, "peak": peak / 1e12,
             "unit": "TIMAD/s", "frac": ach / (peak / 1e12), "traffic": None,
+            "frac_definition": "SURVEY 8(d): entries x 10 Fp mul x 272 IMAD-eq (the reference algorithm's work) / stage time / measured IMAD peak",
+            "mults_per_entry_executed": mults_exec, "frac_executed": ach / (peak / 1e12) * mults_exec / 10.0,
+            "batch_affine_rounds": ba_r,
             "peak_source": "g16_imad_peak microbenchmark, same run (independent mad.lo.u32 chains on all SMs)" + (f" x {world} GPUs" if world > 1 else ""),
             "imad_wide_peak_tops": wide / 1e12, "imad_wide_carry_peak_tops": wide_x / 1e12,
             "field_mul_peak_g_per_s": fp_mul / 1e9, "field_mul_achieved_g_per_s": g1_ops / fp_eq / (g1_ms * 1e-3) / 1e9 / world,
@@ -429,10 +438,6 @@ def run_ours(args):
                    "frac": g1_bytes / (g1_ms * 1e-3) / 1e9 / (pk_["hbm_gbs"] * world), "peak_source": src,
                    "algorithmic_bytes_per_launch_2p22": (1 << 22) * 13 * 68,
                    "note": "the accumulate kernel is bound by the integer multiplier, not HBM: it moves <10 % of the copy bandwidth"}
-    if args.log_n == 22 and world == 1:
-        roof["traffic"] = 4.10e9
-        roof["traffic_source"] = ("profiles/r01d_accumulate_ntt_2p22_ncu_raw.csv: 3.97 GB read + 0.13 GB written per 2^22-point launch "
-                                  "(8.6 ms, 54.5 M entries x 68 B = 3.71 GB algorithmic); before the 64-byte L2 fill hint: 7.45 GB")
     ntt_bytes = 7 * 64 * n
     if st["ms_compute_h"] > 0:
         roof["compute_h"] = {"bound": "hbm", "achieved": ntt_bytes / (st["ms_compute_h"] * 1e-3) / 1e9, "peak": pk_["hbm_gbs"] * world,
@@ -455,12 +460,19 @@ def run_ours(args):
             "placement": {f"gpu{r}": {POINT_NAMES[i]: list(placement[r][i]) for i in range(5) if placement[r][i][1] > placement[r][i][0]} for r in range(world)},
             "stages_ms": {"serialised_total": st["ms_total"], "compute_h": st["ms_compute_h"], "msm": st["ms_msm"], "accumulate": st["ms_accumulate"],
                           "host_epilogue": st["ms_host"], "msm_c": st["msm_c"], "e2e_h2d": st_e["ms_h2d"]}}
-    if world == 1 and not args.no_extras:
-        line["extras"] = extras(torch, ctx, ext, dev, pk_, imad, full=args.sweep)
+    if not args.no_extras:
+        ctx.pk_free(handle)
+        handle = None
+        single = lib.Context(0) if world > 1 else None
+        line["extras"] = extras(torch, ctx, ext, dev, pk_, imad, full=args.sweep, world=world, single=single)
+        bad = [k for k, v in line["extras"].items() if v.get("parity_ok") is False]
+        if bad:
+            raise SystemExit(f"bench.py: sweep entries fail their parity check: {bad}")
     if world == 1 and not args.no_cpu:
         # cpu_baseline: the oracle prover on the SAME instance, once, all host cores (~10-30 s); its five points double as a
         # second, Pippenger-side parity check of the GPU's
-        ctx.pk_free(handle)
+        if handle is not None:
+            ctx.pk_free(handle)
         ms_cpu, pts_cpu, _ = cpu_prove(case, ocpu)
         if not np.array_equal(pts_cpu, pts_dev):
             raise SystemExit("bench.py: the CPU oracle prover and the GPU disagree on the benchmarked instance")
@@ -534,12 +546,22 @@ def run_ours_synthetic(args):
     print(json.dumps(line))
 
 
-def extras(torch, ctx, ext, dev, pk_, imad, full=False):
-    """the other two headline numbers of BASELINE.json's metric: G1 MSM Mpoints/s @ 2^24 and NTT GB/s.
-    full=True (--sweep): the whole 2^16..2^26 sweeps of configs 2 and 3."""
+def extras(torch, ctx, ext, dev, pk_, imad, full=False, world=1, single=None):
+    """the other two headline numbers of BASELINE.json's metric: G1 MSM Mpoints/s @ 2^24 and NTT GB/s (configs 2 and 3).
+    full=True (--sweep): the whole 2^16..2^26 sweeps.  world > 1: `ctx` is a group context -- resident bases are sharded
+    by point range, transforms and computeH run four-step over the GPUs with arrays on the first one (so the numbers
+    include moving them over NVLink) -- and `single` is a one-GPU context used as the bit-for-bit checker.
+    Every entry carries a parity flag: MSMs against the trapdoor identity (oracle/c), transforms by FFT(DIT) o
+    FFTInverse(DIF) = id and (groups) equality with the single-GPU result; the oracle compares at these sizes are in
+    tests/test_gpu_large.py."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oracle import cpu as ocpu
+    from helpers import g1_gen_arr
     out = {}
     gen = torch.Generator(device=dev)
     gen.manual_seed(7)
+    peak = imad * world
+    hbm = pk_["hbm_gbs"] * world
 
     def ev_time(fn, reps=3):
         fn()
@@ -554,47 +576,94 @@ def extras(torch, ctx, ext, dev, pk_, imad, full=False):
             best = min(best, e0.elapsed_time(e1))
         return best
 
-    for logn in (range(16, 27) if full else (20, 22, 24)):
+    host = lambda t: t.cpu().numpy().view(np.uint64)
+    msm_sizes = range(16, 27) if full else ((20, 22, 24) if world == 1 else (24,))
+    for logn in msm_sizes:
         m = 1 << logn
         k = rand_fr_cuda(torch, m, gen, dev)
         bases = torch.empty((m, ctx.g1w), dtype=torch.int64, device=dev)
+        torch.cuda.synchronize()
         ctx.g1_fixed_base_mul_dev(k.data_ptr(), m, bases.data_ptr())
         s = rand_fr_cuda(torch, m, gen, dev)
-        ms = ev_time(lambda: ctx.msm_g1_dev(s.data_ptr(), bases.data_ptr(), m))
-        out[f"msm_g1_2p{logn}"] = {"ms": ms, "mpts_per_s": m / ms / 1e3}
+        want = ocpu.g1_mul(g1_gen_arr(), ocpu.fr_dot(host(s), host(k)))
+        if world == 1:
+            got = ctx.msm_g1_dev(s.data_ptr(), bases.data_ptr(), m)
+            ms = ev_time(lambda: ctx.msm_g1_dev(s.data_ptr(), bases.data_ptr(), m))
+            out[f"msm_g1_2p{logn}"] = {"ms": ms, "mpts_per_s": m / ms / 1e3, "parity_ok": bool(np.array_equal(got, want))}
         # the Groth16 case: bases resident with their precomputed multiples (g16_bases_upload, one-time)
         hb = ctx.bases_upload_dev(bases.data_ptr(), m)
         del bases
+        got = ctx.msm_resident_dev(hb, s.data_ptr())
         ms = ev_time(lambda: ctx.msm_resident_dev(hb, s.data_ptr()))
-        out[f"msm_g1_resident_2p{logn}"] = {"ms": ms, "mpts_per_s": m / ms / 1e3}
+        windows = 255 // 20 + 1
+        out[f"msm_g1_resident_2p{logn}"] = {"ms": ms, "mpts_per_s": m / ms / 1e3, "parity_ok": bool(np.array_equal(got, want)),
+                                            "imad_frac_c20": m * windows * MADD_MULS["g1"] * IMAD_EQ_PER_FP_MUL / (ms * 1e-3) / peak,
+                                            "gpus": world}
         ctx.bases_free(hb)
         del k, s
-    m = 1 << 20
-    k = rand_fr_cuda(torch, m, gen, dev)
-    b2 = torch.empty((m, ctx.g2w), dtype=torch.int64, device=dev)
-    ctx.g2_fixed_base_mul_dev(k.data_ptr(), m, b2.data_ptr())
-    s = rand_fr_cuda(torch, m, gen, dev)
-    ms = ev_time(lambda: ctx.msm_g2_dev(s.data_ptr(), b2.data_ptr(), m))
-    out["msm_g2_2p20"] = {"ms": ms, "mpts_per_s": m / ms / 1e3}
-    del k, b2, s
-    for logn in (range(16, 27) if full else (20, 22, 24, 26)):
+    if world == 1:
+        m = 1 << 20
+        k = rand_fr_cuda(torch, m, gen, dev)
+        b2 = torch.empty((m, ctx.g2w), dtype=torch.int64, device=dev)
+        torch.cuda.synchronize()
+        ctx.g2_fixed_base_mul_dev(k.data_ptr(), m, b2.data_ptr())
+        s = rand_fr_cuda(torch, m, gen, dev)
+        ms = ev_time(lambda: ctx.msm_g2_dev(s.data_ptr(), b2.data_ptr(), m))
+        out["msm_g2_2p20"] = {"ms": ms, "mpts_per_s": m / ms / 1e3}
+        del k, b2, s
+    ntt_sizes = range(16, 27) if full else ((20, 22, 24, 26) if world == 1 else (24, 26))
+    for logn in ntt_sizes:
         m = 1 << logn
         x = rand_fr_cuda(torch, m, gen, dev)
+        shapes = (("ntt_coset_dit", dict(inverse=False, coset=True, decimation=1)),)
         if full:
-            for name, kw in (("ntt_fwd_dit", dict(inverse=False, coset=False, decimation=1)),
-                             ("intt_dif", dict(inverse=True, coset=False, decimation=0)),
-                             ("intt_coset_dif", dict(inverse=True, coset=True, decimation=0))):
-                ms = ev_time(lambda: ctx.ntt_dev(x.data_ptr(), m, **kw))
-                out[f"{name}_2p{logn}"] = {"ms": ms, "gb_per_s": 64.0 * m / (ms * 1e-3) / 1e9}
-            abc = [rand_fr_cuda(torch, m, gen, dev) for _ in range(3)]
-            ms = ev_time(lambda: ctx.compute_h_dev(abc[0].data_ptr(), abc[1].data_ptr(), abc[2].data_ptr(), m))
-            out[f"compute_h_2p{logn}"] = {"ms": ms, "gb_per_s": 448.0 * m / (ms * 1e-3) / 1e9}
-            del abc
-        ms = ev_time(lambda: ctx.ntt_dev(x.data_ptr(), m, inverse=False, coset=True, decimation=1))
-        gbs = 64.0 * m / (ms * 1e-3) / 1e9
-        muls = (m // 2) * logn
-        out[f"ntt_coset_dit_2p{logn}"] = {"ms": ms, "gb_per_s": gbs, "hbm_frac": gbs / pk_["hbm_gbs"],
-                                         "imad_frac": muls * IMAD_EQ_PER_FP_MUL / (ms * 1e-3) / imad}
+            shapes += (("ntt_fwd_dit", dict(inverse=False, coset=False, decimation=1)), ("intt_dif", dict(inverse=True, coset=False, decimation=0)),
+                       ("intt_coset_dif", dict(inverse=True, coset=True, decimation=0)))
+        for name, kw in shapes:
+            ms = ev_time(lambda: ctx.ntt_dev(x.data_ptr(), m, **kw))
+            gbs = 64.0 * m / (ms * 1e-3) / 1e9
+            out[f"{name}_2p{logn}"] = {"ms": ms, "gb_per_s": gbs, "hbm_frac": gbs / hbm, "gpus": world,
+                                       "imad_frac": (m // 2) * logn * IMAD_EQ_PER_FP_MUL / (ms * 1e-3) / peak}
+        # parity: FFT(DIT) o FFTInverse(DIF) = id (different twiddle tables), and a group against the single-GPU transform
+        y = x.clone()
+        torch.cuda.synchronize()
+        ctx.ntt_dev(y.data_ptr(), m, inverse=True, coset=False, decimation=0)
+        if single is not None:
+            z = x.clone()
+            torch.cuda.synchronize()
+            single.ntt_dev(z.data_ptr(), m, inverse=True, coset=False, decimation=0)
+            torch.cuda.synchronize()
+            same = bool(torch.equal(y, z))
+            del z
+        else:
+            same = None
+        ctx.ntt_dev(y.data_ptr(), m, inverse=False, coset=False, decimation=1)
+        torch.cuda.synchronize()
+        out[f"ntt_coset_dit_2p{logn}"]["parity_ok"] = bool(torch.equal(x, y)) and same is not False
+        out[f"ntt_coset_dit_2p{logn}"]["parity"] = "round trip" + (", equals the single-GPU transform" if same else "")
+        del y
+        if full or world > 1 or logn in (22, 24):
+            abc = torch.stack([x, rand_fr_cuda(torch, m, gen, dev), rand_fr_cuda(torch, m, gen, dev)])
+            work = abc.clone()
+            torch.cuda.synchronize()
+
+            def ch():
+                ctx.compute_h_dev(work[0].data_ptr(), work[1].data_ptr(), work[2].data_ptr(), m)
+            ms = ev_time(ch)                      # (the inputs are whatever the previous run left: timing only)
+            ent = {"ms": ms, "gb_per_s": 448.0 * m / (ms * 1e-3) / 1e9, "hbm_frac": 448.0 * m / (ms * 1e-3) / 1e9 / hbm, "gpus": world,
+                   "imad_frac": 7 * (m // 2) * logn * IMAD_EQ_PER_FP_MUL / (ms * 1e-3) / peak}
+            if single is not None:
+                work.copy_(abc)
+                ref = abc.clone()
+                torch.cuda.synchronize()
+                ch()
+                single.compute_h_dev(ref[0].data_ptr(), ref[1].data_ptr(), ref[2].data_ptr(), m)
+                torch.cuda.synchronize()
+                ent["parity_ok"] = bool(torch.equal(work[0], ref[0]))
+                ent["parity"] = "equals the single-GPU computeH bit for bit"
+                del ref
+            out[f"compute_h_2p{logn}"] = ent
+            del abc, work
         del x
     return out
 
@@ -608,6 +677,7 @@ def main():
     ap.add_argument("--log-n", type=int, default=22, help="log2 of the constraint count (BASELINE: 22)")
     ap.add_argument("--cpu-budget-s", type=float, default=150.0, help="--impl reference: stop timing further proves once the timed region exceeds this")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg of the GPU arm")
+    ap.add_argument("--ba-rounds", type=int, default=4, help="batch-affine rounds of the MSMs (library default 4; 0 = XYZZ accumulation only)")
     ap.add_argument("--curve", default="bn254", choices=["bn254", "bls12_377"],
                     help="bls12_377 = BASELINE config 5 (use --log-n 24); the default line is the BN254 headline")
     ap.add_argument("--no-extras", action="store_true")

@@ -175,6 +175,9 @@ int g16_ctx_set(g16_ctx* ctx, const char* key, int64_t value) {
     else if (k == "dist_sync") ctx->dist_sync = (int)value;
     else if (k == "g2_weight") ctx->g2_weight = (int)value;
     else if (k == "stage_threads") ctx->stage_threads = (int)value;
+    else if (k == "msm_ba_rounds") { for (auto& w : ctx->ws) w.ba_rounds = (int)value; }
+    else if (k == "msm_ba_rounds_g1") { for (int i = 0; i < 4; i++) ctx->ws[i].ba_rounds = (int)value; }
+    else if (k == "msm_ba_rounds_g2") ctx->ws[4].ba_rounds = (int)value;
     else { ctx->err = "unknown tunable " + k; return 1; }
     if (ctx->multi) multi_set(ctx->multi, key, value);
     return 0;

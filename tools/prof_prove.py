@@ -20,6 +20,8 @@ ap.add_argument("--log-n", type=int, default=22)
 ap.add_argument("--proves", type=int, default=2)
 ap.add_argument("--streams", type=int, default=1)
 ap.add_argument("--curve", default="bn254")
+ap.add_argument("--ba", type=int, default=-1, help="msm_ba_rounds_g1 (-1: library default)")
+ap.add_argument("--ba2", type=int, default=-1, help="msm_ba_rounds_g2 (-1: library default)")
 args = ap.parse_args()
 dev = torch.device("cuda:0")
 ctx = lib.Context(0, curve=args.curve)
@@ -28,6 +30,10 @@ key, sd, sh, n, nw = bench.build_inputs(torch, ctx, nc, dev)
 h = ctx.pk_upload(key["domain_n"], key["g1_a"], key["g1_b"], key["g1_k"], key["g1_z"], key["g2_b"], key["inf_a"], key["inf_b"], nw)
 del key
 ctx.set("streams", args.streams)
+if args.ba >= 0:
+    ctx.set("msm_ba_rounds_g1", args.ba)
+if args.ba2 >= 0:
+    ctx.set("msm_ba_rounds_g2", args.ba2)
 work = [torch.empty_like(sd[k]) for k in ("a", "b", "c")]
 for it in range(args.proves):
     for w, k in zip(work, ("a", "b", "c")):
