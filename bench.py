@@ -445,7 +445,7 @@ def run_ours(args):
                              "peak_source": src, "ms": st["ms_compute_h"],
                              "note": "7 transforms x 64n B algorithmic; the butterflies are IMAD-bound at 254 bits"
                                      + ("; distributed: slowest rank, exchanges and their waits included" if world > 1 else "")}
-    par = "1 GPU" if world == 1 else (f"{world} GPUs behind one g16 context: key placed on a cost line (G2 point = 3.4 G1 points), computeH split at one "
+    par = "1 GPU" if world == 1 else (f"{world} GPUs behind one g16 context: key placed on a cost line (G2 point = 3 G1 points), computeH split at one "
                                       "stage with 3 peer-store exchanges over NVLink, partial points summed on the host")
     line = {"metric": "groth16_bn254_prove_ms", "value": ms_dev, "unit": "ms", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_dev, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,

@@ -136,7 +136,7 @@ struct g16_ctx {
     int dist_sync = 1;           // g16_dist_*_dev return after the stream has drained (0: stream-ordered, caller synchronises)
     int msm_precompute = 1;      // keep 2^(c j) multiples of every key base resident (one shared bucket set, larger windows)
     int msm_pre_c = 0;           // window bits of the tables built by the next uploads (0 = chosen from the array size)
-    int g2_weight = 340;         // multi-GPU placement: cost of a G2 point in hundredths of a G1 point
+    int g2_weight = 0;           // multi-GPU placement: cost of a G2 point in hundredths of a G1 point (0 = by group size)
     int stage_threads = 0;       // copier threads for pageable caller memory (0 = from the core count)
     g16::HostStager stager;
     g16::MultiGpu* multi = nullptr;   // non-null on a context created over several devices (this context is rank 0)

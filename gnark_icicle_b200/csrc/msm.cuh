@@ -869,12 +869,18 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
         ws.sort_n = n; ws.sort_c = pl.c; ws.sort_pre = pl.pre;
         G16_CUDA(cudaEventRecord(ws.sort_done, st));
     }
-    if (acc_gate) G16_CUDA(cudaStreamWaitEvent(st, acc_gate, 0));
-    if (stats && stats->acc_begin) G16_CUDA(cudaEventRecord(stats->acc_begin, st));
     // ---- batch-affine rounds: every round halves the entries of every bucket with 6M instead of 10M per addition
     const typename C::Aff* acc_bases = bases_d;
     uint32_t acc_total_max = total_max;
-    const int ba_rounds = (ws.ba_rounds > 0 && !ws.ba_no_memory && n >= (1u << 17)) ? (ws.ba_rounds > 6 ? 6 : ws.ba_rounds) : 0;
+    // every round pays a fixed inversion-tree latency (~0.4-0.6 ms, one Fermat chain): small MSMs -- the pieces of a
+    // multi-GPU prove, which have little else running beside them -- get fewer rounds
+    int ba_rounds = (ws.ba_rounds > 0 && !ws.ba_no_memory && n >= (1u << 17)) ? (ws.ba_rounds > 6 ? 6 : ws.ba_rounds) : 0;
+    if (ba_rounds > 3 && total_max < (32u << 20)) ba_rounds = 3;
+    if (ba_rounds > 2 && total_max < (6u << 20)) ba_rounds = 2;
+    // the gate exists for the long-lived CTAs of a direct XYZZ accumulation (~180 entries per thread); the kernels of the
+    // batch-affine rounds are short-lived, and after >= 3 rounds so is the accumulation that follows them
+    if (acc_gate && ba_rounds < 3) G16_CUDA(cudaStreamWaitEvent(st, acc_gate, 0));
+    if (stats && stats->acc_begin) G16_CUDA(cudaEventRecord(stats->acc_begin, st));
     if (ba_rounds) {
         // the same groups over the lazily reduced fields (values in [0, 2p) between multiplications; G1 with the
         // multiplications inlined): identical memory layout, canonical values in memory

@@ -5,9 +5,10 @@
 // distributed computeH are stores into peer memory over NVLink / NVSwitch issued by the kernel that changes the layout
 // (ntt.cu k_dist_exchange), ordered by CUDA events across the devices.
 //
-//  * key placement (SURVEY.md 8(e) levels 1 + 2): the five MSMs are laid end to end on a cost line (a G2 point costs
-//    g2_weight/100 G1 points) and the line is cut into n equal parts, so every GPU holds at most two or three LARGE
-//    pieces (G2.B alone fills ~3 of 8 GPUs) instead of 1/n of all five: larger windows, fewer sort heads and tails;
+//  * key placement (SURVEY.md 8(e) levels 1 + 2): the four MSMs over W are laid end to end on a cost line (a G2 point
+//    costs g2_weight/100 G1 points) and the line is cut into n equal parts, so every GPU holds one or two LARGE pieces
+//    (G2.B alone fills ~3 of 8 GPUs) instead of 1/n of all four: larger windows, fewer sort heads and tails; G1.Z is cut
+//    by the block distribution of h, so every GPU multiplies the block of h that computeH leaves on it, last;
 //  * computeH (level 3): every size-N transform is "local stages - exchange - local stages" between the distribution
 //    D(rb) (rank = position bits [rb, rb+g)) and the block distribution; a, b, c are loaded from the host straight into
 //    D(rb) (strided copies of 2^rb x 32 B), h leaves block-distributed in bit-reversed order and the GPUs that hold a
@@ -33,6 +34,8 @@ struct RankState {
     DevBuf hbuf;                     // the range of h under this rank's G1.Z slice when other ranks own (part of) it
     cudaEvent_t ev_x[4] = {};        // [k]: this rank's exchange k has landed everywhere; [3]: its block of h is final
     cudaEvent_t ev_in = nullptr;     // rank 0: the caller's device-resident inputs are ready
+    cudaEvent_t ev_w = nullptr;      // this rank's 1/n slice of the wire vector is on its GPU
+    cudaEvent_t mark[12] = {};       // G16_TIMELINE: phases of the distributed computeH on hs
     ProvePartial part;
     g16_stats st;
 };
@@ -107,11 +110,15 @@ void load_host_rows(g16_ctx* c, int world, Fr::T* dst, const void* src, uint64_t
         G16_CUDA(cudaMemcpyAsync(dst + full * row, s + start(full) * 32, (size_t)(n_constraints - start(full)) * 32, cudaMemcpyHostToDevice, st));
 }
 
-// cut the cost line [BS2 | AR | KRS_K | BS1 | KRS_HZ] into `parts` equal pieces
-std::vector<PkRanges> place_key(const uint64_t lens[5], int parts, double g2_weight) {
-    const int order[5] = {G16_OUT_BS2, G16_OUT_AR, G16_OUT_KRS_K, G16_OUT_BS1, G16_OUT_KRS_HZ};
-    double w[5], begin[5], total = 0;
-    for (int k = 0; k < 5; k++) {
+// Placement of the key over `parts` GPUs.  The four MSMs over W are laid end to end on a cost line [BS2 | AR | KRS_K | BS1]
+// (a G2 point costs g2_weight G1 points) and the line is cut into equal parts: every GPU gets one or two LARGE pieces.
+// G1.Z is cut by the block distribution of h instead: every GPU multiplies its own block of h, which computeH leaves in
+// place, and does so last -- the W pieces keep it busy until h exists (with Z on the cost line the GPUs that held only Z
+// sat idle for the whole of computeH: 3.7 of 13.5 ms at N = 8).
+std::vector<PkRanges> place_key(const uint64_t lens[5], int parts, double g2_weight, uint64_t domain_n) {
+    const int order[4] = {G16_OUT_BS2, G16_OUT_AR, G16_OUT_KRS_K, G16_OUT_BS1};
+    double w[5] = {1, 1, 1, 1, 1}, begin[5] = {0, 0, 0, 0, 0}, total = 0;
+    for (int k = 0; k < 4; k++) {
         const int i = order[k];
         w[i] = i == G16_OUT_BS2 ? g2_weight : 1.0;
         begin[i] = total;
@@ -128,8 +135,14 @@ std::vector<PkRanges> place_key(const uint64_t lens[5], int parts, double g2_wei
         return p > lens[i] ? lens[i] : p;
     };
     std::vector<PkRanges> out(parts);
-    for (int r = 0; r < parts; r++)
-        for (int i = 0; i < 5; i++) { out[r].lo[i] = cut(r, i); out[r].hi[i] = cut(r + 1, i); }
+    const uint64_t nz = lens[G16_OUT_KRS_HZ];
+    for (int r = 0; r < parts; r++) {
+        for (int k = 0; k < 4; k++) { const int i = order[k]; out[r].lo[i] = cut(r, i); out[r].hi[i] = cut(r + 1, i); }
+        uint64_t lo, hi;
+        slice(domain_n, (uint32_t)r, (uint32_t)parts, lo, hi);
+        out[r].lo[G16_OUT_KRS_HZ] = lo > nz ? nz : lo;
+        out[r].hi[G16_OUT_KRS_HZ] = hi > nz ? nz : hi;
+    }
     return out;
 }
 
@@ -184,6 +197,8 @@ MultiGpu* multi_create(g16_ctx* rank0, const int* device_ids, int n_devices) {
             G16_CUDA(cudaStreamCreateWithPriority(&R.hs, cudaStreamNonBlocking, prio_hi));
             for (auto& e : R.ev_x) G16_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
             G16_CUDA(cudaEventCreateWithFlags(&R.ev_in, cudaEventDisableTiming));
+            G16_CUDA(cudaEventCreateWithFlags(&R.ev_w, cudaEventDisableTiming));
+            for (auto& e : R.mark) G16_CUDA(cudaEventCreate(&e));
         }
         G16_CUDA(cudaSetDevice(rank0->device));
     } catch (...) {
@@ -206,6 +221,8 @@ void multi_destroy(MultiGpu* mg) {
         R.buf[0].release(); R.buf[1].release(); R.hbuf.release();
         for (auto& e : R.ev_x) if (e) cudaEventDestroy(e);
         if (R.ev_in) cudaEventDestroy(R.ev_in);
+        if (R.ev_w) cudaEventDestroy(R.ev_w);
+        for (auto& e : R.mark) if (e) cudaEventDestroy(e);
         if (R.hs) cudaStreamDestroy(R.hs);
         if (r > 0) ctx_destroy_single(R.ctx);   // rank 0 belongs to the caller (g16_ctx_destroy)
     }
@@ -238,7 +255,10 @@ void multi_pk_upload(g16_ctx* ctx, const g16_pk_desc* d, const Src* src, uint64_
     const int L = ilog2_ceil(d->domain_n);
     gp.active = L >= 2 * mg.g + 4 ? mg.n : 1;   // every rank needs a few stages on either side of the exchanges
     const uint64_t lens[5] = {d->n_a, d->n_b, d->n_k, d->n_z < d->domain_n ? d->n_z : d->domain_n - 1, d->n_b2};
-    std::vector<PkRanges> place = place_key(lens, gp.active, ctx->g2_weight / 100.0);
+    // cost of a G2 point in G1 points: "g2_weight" if set, else by group size -- the smaller the pieces, the more a G2 piece
+    // pays for its smaller window and its exposed bucket reduction (measured per piece at N = 2 / 4 / 8: ~3.0 / 3.4 / 4.0)
+    const double w2 = ctx->g2_weight > 0 ? ctx->g2_weight / 100.0 : (gp.active >= 8 ? 4.0 : gp.active >= 4 ? 3.4 : 3.0);
+    std::vector<PkRanges> place = place_key(lens, gp.active, w2, d->domain_n);
     PkRanges none;
     for (int i = 0; i < 5; i++) none.lo[i] = none.hi[i] = 0;
     const uint64_t h = ctx->next_pk++;
@@ -358,16 +378,25 @@ void dist_compute_h(const ProveJob& J, int r) {
     Fr::T* B = R.buf[1].as<Fr::T>();
     const int g = J.g, X = J.X, rb = J.rb;
     const uint64_t nl = J.n_local;
+    auto mark = [&](int i) { G16_CUDA(cudaEventRecord(R.mark[i], hs)); };
+    mark(0);
     ntt_dist_stages(dom, dist_batch(A, 3, nl), TW_INV, true, g, (uint32_t)r, true, X, hs, rb);          // 3 x iNTT, upper stages
+    mark(1);
     dist_exchange(J, r, 0, A, 1, 3, 1);
+    mark(2);
     ntt_dist_stages(dom, dist_batch(B, 3, nl), TW_INV, true, g, (uint32_t)r, false, X, hs);             //           lower stages
     ntt_dist_stages(dom, dist_batch(B, 3, nl), TW_COSET_FWD, false, g, (uint32_t)r, false, X, hs);      // 3 x coset NTT, lower stages
+    mark(3);
     dist_exchange(J, r, 1, B, 0, 3, 0);
+    mark(4);
     ntt_dist_stages(dom, dist_batch(A, 3, nl), TW_COSET_FWD, false, g, (uint32_t)r, true, X, hs, rb);   //               upper stages
     fr_pointwise_h(A, A + nl, A + 2 * nl, nl, dom.h_c1, dom.h_c2, hs);
     ntt_dist_stages(dom, dist_batch(A, 1, nl), TW_COSET_INV, true, g, (uint32_t)r, true, X, hs, rb);    // coset iNTT, upper stages
+    mark(5);
     dist_exchange(J, r, 2, A, 1, 1, 1);
+    mark(6);
     ntt_dist_stages(dom, dist_batch(B, 1, nl), TW_COSET_INV, true, g, (uint32_t)r, false, X, hs);       //            lower stages
+    mark(7);
 }
 
 void rank_prove(const ProveJob& J, int r) {
@@ -385,6 +414,7 @@ void rank_prove(const ProveJob& J, int r) {
     // buffers exist before anybody stores into them
     R.buf[0].reserve((size_t)3 * n_local * sizeof(Fr::T));
     R.buf[1].reserve((size_t)3 * n_local * sizeof(Fr::T));
+    c->stage[3].reserve((size_t)pk.n_wires * 32);
     const R1csDev* rdev = nullptr;
     if (in.r1cs) {
         auto ir = c->r1cs.find(in.r1cs);
@@ -399,24 +429,37 @@ void rank_prove(const ProveJob& J, int r) {
         G16_CUDA(cudaStreamWaitEvent(st, mg.rk[0].ev_in, 0));
         G16_CUDA(cudaStreamWaitEvent(hs, mg.rk[0].ev_in, 0));
     }
-    // ---- W: the wires this rank's slices of A, B, K read (all of them when a, b, c are evaluated here)
+    // ---- W.  A rank's pieces of A, B, K read wires from all over the vector (the placement cuts every array on its own), so
+    // the ranks together would pull several copies of W through the host's memory system (measured at N = 8: 3.8 - 5.6 ms
+    // until W was resident).  Instead every rank uploads ONE n-th of W and fetches the other slices it needs from its peers
+    // over NVLink: the host serves W exactly once, in n parallel streams.
     const uint64_t w_lo = rdev ? 0 : pk.w_lo, w_hi = rdev ? pk.n_wires : pk.w_hi;
-    const size_t w_bytes = (size_t)(w_hi - w_lo) * 32;
-    const Fr::T* W_ptr;
     const int dev0 = mg.rk[0].ctx->device;
-    if (in.device && c->device == dev0) {
-        W_ptr = (const Fr::T*)in.W;
-    } else {
-        c->stage[3].reserve((size_t)pk.n_wires * 32);
-        char* dst = (char*)c->stage[3].p + (size_t)w_lo * 32;
-        const char* srcp = (const char*)in.W + (size_t)w_lo * 32;
-        if (w_bytes) {
-            if (in.device) G16_CUDA(cudaMemcpyPeerAsync(dst, c->device, srcp, dev0, w_bytes, st));
-            else h2d_caller(c, dst, srcp, w_bytes, st, mg.n);
+    c->stage[3].reserve((size_t)pk.n_wires * 32);
+    {
+        uint64_t s_lo, s_hi;
+        slice(pk.n_wires, (uint32_t)r, (uint32_t)mg.n, s_lo, s_hi);
+        char* dst = (char*)c->stage[3].p + (size_t)s_lo * 32;
+        const char* srcp = (const char*)in.W + (size_t)s_lo * 32;
+        const size_t bytes = (size_t)(s_hi - s_lo) * 32;
+        if (bytes) {
+            if (in.device) G16_CUDA(cudaMemcpyPeerAsync(dst, c->device, srcp, dev0, bytes, st));
+            else { h2d_caller(c, dst, srcp, bytes, st, mg.n); R.st.h2d_bytes += bytes; }
         }
-        W_ptr = c->stage[3].as<Fr::T>();
-        R.st.h2d_bytes += in.device ? 0 : w_bytes;
+        G16_CUDA(cudaEventRecord(R.ev_w, st));
     }
+    if (!mg.bar.wait()) throw std::runtime_error("another rank failed");      // every rank has recorded its slice event
+    for (int p = 0; p < mg.n; p++) {
+        if (p == r) continue;
+        uint64_t s_lo, s_hi;
+        slice(pk.n_wires, (uint32_t)p, (uint32_t)mg.n, s_lo, s_hi);
+        const uint64_t lo = s_lo > w_lo ? s_lo : w_lo, hi = s_hi < w_hi ? s_hi : w_hi;
+        if (hi <= lo) continue;
+        G16_CUDA(cudaStreamWaitEvent(st, mg.rk[p].ev_w, 0));
+        G16_CUDA(cudaMemcpyPeerAsync((char*)c->stage[3].p + (size_t)lo * 32, c->device, (const char*)mg.rk[p].ctx->stage[3].p + (size_t)lo * 32,
+                                     mg.rk[p].ctx->device, (size_t)(hi - lo) * 32, st));
+    }
+    const Fr::T* W_ptr = c->stage[3].as<Fr::T>();
     G16_CUDA(cudaEventRecord(c->ev[15], st));
 
     // ---- a, b, c of this rank in D(rb)
@@ -482,6 +525,16 @@ void rank_prove(const ProveJob& J, int r) {
     G16_CUDA(cudaStreamSynchronize(hs));
     G16_CUDA(cudaEventElapsedTime(&R.st.ms_compute_h, c->ev[30], c->ev[31]));
     G16_CUDA(cudaEventElapsedTime(&R.st.ms_total, c->ev[26], c->ev[14]));
+    static const bool timeline = getenv("G16_TIMELINE") != nullptr;   // diagnostic: where this rank's share of computeH goes
+    if (timeline) {
+        float m[8], w = 0, e0 = 0;
+        for (int i = 0; i < 8; i++) cudaEventElapsedTime(&m[i], c->ev[26], R.mark[i]);
+        cudaEventElapsedTime(&w, c->ev[26], c->ev[15]);
+        cudaEventElapsedTime(&e0, c->ev[26], c->ev[0]);
+        fprintf(stderr, "[g16 timeline] rank %d: W ready %.2f | computeH: load done %.2f, iNTT-upper %.2f, xchg0 %.2f, lower+coset-lower %.2f, xchg1 %.2f, "
+                        "upper+pointwise+upper %.2f, xchg2 %.2f, lower %.2f | MSM enqueue at %.2f | end %.2f\n",
+                r, w, m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[7], e0, R.st.ms_total);
+    }
 }
 
 }  // namespace
