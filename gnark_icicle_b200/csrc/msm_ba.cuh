@@ -44,6 +44,19 @@ __device__ __forceinline__ typename C::E ba_load_e(const typename C::E* p) {
     for (int i = 0; i < Q; i++) d[i] = s[i];
     return r;
 }
+// the same through the read-only path with a 64-byte L2 fill: for the random gathers of round 0 (ncu, 2^22-point G1 MSM:
+// 7.06 GB read by k_ba_fwd for 54.5 M 32-byte coordinates -- every access filled a 128-byte line)
+template <class C>
+__device__ __forceinline__ typename C::E ba_gather_e(const typename C::E* p) {
+    typename C::E r;
+    constexpr int Q = sizeof(typename C::E) / 16;
+    const uint4* s = reinterpret_cast<const uint4*>(p);
+    uint4* d = reinterpret_cast<uint4*>(&r);
+#pragma unroll
+    for (int i = 0; i < Q; i++)
+        asm volatile("ld.global.nc.L2::64B.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(d[i].x), "=r"(d[i].y), "=r"(d[i].z), "=r"(d[i].w) : "l"(s + i));
+    return r;
+}
 template <class C>
 __device__ __forceinline__ void ba_store_e(typename C::E* p, const typename C::E& v) {
     constexpr int Q = sizeof(typename C::E) / 16;
@@ -101,7 +114,7 @@ __device__ __forceinline__ int ba_classify_x(const BaSrc<C>& src, uint32_t i0, t
     uint32_t n1, n2;
     const typename C::Aff* a1 = src.addr(i0, n1);
     const typename C::Aff* a2 = src.addr(i0 + 1, n2);
-    const E x1 = ba_load_e<C>(&a1->x), x2 = ba_load_e<C>(&a2->x);
+    const E x1 = src.sorted ? ba_gather_e<C>(&a1->x) : ba_load_e<C>(&a1->x), x2 = src.sorted ? ba_gather_e<C>(&a2->x) : ba_load_e<C>(&a2->x);
     if (BF::is_zero(x1) || BF::is_zero(x2) || BF::eq(x1, x2)) {
         typename C::Aff p1, p2;
         p1.x = x1; p1.y = ba_load_e<C>(&a1->y); if (n1) p1 = C::neg(p1);
