@@ -425,11 +425,22 @@ def run_ours(args):
             "imad_wide_peak_tops": wide / 1e12, "imad_wide_carry_peak_tops": wide_x / 1e12,
             "field_mul_peak_g_per_s": fp_mul / 1e9, "field_mul_achieved_g_per_s": g1_ops / fp_eq / (g1_ms * 1e-3) / 1e9 / world,
             "frac_of_multiplier_ceiling": g1_ops / fp_eq / (g1_ms * 1e-3) / fp_mul / world,
-            "g2": {"kernel": "k_accumulate<G2>", "achieved": g2_ops / (g2_ms * 1e-3) / 1e12,
-                   "frac": g2_ops / (g2_ms * 1e-3) / peak},
+            "g2": {"kernel": "bucket accumulation of the G2 MSM: k_ba_fwd / k_ba_bwd rounds + k_accumulate<G2>",
+                   "achieved": g2_ops / (g2_ms * 1e-3) / 1e12, "frac": g2_ops / (g2_ms * 1e-3) / peak,
+                   "frac_definition": "entries x 30 Fp mul x 272 IMAD-eq / stage time / measured IMAD peak (SURVEY 8(d))",
+                   "mults_per_entry_executed": ((1 - 0.5 ** ba_r) * 14 + 0.5 ** ba_r * 28) if ba_r > 0 else 28.0,
+                   "frac_executed": g2_ops / (g2_ms * 1e-3) / peak * (((1 - 0.5 ** ba_r) * 14 + 0.5 ** ba_r * 28) if ba_r > 0 else 28.0) / 30.0},
             "share_of_step": (g1_ms + g2_ms) / st["ms_total"],
-            "note": "kernel times from one extra step with the five MSMs serialised (streams=1); the timed steps overlap them"
+            "note": "stage times from one extra step with the five MSMs serialised (streams=1); the timed steps overlap them, which is "
+                    "where the batch-affine rounds pay: their gathers and inversion trees hide under other MSMs' multiplications "
+                    "(serialised sum 69 ms, overlapped step 58 ms)"
                     + ("; on a group: slowest rank's time per MSM against the whole job's work" if world > 1 else "")}
+    if args.log_n == 22 and world == 1 and ba_r == 4:
+        roof["traffic"] = 20.8e9
+        roof["traffic_source"] = ("profiles/r02_ba_accumulate_2p22_ncu_raw.csv (ncu --set full): dram__bytes_read + write summed over the nine kernels "
+                                  "of one 2^22-point G1 accumulation stage (4 k_ba_fwd + 4 k_ba_bwd + k_accumulate): 19.1 GB read + 5.2 GB written "
+                                  "before the 64-byte fill hint in k_ba_fwd (-3.5 GB), against 3.71 GB for the direct XYZZ kernel of round 1 "
+                                  "(54.5 M entries x 68 B): the rounds trade multiplications for memory traffic")
     pk_, src = peaks()
     # HBM view of the same kernel: 64 B affine point + 4 B sorted index per bucket entry; `traffic` is
     # dram__bytes_read+write per launch of the 2^22-point launch from the ncu --set full capture in profiles/
@@ -493,6 +504,11 @@ def run_ours_synthetic(args):
     ranks = Ranks.__new__(Ranks)
     ranks.torch, ranks.rank, ranks.world, ranks.local, ranks.dist = torch, 0, 1, 0, None
     ctx = lib.Context(0, curve=args.curve)
+    ctx.set("msm_ba_rounds", args.ba_rounds)
+    if args.no_tables:
+        ctx.set("msm_precompute", 0)
+    if args.no_g1_tables:
+        ctx.set("msm_precompute_g1", 0)
     fp_eq = IMAD_EQ_PER_FP_MUL_12
     ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
     nc = 1 << args.log_n
@@ -541,6 +557,7 @@ def run_ours_synthetic(args):
             "e2e": {"value": ms_e2e, "unit": "ms", "h2d_bytes_per_step": int(st_e["h2d_bytes"]), "d2h_bytes_per_step": int(st_e["d2h_bytes"])},
             "gpu_launches": int(launches), "clocks": clk.summary(), "roofline": roof, "cpu_baseline": None,
             "cpu_baseline_note": "the C restatement of the CPU prover (oracle/c) exists for BN254 only",
+            "batch_affine_rounds": args.ba_rounds, "tables_of_multiples": "none" if args.no_tables else ("G2.B only" if args.no_g1_tables else "all five arrays"),
             "stages_ms": {"serialised_total": st["ms_total"], "compute_h": st["ms_compute_h"], "msm": st["ms_msm"],
                           "accumulate": st["ms_accumulate"], "msm_c": st["msm_c"]}}
     print(json.dumps(line))
@@ -681,6 +698,8 @@ def main():
     ap.add_argument("--curve", default="bn254", choices=["bn254", "bls12_377"],
                     help="bls12_377 = BASELINE config 5 (use --log-n 24); the default line is the BN254 headline")
     ap.add_argument("--no-extras", action="store_true")
+    ap.add_argument("--no-g1-tables", action="store_true", help="bls12_377: a table of multiples for G2.B only")
+    ap.add_argument("--no-tables", action="store_true", help="bls12_377: keep no tables of multiples (memory goes to the batch-affine buffers instead)")
     ap.add_argument("--sweep", action="store_true", help="extras = the full 2^16..2^26 MSM and NTT sweeps (configs 2, 3)")
     args = ap.parse_args()
     if args.impl == "reference":

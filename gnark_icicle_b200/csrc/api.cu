@@ -53,7 +53,7 @@ void upload_bases(g16_ctx* ctx, DevBuf& dst, const Src& src, uint64_t n, int& pr
     constexpr bool IS_G2 = sizeof(typename C::E) > sizeof(Fp::T);
     const size_t row = (size_t)n * sizeof(typename C::Aff);
     pre_c = 0;
-    if (ctx->msm_precompute && n >= PRECOMPUTE_MIN_POINTS) {
+    if (ctx->msm_precompute && (IS_G2 || ctx->msm_precompute_g1) && n >= PRECOMPUTE_MIN_POINTS) {
         const int c = msm_pre_choose_c(n, IS_G2, ctx->msm_pre_c);
         const size_t total = row * (size_t)(255 / c + 1);
         size_t free_b = 0, total_b = 0;
@@ -172,6 +172,7 @@ int g16_ctx_set(g16_ctx* ctx, const char* key, int64_t value) {
     else if (k == "streams") ctx->streams = (int)value;
     else if (k == "msm_precompute") ctx->msm_precompute = (int)value;
     else if (k == "msm_pre_c") ctx->msm_pre_c = (int)value;
+    else if (k == "msm_precompute_g1") ctx->msm_precompute_g1 = (int)value;
     else if (k == "dist_sync") ctx->dist_sync = (int)value;
     else if (k == "g2_weight") ctx->g2_weight = (int)value;
     else if (k == "stage_threads") ctx->stage_threads = (int)value;

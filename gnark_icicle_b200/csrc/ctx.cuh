@@ -135,6 +135,7 @@ struct g16_ctx {
     int msm_c = 0, msm_waves = 4;
     int dist_sync = 1;           // g16_dist_*_dev return after the stream has drained (0: stream-ordered, caller synchronises)
     int msm_precompute = 1;      // keep 2^(c j) multiples of every key base resident (one shared bucket set, larger windows)
+    int msm_precompute_g1 = 1;   // ... for the G1 arrays too (0: only G2.B gets a table; for keys that fill the HBM)
     int msm_pre_c = 0;           // window bits of the tables built by the next uploads (0 = chosen from the array size)
     int g2_weight = 0;           // multi-GPU placement: cost of a G2 point in hundredths of a G1 point (0 = by group size)
     int stage_threads = 0;       // copier threads for pageable caller memory (0 = from the core count)

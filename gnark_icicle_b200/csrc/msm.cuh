@@ -896,7 +896,7 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
         if (ws.ba_pts[0].cap < out_max[0] * sizeof(Aff)) {          // first use at this size: only if it fits comfortably
             size_t free_b = 0, total_b = 0;
             G16_CUDA(cudaMemGetInfo(&free_b, &total_b));
-            if (need > free_b / 3) ws.ba_no_memory = true;
+            if (need > free_b / 5 * 3) ws.ba_no_memory = true;
         }
         if (!ws.ba_no_memory) {
             ws.ba_pts[0].reserve(out_max[0] * sizeof(Aff) + 64);

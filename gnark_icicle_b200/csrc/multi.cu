@@ -239,6 +239,7 @@ void multi_set(MultiGpu* mg, const char* key, int64_t value) {
         else if (k == "streams") c->streams = (int)value;
         else if (k == "msm_precompute") c->msm_precompute = (int)value;
         else if (k == "msm_pre_c") c->msm_pre_c = (int)value;
+        else if (k == "msm_precompute_g1") c->msm_precompute_g1 = (int)value;
         else if (k == "msm_ba_rounds") { for (auto& w : c->ws) w.ba_rounds = (int)value; }
         else if (k == "msm_ba_rounds_g1") { for (int i = 0; i < 4; i++) c->ws[i].ba_rounds = (int)value; }
         else if (k == "msm_ba_rounds_g2") c->ws[4].ba_rounds = (int)value;

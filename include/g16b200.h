@@ -74,6 +74,8 @@ const char* g16_last_error(const g16_ctx* ctx);
  * analogue of icicle's precompute_factor -- so that all windows of a prove MSM share one bucket set and the window
  * can grow to 20 bits; costs 13x the key in HBM and is skipped when that exceeds half of the free memory; set 0
  * before the upload to skip the tables, or after it to run the classic per-window path on the same key),
+ * "msm_precompute_g1" (default 1; 0 before the upload: only G2.B gets a table -- for keys whose tables and batch-affine
+ * buffers do not fit the HBM together, e.g. BLS12-377 at 2^24: the G1 MSMs gain more from the batch-affine rounds),
  * "msm_pre_c" (window bits, 16..21, of the tables built by later uploads; 0 = chosen from the array size),
  * "stage_threads" (copier threads that stage PAGEABLE caller memory -- e.g. Go heap slices -- into the context's pinned
  * ring; 0 = half of the host cores divided by the GPU count, between 2 and 8; page-locked buffers are DMA'd directly),
