@@ -692,7 +692,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--log-n", type=int, default=22, help="log2 of the constraint count (BASELINE: 22)")
-    ap.add_argument("--cpu-budget-s", type=float, default=150.0, help="--impl reference: stop timing further proves once the timed region exceeds this")
+    ap.add_argument("--cpu-budget-s", type=float, default=300.0, help="--impl reference: stop timing further proves once the timed region exceeds this")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg of the GPU arm")
     ap.add_argument("--ba-rounds", type=int, default=4, help="batch-affine rounds of the MSMs (library default 4; 0 = XYZZ accumulation only)")
     ap.add_argument("--curve", default="bn254", choices=["bn254", "bls12_377"],
