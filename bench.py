@@ -148,17 +148,33 @@ BENCH_SEED = 22
 POINT_NAMES = ["ar", "bs1", "krs_k", "krs_hz", "bs2"]
 
 
-def chain_case(nc, g1_mul=None, g2_mul=None):
-    """BASELINE config 4: the MiMC-shaped chain at `nc` constraints with a trapdoor setup (tests/helpers.py ChainCase:
-    witness, a, b, c and the setup scalars A(t), B(t), K, Z from oracle/c; bases = [scalar]G from g1_mul / g2_mul --
-    the library's fixed-base kernel in the GPU arm, oracle/c's in the reference arm: same seed, identical key)."""
+def oracle_for(curve):
+    """the C oracle of the curve (the checker, and the timed CPU prover)"""
+    if curve == "bls12_377":
+        from oracle.bls12_377 import cpu as oc
+    else:
+        from oracle import cpu as oc
+    return oc
+
+
+def chain_case(nc, g1_mul=None, g2_mul=None, curve="bn254"):
+    """BASELINE config 4 (BN254, pow5 rounds) / config 5 (BLS12-377, pow17 rounds): the MiMC-shaped chain at `nc`
+    constraints with a trapdoor setup (tests/helpers.py ChainCase: witness, a, b, c and the setup scalars A(t), B(t), K, Z
+    from oracle/c; bases = [scalar]G from g1_mul / g2_mul -- the library's fixed-base kernel in the GPU arm, oracle/c's
+    in the reference arm: same seed, identical key)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from helpers import ChainCase
-    return ChainCase(nc, seed=BENCH_SEED, g1_mul=g1_mul, g2_mul=g2_mul)
+    return ChainCase(nc, seed=BENCH_SEED, g1_mul=g1_mul, g2_mul=g2_mul, oc=oracle_for(curve))
 
 
-def workload_config(case, log_n):
+def workload_config(case, log_n, curve="bn254"):
     pk = case.pk
+    if curve == "bls12_377":
+        return {"workload": f"groth16_bls12_377_prove_2p{log_n}_mimc17_chain", "constraints": case.nc, "domain": case.n, "wires": case.nw,
+                "msm_sizes": {"g1_a": int(len(pk.g1_a)), "g1_b": int(len(pk.g1_b)), "g1_k": int(len(pk.g1_k)),
+                              "g1_z": int(len(pk.g1_z)), "g2_b": int(len(pk.g2_b))},
+                "instance": f"MiMC-shaped pow17 chain (5 constraints per round, std/hash/mimc/encrypt.go:137-143), trapdoor setup, xoshiro seed {BENCH_SEED}",
+                "l2": "inputs larger than L2"}
     return {"workload": f"groth16_bn254_prove_2p{log_n}_mimc_chain", "constraints": case.nc, "domain": case.n,
             "wires": case.nw,
             "msm_sizes": {"g1_a": int(len(pk.g1_a)), "g1_b": int(len(pk.g1_b)), "g1_k": int(len(pk.g1_k)),
@@ -179,9 +195,10 @@ def cpu_prove(case, ocpu):
     return (time.perf_counter() - t0) * 1e3, pts, h
 
 
-def parity_report(got, want, method):
+def parity_report(got, want, method, curve="bn254"):
     got, want = np.asarray(got, dtype=np.uint64).reshape(-1), np.asarray(want, dtype=np.uint64).reshape(-1)
-    bounds = [0, 8, 16, 24, 32, 48]
+    w = 12 if curve == "bls12_377" else 8      # uint64 limbs of a G1 affine point; G2 = 2 w
+    bounds = [0, w, 2 * w, 3 * w, 4 * w, 6 * w]
     bad = [POINT_NAMES[i] for i in range(5) if not np.array_equal(got[bounds[i]:bounds[i + 1]], want[bounds[i]:bounds[i + 1]])]
     return {"checked": POINT_NAMES, "bytes": int(got.size * 8), "mismatches": len(bad), "mismatched": bad, "method": method}
 
@@ -193,9 +210,9 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from oracle import cpu as ocpu
+    ocpu = oracle_for(args.curve)
     t_build = time.perf_counter()
-    case = chain_case(1 << args.log_n)          # key from oracle/c's batch fixed-base multiplication
+    case = chain_case(1 << args.log_n, curve=args.curve)   # key from oracle/c's batch fixed-base multiplication
     t_build = time.perf_counter() - t_build
     want = None
     times, budget = [], args.cpu_budget_s
@@ -204,7 +221,7 @@ def run_reference(args):
         ms, pts, h = cpu_prove(case, ocpu)
         if want is None:
             want = case.expected_points(h)      # exponent side: [sum w_i s_i]G with the setup's trapdoor scalars
-        par = parity_report(pts, want, "trapdoor identity on the oracle prover's five points")
+        par = parity_report(pts, want, "trapdoor identity on the oracle prover's five points", curve=args.curve)
         if par["mismatches"]:
             raise SystemExit(f"bench.py --impl reference: CPU prover disagrees with the trapdoor identity: {par}")
         if it >= warm:
@@ -215,10 +232,11 @@ def run_reference(args):
     cores = ocpu.threads()
     sample = (f"oracle/c restatement of the gnark-crypto CPU prover (not gnark-crypto itself: no Go toolchain, no ADX/BMI2 "
               f"assembly), {len(times)} full prove(s) at 2^{args.log_n} constraints on {cores} threads; key built by oracle/c in {t_build:.0f} s")
-    line = {"impl": "reference", "metric": "groth16_bn254_prove_ms", "value": v, "unit": "ms", "n_gpus": args.gpus,
+    line = {"impl": "reference", "metric": f"groth16_{args.curve}_prove_ms", "value": v, "unit": "ms", "n_gpus": args.gpus,
             "steps": len(times), "steps_requested": args.steps, "steps_run": len(times), "warmup": warm, "warmup_requested": args.warmup,
-            "ms_per_step": v, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "u32x8-montgomery",
-            "data": "synthetic", "config": workload_config(case, args.log_n), "parity": par,
+            "ms_per_step": v, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
+            "dtype": "u32x8-montgomery" if args.curve == "bn254" else "u32x12-montgomery",
+            "data": "synthetic", "config": workload_config(case, args.log_n, args.curve), "parity": par,
             "cpu_baseline": {"value": v, "unit": "ms", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
@@ -495,8 +513,11 @@ def run_ours(args):
 
 
 def run_ours_synthetic(args):
-    """BLS12-377 (BASELINE config 5): synthetic key and solution made on the device (the C oracle is BN254-only, so this
-    curve has no CPU leg; its parity evidence is tests/test_gpu_bls12_377.py against the Python oracle)."""
+    """BLS12-377 (BASELINE config 5) on one GPU: the pow17 MiMC-shaped chain with a trapdoor setup (scalars from the
+    BLS12-377 build of oracle/c, bases from the library's fixed-base kernel), all five points checked against the
+    exponent side before timing, the oracle's CPU prover on the same instance as cpu_baseline.  --synthetic-key skips the
+    instance and the checks (random distinct bases with the pow17 infinity shape): only for sizes whose key the host
+    cannot hold."""
     import torch
     from gnark_icicle_b200 import lib
     dev = torch.device("cuda:0")
@@ -512,12 +533,37 @@ def run_ours_synthetic(args):
     fp_eq = IMAD_EQ_PER_FP_MUL_12
     ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
     nc = 1 << args.log_n
-    key, sd, sh, n, nw = build_inputs(torch, ctx, nc, dev)
-    handle = ctx.pk_upload(key["domain_n"], key["g1_a"], key["g1_b"], key["g1_k"], key["g1_z"], key["g2_b"], key["inf_a"], key["inf_b"], nw)
-    sizes = {k: int(len(key[k])) for k in ("g1_a", "g1_b", "g1_k", "g1_z", "g2_b")}
-    del key
+    case, parity, want = None, None, None
+    if args.synthetic_key:
+        key, sd, sh, n, nw = build_inputs(torch, ctx, nc, dev)
+        handle = ctx.pk_upload(key["domain_n"], key["g1_a"], key["g1_b"], key["g1_k"], key["g1_z"], key["g2_b"], key["inf_a"], key["inf_b"], nw)
+        cfg = {"workload": f"groth16_{args.curve}_prove_2p{args.log_n}_mimc17_chain", "constraints": nc, "domain": n,
+               "msm_sizes": {k: int(len(key[k])) for k in ("g1_a", "g1_b", "g1_k", "g1_z", "g2_b")}, "l2": "inputs larger than L2",
+               "key": "synthetic distinct bases (fixed-base kernel), MiMC pow17 chain infinity shape; no parity check on this line"}
+        del key
+    else:
+        ocpu = oracle_for(args.curve)
+        case = chain_case(nc, g1_mul=ctx.g1_fixed_base_mul, g2_mul=ctx.g2_fixed_base_mul, curve=args.curve)
+        n, nw, pk = case.n, case.nw, case.pk
+        cfg = workload_config(case, args.log_n, args.curve)
+        handle = ctx.pk_upload(pk.domain_n, pk.g1_a, pk.g1_b, pk.g1_k, pk.g1_z, pk.g2_b, pk.infinity_a, pk.infinity_b, nw)
+        h_cpu = ocpu.compute_h(case.a, case.b, case.c, n)
+        want = case.expected_points(h_cpu)
+        del h_cpu
+        pin = lambda v: torch.from_numpy(np.ascontiguousarray(v).view(np.int64)).pin_memory()
+        sh = {"W": pin(case.W), "a": pin(case.a), "b": pin(case.b), "c": pin(case.c)}
+        sd = {"W": sh["W"].to(dev)}
+        for k in ("a", "b", "c"):
+            sd[k] = torch.zeros((n, 4), dtype=torch.int64, device=dev)
+            sd[k][:nc] = sh[k].to(dev)
     wa, wb, wc = (torch.empty_like(sd[k]) for k in ("a", "b", "c"))
     hW, ha, hb, hc = (sh[k].numpy().view(np.uint64) for k in ("W", "a", "b", "c"))
+    if case is not None:
+        pts, _ = ctx.prove(handle, hW, ha, hb, hc)
+        parity = parity_report(pts, want, "trapdoor identity [sum w_i s_i]G on all five points of the benchmarked instance, h from the "
+                                          "CPU oracle's computeH; checked before timing", curve=args.curve)
+        if parity["mismatches"]:
+            raise SystemExit(f"bench.py: GPU prove disagrees with the oracle: {parity}")
 
     def step_dev():
         with torch.cuda.stream(ext):
@@ -533,6 +579,10 @@ def run_ours_synthetic(args):
     ms_e2e, (pts_e2e, st_e) = timed(torch, ranks, ext, lambda: ctx.prove(handle, hW, ha, hb, hc), args.steps, args.warmup)
     if not np.array_equal(pts_dev, pts_e2e):
         raise SystemExit("bench.py: device-resident and host-buffer proofs differ")
+    if want is not None:
+        if not (np.array_equal(pts_dev, want) and np.array_equal(pts_e2e, want)):
+            raise SystemExit("bench.py: a timed prove differs from the oracle's expectation")
+        parity["legs_checked"] = ["value", "e2e"]
     ctx.set("streams", 1)
     step_dev()
     _, st = step_dev()
@@ -544,22 +594,30 @@ def run_ours_synthetic(args):
     g2_ops = st["msm_n"][4] * st["msm_windows"][4] * MADD_MULS["g2"] * fp_eq
     g2_ms = st["ms_accumulate"][4]
     ach = g1_ops / (g1_ms * 1e-3) / 1e12
-    roof = {"bound": "int32-imad", "kernel": "k_accumulate<G1> (4 launches/step)", "achieved": ach, "peak": imad / 1e12, "unit": "TIMAD/s",
+    roof = {"bound": "int32-imad", "kernel": "bucket accumulation of the four G1 MSMs (batch-affine rounds + k_accumulate<G1>)", "achieved": ach,
+            "peak": imad / 1e12, "unit": "TIMAD/s",
             "frac": ach / (imad / 1e12), "traffic": None, "field_mul_peak_g_per_s": fp_mul / 1e9,
+            "frac_definition": "entries x 10 Fp mul x 600 IMAD-eq (12-limb field: 2*12^2+12 limb-MACs x 2) / stage time / measured IMAD peak",
             "frac_of_multiplier_ceiling": g1_ops / fp_eq / (g1_ms * 1e-3) / fp_mul,
-            "g2": {"kernel": "k_accumulate<G2>", "achieved": g2_ops / (g2_ms * 1e-3) / 1e12, "frac": g2_ops / (g2_ms * 1e-3) / imad},
+            "g2": {"kernel": "bucket accumulation of the G2 MSM", "achieved": g2_ops / (g2_ms * 1e-3) / 1e12, "frac": g2_ops / (g2_ms * 1e-3) / imad},
             "share_of_step": (g1_ms + g2_ms) / st["ms_total"]}
     line = {"metric": f"groth16_{args.curve}_prove_ms", "value": ms_dev, "unit": "ms", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_dev, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "u32x12-montgomery",
-            "data": "synthetic", "config": {"workload": f"groth16_{args.curve}_prove_2p{args.log_n}_mimc17_chain", "constraints": nc, "domain": n,
-                                            "msm_sizes": sizes, "l2": "inputs larger than L2",
-                                            "key": "synthetic distinct bases (fixed-base kernel), MiMC pow17 chain infinity shape"},
+            "data": "synthetic", "config": cfg, "parity": parity,
             "e2e": {"value": ms_e2e, "unit": "ms", "h2d_bytes_per_step": int(st_e["h2d_bytes"]), "d2h_bytes_per_step": int(st_e["d2h_bytes"])},
             "gpu_launches": int(launches), "clocks": clk.summary(), "roofline": roof, "cpu_baseline": None,
-            "cpu_baseline_note": "the C restatement of the CPU prover (oracle/c) exists for BN254 only",
             "batch_affine_rounds": args.ba_rounds, "tables_of_multiples": "none" if args.no_tables else ("G2.B only" if args.no_g1_tables else "all five arrays"),
             "stages_ms": {"serialised_total": st["ms_total"], "compute_h": st["ms_compute_h"], "msm": st["ms_msm"],
                           "accumulate": st["ms_accumulate"], "msm_c": st["msm_c"]}}
+    if case is not None and not args.no_cpu:
+        ctx.pk_free(handle)
+        ms_cpu, pts_cpu, _ = cpu_prove(case, ocpu)
+        if not np.array_equal(pts_cpu, pts_dev):
+            raise SystemExit("bench.py: the CPU oracle prover and the GPU disagree on the benchmarked instance")
+        line["parity"]["cpu_prover_points_equal"] = True
+        line["cpu_baseline"] = {"value": ms_cpu, "unit": "ms", "cores": ocpu.threads(), "kind": "port",
+                                "sample": f"one full prove of the same 2^{args.log_n}-constraint instance by the BLS12-377 build of the oracle/c "
+                                          "restatement of the gnark-crypto CPU prover (not gnark-crypto itself), all host threads"}
     print(json.dumps(line))
 
 
@@ -698,6 +756,7 @@ def main():
     ap.add_argument("--curve", default="bn254", choices=["bn254", "bls12_377"],
                     help="bls12_377 = BASELINE config 5 (use --log-n 24); the default line is the BN254 headline")
     ap.add_argument("--no-extras", action="store_true")
+    ap.add_argument("--synthetic-key", action="store_true", help="bls12_377: random bases with the pow17 infinity shape instead of the trapdoor instance (no parity, no CPU leg)")
     ap.add_argument("--no-g1-tables", action="store_true", help="bls12_377: a table of multiples for G2.B only")
     ap.add_argument("--no-tables", action="store_true", help="bls12_377: keep no tables of multiples (memory goes to the batch-affine buffers instead)")
     ap.add_argument("--sweep", action="store_true", help="extras = the full 2^16..2^26 MSM and NTT sweeps (configs 2, 3)")

@@ -1,4 +1,5 @@
-"""CPU oracle for the Groth16 BN254 proving hot path.
+"""CPU oracle for the Groth16 proving hot path (BN254; BLS12-377 through the alias package oracle.bls12_377 and
+the second build of oracle/c).
 
 TEST INFRASTRUCTURE ONLY.  Nothing under ``oracle/`` is part of the product:
 only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline /

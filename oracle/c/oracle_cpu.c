@@ -1,5 +1,8 @@
 /* Multithreaded CPU oracle for the Groth16 BN254 hot path.
  *
+ * (ORC_CURVE=377 builds the same file for BLS12-377, BASELINE.json config 5:
+ *  backend/groth16/bls12-377/prove.go is bn254/prove.go over the other curve package.)
+ *
  * TEST INFRASTRUCTURE ONLY -- never linked into or called from the product
  * library; used by tests/ as the checker at sizes Python cannot reach and by
  * bench.py as the timed CPU baseline ("port": a restatement of the
@@ -20,34 +23,60 @@
 #include "field.h"
 
 /* ------------------------------------------------------------ fp / fp2 adapters */
+#if ORC_CURVE == 254
 typedef fe fp_t;
-static inline void fp_add(fe *r, const fe *a, const fe *b) { f_add(&FP, r, a, b); }
-static inline void fp_sub(fe *r, const fe *a, const fe *b) { f_sub(&FP, r, a, b); }
-static inline void fp_mul(fe *r, const fe *a, const fe *b) { f_mul(&FP, r, a, b); }
-static inline void fp_sqr(fe *r, const fe *a) { f_mul(&FP, r, a, a); }
-static inline void fp_inv(fe *r, const fe *a) { f_inv(&FP, r, a); }
-static inline int fp_is_zero(const fe *a) { return fe_is_zero(a); }
-static inline int fp_eq(const fe *a, const fe *b) { return fe_eq(a, b); }
-static inline void fp_set_one(fe *r) { *r = FP.one; }
-static inline void fp_set_zero(fe *r) { memset(r, 0, sizeof *r); }
+#define FPF(x) f_##x
+#define FPE(x) fe_##x
+#define FP2_NONRES 1    /* Fp2 = Fp[u]/(u^2 + 1) */
+#define G1_B 3          /* y^2 = x^3 + 3 */
+#define FR_COSET_GEN 5  /* fft.Domain FrMultiplicativeGen */
+#define FR_ADICITY 28
+#else
+typedef fe6 fp_t;
+#define FPF(x) f6_##x
+#define FPE(x) fe6_##x
+#define FP2_NONRES 5    /* Fp2 = Fp[u]/(u^2 + 5) (gnark-crypto bls12-377 E2) */
+#define G1_B 1          /* y^2 = x^3 + 1 */
+#define FR_COSET_GEN 22
+#define FR_ADICITY 47
+#endif
+static inline void fp_add(fp_t *r, const fp_t *a, const fp_t *b) { FPF(add)(&FP, r, a, b); }
+static inline void fp_sub(fp_t *r, const fp_t *a, const fp_t *b) { FPF(sub)(&FP, r, a, b); }
+static inline void fp_mul(fp_t *r, const fp_t *a, const fp_t *b) { FPF(mul)(&FP, r, a, b); }
+static inline void fp_sqr(fp_t *r, const fp_t *a) { FPF(mul)(&FP, r, a, a); }
+static inline void fp_inv(fp_t *r, const fp_t *a) { FPF(inv)(&FP, r, a); }
+static inline void fp_neg(fp_t *r, const fp_t *a) { FPF(neg)(&FP, r, a); }
+static inline int fp_is_zero(const fp_t *a) { return FPE(is_zero)(a); }
+static inline int fp_eq(const fp_t *a, const fp_t *b) { return FPE(eq)(a, b); }
+static inline void fp_set_one(fp_t *r) { *r = FP.one; }
+static inline void fp_set_zero(fp_t *r) { memset(r, 0, sizeof *r); }
+/* r = k*a for the small non-residue */
+static inline void fp_mul_nonres(fp_t *r, const fp_t *a) {
+#if FP2_NONRES == 1
+    *r = *a;
+#else
+    fp_t t, u; fp_add(&t, a, a); fp_add(&t, &t, &t); fp_add(&u, &t, a); *r = u;   /* 5a */
+#endif
+}
 
-typedef struct { fe a0, a1; } fp2_t;   /* a0 + a1*u, u^2 = -1 (gnark E2{A0,A1}) */
+typedef struct { fp_t a0, a1; } fp2_t;   /* a0 + a1*u, u^2 = -FP2_NONRES (gnark E2{A0,A1}) */
 static inline void fp2_add(fp2_t *r, const fp2_t *a, const fp2_t *b) { fp_add(&r->a0, &a->a0, &b->a0); fp_add(&r->a1, &a->a1, &b->a1); }
 static inline void fp2_sub(fp2_t *r, const fp2_t *a, const fp2_t *b) { fp_sub(&r->a0, &a->a0, &b->a0); fp_sub(&r->a1, &a->a1, &b->a1); }
 static inline void fp2_mul(fp2_t *r, const fp2_t *a, const fp2_t *b) {
-    fe t0, t1, t2, t3;
+    fp_t t0, t1, t2, t3;
     fp_mul(&t0, &a->a0, &b->a0); fp_mul(&t1, &a->a1, &b->a1);
     fp_mul(&t2, &a->a0, &b->a1); fp_mul(&t3, &a->a1, &b->a0);
+    fp_mul_nonres(&t1, &t1);
     fp_sub(&r->a0, &t0, &t1); fp_add(&r->a1, &t2, &t3);
 }
 static inline void fp2_sqr(fp2_t *r, const fp2_t *a) { fp2_mul(r, a, a); }
-static inline void fp2_inv(fp2_t *r, const fp2_t *a) {
-    fe t0, t1; fp_sqr(&t0, &a->a0); fp_sqr(&t1, &a->a1); fp_add(&t0, &t0, &t1); fp_inv(&t0, &t0);
-    fp_mul(&r->a0, &a->a0, &t0); fp_mul(&t1, &a->a1, &t0); f_neg(&FP, &r->a1, &t1);
+static inline void fp2_inv(fp2_t *r, const fp2_t *a) {      /* conj(a) / (a0^2 + NONRES a1^2) */
+    fp_t t0, t1; fp_sqr(&t0, &a->a0); fp_sqr(&t1, &a->a1); fp_mul_nonres(&t1, &t1); fp_add(&t0, &t0, &t1); fp_inv(&t0, &t0);
+    fp_mul(&r->a0, &a->a0, &t0); fp_mul(&t1, &a->a1, &t0); fp_neg(&r->a1, &t1);
 }
-static inline int fp2_is_zero(const fp2_t *a) { return fe_is_zero(&a->a0) && fe_is_zero(&a->a1); }
-static inline int fp2_eq(const fp2_t *a, const fp2_t *b) { return fe_eq(&a->a0, &b->a0) && fe_eq(&a->a1, &b->a1); }
-static inline void fp2_set_one(fp2_t *r) { r->a0 = FP.one; memset(&r->a1, 0, sizeof(fe)); }
+static inline int fp2_is_zero(const fp2_t *a) { return fp_is_zero(&a->a0) && fp_is_zero(&a->a1); }
+static inline int fp2_eq(const fp2_t *a, const fp2_t *b) { return fp_eq(&a->a0, &b->a0) && fp_eq(&a->a1, &b->a1); }
+static inline void fp2_set_one(fp2_t *r) { r->a0 = FP.one; memset(&r->a1, 0, sizeof(fp_t)); }
 static inline void fp2_set_zero(fp2_t *r) { memset(r, 0, sizeof *r); }
 
 #define EC g1
@@ -122,15 +151,29 @@ void orc_fr_dot(const fe *a, const fe *b, uint64_t n, fe *out) {
 }
 
 /* ------------------------------------------------------------ generators */
-static const fe G2X0 = {{0x46debd5cd992f6edULL, 0x674322d4f75edaddULL, 0x426a00665e5c4479ULL, 0x1800deef121f1e76ULL}};
-static const fe G2X1 = {{0x97e485b7aef312c2ULL, 0xf1aa493335a9e712ULL, 0x7260bfb731fb5d25ULL, 0x198e9393920d483aULL}};
-static const fe G2Y0 = {{0x4ce6cc0166fa7daaULL, 0xe3d1e7690c43d37bULL, 0x4aab71808dcb408fULL, 0x12c85ea5db8c6debULL}};
-static const fe G2Y1 = {{0x55acdadcd122975bULL, 0xbc4b313370b38ef3ULL, 0xec9e99ad690c3395ULL, 0x090689d0585ff075ULL}};
+#if ORC_CURVE == 254
+/* G1 = (1, 2); G2 = the EIP-197 / gnark-crypto bn254.Generators point (plain integers) */
+static const fp_t G1X = {{1, 0, 0, 0}}, G1Y = {{2, 0, 0, 0}};
+static const fp_t G2X0 = {{0x46debd5cd992f6edULL, 0x674322d4f75edaddULL, 0x426a00665e5c4479ULL, 0x1800deef121f1e76ULL}};
+static const fp_t G2X1 = {{0x97e485b7aef312c2ULL, 0xf1aa493335a9e712ULL, 0x7260bfb731fb5d25ULL, 0x198e9393920d483aULL}};
+static const fp_t G2Y0 = {{0x4ce6cc0166fa7daaULL, 0xe3d1e7690c43d37bULL, 0x4aab71808dcb408fULL, 0x12c85ea5db8c6debULL}};
+static const fp_t G2Y1 = {{0x55acdadcd122975bULL, 0xbc4b313370b38ef3ULL, 0xec9e99ad690c3395ULL, 0x090689d0585ff075ULL}};
+#else
+/* gnark-crypto's bls12-377 G1 generator; the G2 point is the harness generator of oracle/curve.py (cofactor times
+ * the twist point with x = 2): every G2 operand of the proving path comes from the key, so only the harness's own
+ * keys depend on it.  Plain integers. */
+static const fp_t G1X = {{0xeab9b16eb21be9efULL, 0xd5481512ffcd394eULL, 0x188282c8bd37cb5cULL, 0x85951e2caa9d41bbULL, 0xc8fc6225bf87ff54ULL, 0x008848defe740a67ULL}};
+static const fp_t G1Y = {{0xfd82de55559c8ea6ULL, 0xc2fe3d3634a9591aULL, 0x6d182ad44fb82305ULL, 0xbd7fb348ca3e52d9ULL, 0x1f674f5d30afeec4ULL, 0x01914a69c5102effULL}};
+static const fp_t G2X0 = {{0x7faab58c9b87bda9ULL, 0x20a7c4c78130d2d0ULL, 0x401724764cd34f4dULL, 0x049f123bf27dce03ULL, 0x35bb08884aee7b99ULL, 0x00415abb1137c889ULL}};
+static const fp_t G2X1 = {{0x0ddf884b60d27f88ULL, 0x4de60b0c0f56b5e1ULL, 0xa208c4859cf3630fULL, 0x24148cd0d42beba1ULL, 0x9d9f07b86366d6eaULL, 0x00a272c24ca7d342ULL}};
+static const fp_t G2Y0 = {{0x76521ebbbb23ee23ULL, 0x33cc6492b66b5ee5ULL, 0x4ac4ef1a54a524d9ULL, 0xf523908ed09da02fULL, 0xb97bc0e7237bbb97ULL, 0x0199275defaacc0dULL}};
+static const fp_t G2Y1 = {{0xeb2f80ac9c3a8051ULL, 0xe66e6d2df31cbe0cULL, 0x78536c115ac38999ULL, 0x509504b67ef09df5ULL, 0x4752e212f85ed167ULL, 0x0121cb2668f07eaaULL}};
+#endif
 
-static void g1_gen(g1_aff *g) { g->x = FP.one; fp_add(&g->y, &FP.one, &FP.one); }
+static void g1_gen(g1_aff *g) { FPF(to_mont)(&FP, &g->x, &G1X); FPF(to_mont)(&FP, &g->y, &G1Y); }
 static void g2_gen(g2_aff *g) {
-    f_to_mont(&FP, &g->x.a0, &G2X0); f_to_mont(&FP, &g->x.a1, &G2X1);
-    f_to_mont(&FP, &g->y.a0, &G2Y0); f_to_mont(&FP, &g->y.a1, &G2Y1);
+    FPF(to_mont)(&FP, &g->x.a0, &G2X0); FPF(to_mont)(&FP, &g->x.a1, &G2X1);
+    FPF(to_mont)(&FP, &g->y.a0, &G2Y0); FPF(to_mont)(&FP, &g->y.a1, &G2Y1);
 }
 
 /* ------------------------------------------------------------ fixed-base [k]G, 8-bit windows
@@ -297,16 +340,21 @@ void orc_g2_add(const g2_aff *a, const g2_aff *b, g2_aff *out) {
 }
 int orc_g1_on_curve(const g1_aff *p) {
     if (g1_aff_is_inf(p)) return 1;
-    fe l, r, three; fp_sqr(&l, &p->y); fp_sqr(&r, &p->x); fp_mul(&r, &r, &p->x);
-    f_set_u64(&FP, &three, 3); fp_add(&r, &r, &three); return fe_eq(&l, &r);
+    fp_t l, r, b; fp_sqr(&l, &p->y); fp_sqr(&r, &p->x); fp_mul(&r, &r, &p->x);
+    FPF(set_u64)(&FP, &b, G1_B); fp_add(&r, &r, &b); return fp_eq(&l, &r);
 }
 
 /* ------------------------------------------------------------ fft.Domain (prove.go:356-399) */
-static const fe ROOT_2_28 = {{0x9bd61b6e725b19f0ULL, 0x402d111e41112ed4ULL, 0x00e0a7eb8ef62abcULL, 0x2a3c09f0a58a7e85ULL}};
+/* primitive 2^FR_ADICITY-th root of unity FR_COSET_GEN^((r-1)/2^FR_ADICITY), plain integer (gnark-crypto's fft.Domain generator) */
+#if ORC_CURVE == 254
+static const fe ROOT_2_ADIC = {{0x9bd61b6e725b19f0ULL, 0x402d111e41112ed4ULL, 0x00e0a7eb8ef62abcULL, 0x2a3c09f0a58a7e85ULL}};
+#else
+static const fe ROOT_2_ADIC = {{0x476ef4a4ec2a895eULL, 0x9b506ee363e3f04aULL, 0x60c69477d1a8a12fULL, 0x11d4b7f60cb92cc1ULL}};
+#endif
 static void fr_pow_u64(fe *r, const fe *a, uint64_t e) { fe ee = {{e, 0, 0, 0}}; f_pow(&FR, r, a, &ee); }
 static void domain_gen(fe *w, int logn) {           /* primitive 2^logn-th root, Montgomery */
-    fe g; f_to_mont(&FR, &g, &ROOT_2_28);
-    for (int i = logn; i < 28; i++) f_sqr(&FR, &g, &g);
+    fe g; f_to_mont(&FR, &g, &ROOT_2_ADIC);
+    for (int i = logn; i < FR_ADICITY; i++) f_sqr(&FR, &g, &g);
     *w = g;
 }
 static size_t brev(size_t i, int logn) { size_t r = 0; for (int k = 0; k < logn; k++) { r = (r << 1) | (i & 1); i >>= 1; } return r; }
@@ -350,7 +398,7 @@ void orc_fft(fe *a, uint64_t n, int mode, int threads) {
     int logn = 0; while (((uint64_t)1 << logn) < n) logn++;
     fe w, winv, five, fiveinv, ninv, one = FR.one;
     domain_gen(&w, logn); f_inv(&FR, &winv, &w);
-    f_set_u64(&FR, &five, 5); f_inv(&FR, &fiveinv, &five);
+    f_set_u64(&FR, &five, FR_COSET_GEN); f_inv(&FR, &fiveinv, &five);
     f_set_u64(&FR, &ninv, n); f_inv(&FR, &ninv, &ninv);
     int inverse = (mode == 0 || mode == 2), dit = (mode == 1 || mode == 3);
     if (mode == 1) { sc_ctx s = {a, five, one, logn, 1}; par_for(n, threads, scale_range, &s); }
@@ -376,23 +424,32 @@ void orc_compute_h(const fe *a, const fe *b, const fe *c, uint64_t nc, uint64_t 
     orc_fft(h, n, 0, threads); orc_fft(bb, n, 0, threads); orc_fft(cc, n, 0, threads);
     orc_fft(h, n, 1, threads); orc_fft(bb, n, 1, threads); orc_fft(cc, n, 1, threads);
     pw_ctx p = {h, bb, cc, FR.one};
-    fe five; f_set_u64(&FR, &five, 5); fr_pow_u64(&p.den, &five, n); f_sub(&FR, &p.den, &p.den, &FR.one); f_inv(&FR, &p.den, &p.den);
+    fe five; f_set_u64(&FR, &five, FR_COSET_GEN); fr_pow_u64(&p.den, &five, n); f_sub(&FR, &p.den, &p.den, &FR.one); f_inv(&FR, &p.den, &p.den);
     par_for(n, threads, pw_range, &p);
     orc_fft(h, n, 2, threads);
     free(bb); free(cc);
 }
 
 /* ------------------------------------------------------------ MiMC-shaped chain (oracle/r1cs.py mimc_chain)
- * wires: 0=ONE 1=OUT 2=X0 3=K, then one internal wire per constraint but the last; nb_wires = nc+3 */
+ * wires: 0=ONE 1=OUT 2=X0 3=K, then one internal wire per constraint but the last; nb_wires = nc+3.
+ * A round is x <- (x + k + c_i)^e: t*t, CHAIN_SQ further squarings, one product with t.  BN254: e = 5, 3 constraints
+ * (std/hash/mimc/encrypt.go:124-128,147-153); BLS12-377: e = 17, 5 constraints (encrypt.go:137-143). */
+#if ORC_CURVE == 254
+#define CHAIN_SQ 1
+#else
+#define CHAIN_SQ 3
+#endif
+#define CHAIN_PER_ROUND (CHAIN_SQ + 2)
 typedef struct { uint64_t nc, rounds; xo_t g; uint64_t j, xw, next; } chain_it;
 static void chain_begin(chain_it *it, uint64_t nc, uint64_t seed) {
-    it->nc = nc; it->rounds = (nc - 1) / 3; xo_seed(&it->g, seed); it->j = 0; it->xw = 2; it->next = 4;
+    it->nc = nc; it->rounds = (nc - 1) / CHAIN_PER_ROUND; xo_seed(&it->g, seed); it->j = 0; it->xw = 2; it->next = 4;
 }
-/* the (nc-1)/3 round constants of the chain, Montgomery (tests build the constraint matrices from them) */
+/* the (nc-1)/CHAIN_PER_ROUND round constants of the chain, Montgomery (tests build the constraint matrices from them) */
 void orc_mimc_chain_constants(uint64_t nc, uint64_t seed, fe *out) {
     chain_it it; chain_begin(&it, nc, seed);
     for (uint64_t r = 0; r < it.rounds; r++) xo_field(&it.g, &FR, &out[r]);
 }
+int orc_mimc_chain_per_round(void) { return CHAIN_PER_ROUND; }
 /* W (nc+3), a,b,c (nc): solved witness and per-constraint L.w, R.w, O.w; all Montgomery */
 void orc_mimc_chain_witness(uint64_t nc, uint64_t seed, const fe *x0, const fe *k, fe *W, fe *a, fe *b, fe *c) {
     chain_it it; chain_begin(&it, nc, seed);
@@ -401,10 +458,15 @@ void orc_mimc_chain_witness(uint64_t nc, uint64_t seed, const fe *x0, const fe *
     for (uint64_t r = 0; r < it.rounds; r++) {
         fe ci, t; xo_field(&it.g, &FR, &ci);
         f_add(&FR, &t, &W[it.xw], k); f_add(&FR, &t, &t, &ci);
-        uint64_t u = it.next++, v = it.next++, nx = it.next++;
-        f_mul(&FR, &W[u], &t, &t); a[j] = t; b[j] = t; c[j] = W[u]; j++;
-        f_mul(&FR, &W[v], &W[u], &W[u]); a[j] = W[u]; b[j] = W[u]; c[j] = W[v]; j++;
-        f_mul(&FR, &W[nx], &W[v], &t); a[j] = W[v]; b[j] = t; c[j] = W[nx]; j++;
+        uint64_t prev = it.next++;
+        f_mul(&FR, &W[prev], &t, &t); a[j] = t; b[j] = t; c[j] = W[prev]; j++;
+        for (int q = 0; q < CHAIN_SQ; q++) {
+            uint64_t v = it.next++;
+            f_mul(&FR, &W[v], &W[prev], &W[prev]); a[j] = W[prev]; b[j] = W[prev]; c[j] = W[v]; j++;
+            prev = v;
+        }
+        uint64_t nx = it.next++;
+        f_mul(&FR, &W[nx], &W[prev], &t); a[j] = W[prev]; b[j] = t; c[j] = W[nx]; j++;
         it.xw = nx;
     }
     while (j < nc - 1) {
@@ -436,12 +498,17 @@ void orc_mimc_chain_setup_scalars(uint64_t nc, uint64_t n, uint64_t seed, const 
     uint64_t j = 0;
     for (uint64_t r = 0; r < it.rounds; r++) {
         fe ci, cl; xo_field(&it.g, &FR, &ci);
-        uint64_t u = it.next++, v = it.next++, nx = it.next++;
+        uint64_t prev = it.next++;
         f_mul(&FR, &cl, &ci, &L[j]);
-        acc(&A[it.xw], &L[j]); acc(&A[3], &L[j]); acc(&A[0], &cl); acc(&B[it.xw], &L[j]); acc(&B[3], &L[j]); acc(&B[0], &cl); acc(&Cc[u], &L[j]); j++;
-        acc(&A[u], &L[j]); acc(&B[u], &L[j]); acc(&Cc[v], &L[j]); j++;
+        acc(&A[it.xw], &L[j]); acc(&A[3], &L[j]); acc(&A[0], &cl); acc(&B[it.xw], &L[j]); acc(&B[3], &L[j]); acc(&B[0], &cl); acc(&Cc[prev], &L[j]); j++;
+        for (int q = 0; q < CHAIN_SQ; q++) {
+            uint64_t v = it.next++;
+            acc(&A[prev], &L[j]); acc(&B[prev], &L[j]); acc(&Cc[v], &L[j]); j++;
+            prev = v;
+        }
+        uint64_t nx = it.next++;
         f_mul(&FR, &cl, &ci, &L[j]);
-        acc(&A[v], &L[j]); acc(&B[it.xw], &L[j]); acc(&B[3], &L[j]); acc(&B[0], &cl); acc(&Cc[nx], &L[j]); j++;
+        acc(&A[prev], &L[j]); acc(&B[it.xw], &L[j]); acc(&B[3], &L[j]); acc(&B[0], &cl); acc(&Cc[nx], &L[j]); j++;
         it.xw = nx;
     }
     while (j < nc - 1) { uint64_t nx = it.next++; acc(&A[it.xw], &L[j]); acc(&B[it.xw], &L[j]); acc(&Cc[nx], &L[j]); j++; it.xw = nx; }

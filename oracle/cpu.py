@@ -1,22 +1,27 @@
-"""ctypes binding of the C oracle (oracle/c/liboracle_cpu.so).  Test infrastructure only.
+"""ctypes binding of the C oracle (oracle/c/liboracle_cpu*.so).  Test infrastructure only.
 
-Arrays are numpy uint64 with a trailing limb axis: Fr (n,4), G1 affine (n,8),
-G2 affine (n,16) -- the gnark memory image (Montgomery, little-endian limbs).
+Arrays are numpy uint64 with a trailing limb axis: Fr (n,4), G1 affine (n,G1W),
+G2 affine (n,G2W) -- the gnark memory image (Montgomery, little-endian limbs); G1W, G2W = 8, 16 for BN254 and
+12, 24 for BLS12-377.  Curve-generic like oracle/curve.py: ``oracle.cpu`` binds the BN254 library and
+``oracle.bls12_377.cpu`` (the alias package) the BLS12-377 one, both built from the same C sources.
 """
 import ctypes
 import os
 import subprocess
 import numpy as np
 
+NAME = "bls12_377" if (__package__ or "").endswith("bls12_377") else "bn254"
+G1W, G2W = (12, 24) if NAME == "bls12_377" else (8, 16)
 _DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "c")
-_SO = os.path.join(_DIR, "liboracle_cpu.so")
+_SO_NAME = "liboracle_cpu_bls12_377.so" if NAME == "bls12_377" else "liboracle_cpu.so"
+_SO = os.path.join(_DIR, _SO_NAME)
 
 
 def build(force=False):
-    srcs = [os.path.join(_DIR, f) for f in ("oracle_cpu.c", "field.h", "ec_tmpl.h", "Makefile")]
+    srcs = [os.path.join(_DIR, f) for f in ("oracle_cpu.c", "field.h", "field_tmpl.h", "ec_tmpl.h", "Makefile")]
     if force or not os.path.exists(_SO) or any(
             os.path.exists(s) and os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs):
-        subprocess.check_call(["make", "-C", _DIR, "-B", "liboracle_cpu.so"], stdout=subprocess.DEVNULL)
+        subprocess.check_call(["make", "-C", _DIR, "-B", _SO_NAME], stdout=subprocess.DEVNULL)
     return _SO
 
 
@@ -71,14 +76,14 @@ def fr_mul_vec(a, b):
 
 def g1_mul_gen_batch(scalars, nthreads=0):
     s = _c(scalars)
-    out = np.empty((len(s), 8), dtype=np.uint64)
+    out = np.empty((len(s), G1W), dtype=np.uint64)
     lib().orc_g1_mul_gen_batch(_p(s), u64(len(s)), _p(out), ci(nthreads or threads()))
     return out
 
 
 def g2_mul_gen_batch(scalars, nthreads=0):
     s = _c(scalars)
-    out = np.empty((len(s), 16), dtype=np.uint64)
+    out = np.empty((len(s), G2W), dtype=np.uint64)
     lib().orc_g2_mul_gen_batch(_p(s), u64(len(s)), _p(out), ci(nthreads or threads()))
     return out
 
@@ -86,7 +91,7 @@ def g2_mul_gen_batch(scalars, nthreads=0):
 def msm_g1(points, scalars, c=0, nthreads=0):
     p, s = _c(points), _c(scalars)
     assert len(p) == len(s)
-    out = np.zeros(8, dtype=np.uint64)
+    out = np.zeros(G1W, dtype=np.uint64)
     lib().orc_msm_g1(_p(p), _p(s), u64(len(s)), _p(out), ci(c), ci(nthreads or threads()))
     return out
 
@@ -94,35 +99,35 @@ def msm_g1(points, scalars, c=0, nthreads=0):
 def msm_g2(points, scalars, c=0, nthreads=0):
     p, s = _c(points), _c(scalars)
     assert len(p) == len(s)
-    out = np.zeros(16, dtype=np.uint64)
+    out = np.zeros(G2W, dtype=np.uint64)
     lib().orc_msm_g2(_p(p), _p(s), u64(len(s)), _p(out), ci(c), ci(nthreads or threads()))
     return out
 
 
 def g1_mul(point, k):
     p, k = _c(point), _c(k)
-    out = np.zeros(8, dtype=np.uint64)
+    out = np.zeros(G1W, dtype=np.uint64)
     lib().orc_g1_mul(_p(p), _p(k), _p(out))
     return out
 
 
 def g2_mul(point, k):
     p, k = _c(point), _c(k)
-    out = np.zeros(16, dtype=np.uint64)
+    out = np.zeros(G2W, dtype=np.uint64)
     lib().orc_g2_mul(_p(p), _p(k), _p(out))
     return out
 
 
 def g1_add(a, b):
     a, b = _c(a), _c(b)
-    out = np.zeros(8, dtype=np.uint64)
+    out = np.zeros(G1W, dtype=np.uint64)
     lib().orc_g1_add(_p(a), _p(b), _p(out))
     return out
 
 
 def g2_add(a, b):
     a, b = _c(a), _c(b)
-    out = np.zeros(16, dtype=np.uint64)
+    out = np.zeros(G2W, dtype=np.uint64)
     lib().orc_g2_add(_p(a), _p(b), _p(out))
     return out
 
@@ -152,7 +157,8 @@ def mimc_chain_witness(nc, seed, x0, k):
 
 
 def mimc_chain_constants(nc, seed):
-    out = np.empty(((nc - 1) // 3, 4), dtype=np.uint64)
+    lib().orc_mimc_chain_per_round.restype = ctypes.c_int
+    out = np.empty(((nc - 1) // lib().orc_mimc_chain_per_round(), 4), dtype=np.uint64)
     lib().orc_mimc_chain_constants(u64(nc), u64(seed), _p(out))
     return out
 
@@ -166,32 +172,42 @@ def mimc_chain_setup_scalars(nc, n, seed, tw):
     return A, B, K, Z
 
 
-# ---- conversions between Python ints (oracle/bn254.py) and limb arrays
+# ---- conversions between Python ints (oracle/curve.py of the same instance) and limb arrays
 def fr_arr(vals):
-    from .bn254 import fr_vec_to_bytes
+    from .curve import fr_vec_to_bytes
     return np.frombuffer(fr_vec_to_bytes(vals), dtype=np.uint64).reshape(-1, 4).copy()
 
 
 def fr_ints(arr):
-    from .bn254 import fr_vec_from_bytes
+    from .curve import fr_vec_from_bytes
     return fr_vec_from_bytes(_c(arr).tobytes())
 
 
 def g1_arr(pts):
-    from .bn254 import g1_vec_to_bytes
-    return np.frombuffer(g1_vec_to_bytes(pts), dtype=np.uint64).reshape(-1, 8).copy()
+    from .curve import g1_vec_to_bytes
+    return np.frombuffer(g1_vec_to_bytes(pts), dtype=np.uint64).reshape(-1, G1W).copy()
 
 
 def g2_arr(pts):
-    from .bn254 import g2_vec_to_bytes
-    return np.frombuffer(g2_vec_to_bytes(pts), dtype=np.uint64).reshape(-1, 16).copy()
+    from .curve import g2_vec_to_bytes
+    return np.frombuffer(g2_vec_to_bytes(pts), dtype=np.uint64).reshape(-1, G2W).copy()
 
 
 def g1_pt(arr):
-    from .bn254 import g1_from_bytes
+    from .curve import g1_from_bytes
     return g1_from_bytes(_c(arr).tobytes())
 
 
 def g2_pt(arr):
-    from .bn254 import g2_from_bytes
+    from .curve import g2_from_bytes
     return g2_from_bytes(_c(arr).tobytes())
+
+
+def g1_gen_arr():
+    from .curve import G1_GEN
+    return g1_arr([G1_GEN])[0]
+
+
+def g2_gen_arr():
+    from .curve import G2_GEN
+    return g2_arr([G2_GEN])[0]

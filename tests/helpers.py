@@ -83,24 +83,26 @@ def is_zero_rows(a):
 
 
 class ChainCase:
-    """MiMC-shaped chain (config 4 shape) with a trapdoor setup: scalars from the C oracle, bases = [scalar]G
-    produced by `g1_mul` / `g2_mul` callables (CPU oracle for small sizes, the GPU fixed-base kernel for large)."""
+    """MiMC-shaped chain (config 4 shape; pow17 rounds = config 5 shape with the BLS12-377 oracle) with a trapdoor
+    setup: scalars from the C oracle `oc` (oracle.cpu, or oracle.bls12_377.cpu), bases = [scalar]G produced by
+    `g1_mul` / `g2_mul` callables (CPU oracle for small sizes, the GPU fixed-base kernel for large)."""
 
-    def __init__(self, nc, seed, g1_mul=None, g2_mul=None):
+    def __init__(self, nc, seed, g1_mul=None, g2_mul=None, oc=None):
         from gnark_icicle_b200 import ProvingKey
-        g1_mul = g1_mul or ocpu.g1_mul_gen_batch
-        g2_mul = g2_mul or ocpu.g2_mul_gen_batch
+        oc = self.oc = oc or ocpu
+        g1_mul = g1_mul or oc.g1_mul_gen_batch
+        g2_mul = g2_mul or oc.g2_mul_gen_batch
         n = 1
         while n < nc:
             n <<= 1
         self.nc, self.n, self.nw = nc, n, nc + 3
-        rnd = fr_rand(1000 + seed, 9)
+        rnd = oc.fr_random(SEED_BASE + 1000 + seed, 9)
         self.tw = rnd[0:5]
         self.r, self.s = rnd[5], rnd[6]
         x0, k = rnd[7], rnd[8]
         cseed = SEED_BASE + 2000 + seed
-        self.W, self.a, self.b, self.c = ocpu.mimc_chain_witness(nc, cseed, x0, k)
-        A, B, K, Z = ocpu.mimc_chain_setup_scalars(nc, n, cseed, self.tw)
+        self.W, self.a, self.b, self.c = oc.mimc_chain_witness(nc, cseed, x0, k)
+        A, B, K, Z = oc.mimc_chain_setup_scalars(nc, n, cseed, self.tw)
         self.inf_a, self.inf_b = is_zero_rows(A), is_zero_rows(B)
         self.sA, self.sB = A[~self.inf_a], B[~self.inf_b]
         self.sK = K[2:]
@@ -119,10 +121,13 @@ class ChainCase:
 
     def expected_points(self, h):
         """the five raw MSM results through the trapdoor identity (exponent side), given the oracle's h."""
+        oc = self.oc
+        g1, g2 = oc.g1_gen_arr(), oc.g2_gen_arr()
         wa, wb, wk = self.W[~self.inf_a], self.W[~self.inf_b], self.W[2:]
+        t1 = lambda sc, logs: oc.g1_mul(g1, oc.fr_dot(sc, logs))
         return np.concatenate([
-            trapdoor_g1(wa, self.sA), trapdoor_g1(wb, self.sB), trapdoor_g1(wk, self.sK),
-            trapdoor_g1(h[: self.n - 1], self.sZ), trapdoor_g2(wb, self.sB)])
+            t1(wa, self.sA), t1(wb, self.sB), t1(wk, self.sK), t1(h[: self.n - 1], self.sZ),
+            oc.g2_mul(g2, oc.fr_dot(wb, self.sB))])
 
 
 # ---------------------------------------------------------------- constraint matrices for the device (8(f) N1)

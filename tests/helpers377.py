@@ -1,5 +1,5 @@
 """BLS12-377 test helpers: Python-oracle values <-> gnark memory image as numpy limb arrays (Fr (n,4), G1 (n,12),
-G2 (n,24) uint64).  The BN254 tests use the C oracle for this; the BLS12-377 oracle is Python only."""
+G2 (n,24) uint64).  These serve the Python-oracle tests; the large-size tests (test_gpu_bls12_377_large.py) use oracle.bls12_377.cpu, the C oracle built for this curve."""
 import numpy as np
 
 from oracle.bls12_377 import curve as C
