@@ -887,6 +887,9 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
         typedef typename LazyCurve<C, (IS_G2 || G16_CURVE == 377) ? 0 : 1>::type CB;   // 12-limb bodies would overflow the instruction cache
         typedef typename CB::E E;
         typedef typename CB::Aff Aff;
+        typedef BaNorm<typename CB::BaseField> BN;      // the shared inversion runs in the prime field (norms of Fp2 denominators)
+        typedef typename BN::NF NF;
+        typedef typename NF::T NE;
         uint64_t out_max[8], in_max = total_max;
         for (int r = 0; r < ba_rounds; r++) { out_max[r] = in_max / 2 + pl.NB; in_max = out_max[r]; }
         const uint64_t t0_max = (out_max[0] + 32 * BA_K - 1) / (32 * BA_K) * 32;
@@ -920,23 +923,25 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
                 G16_LAUNCH_CHECK();
                 const uint32_t nthr = (uint32_t)((out_max[r] + 32 * BA_K - 1) / (32 * BA_K)) * 32;   // whole warps of 32 K outputs
                 const unsigned grid = (nthr + BA_THREADS - 1) / BA_THREADS;
-                E* tot0 = ws.ba_tot[0].as<E>();
-                k_ba_fwd<CB><<<grid, BA_THREADS, 0, st>>>(src, off_in, off_out, pl.NB, ws.ba_desc.as<uint32_t>(), ws.ba_prefix.as<E>(), tot0, nthr);
+                NE* tot0 = ws.ba_tot[0].as<NE>();
+                NE* prefix = ws.ba_prefix.as<NE>();
+                NE* nrm = BN::EXT ? prefix + out_max[0] : nullptr;      // Fp2: the second half of the prefix buffer holds the norms
+                k_ba_fwd<CB><<<grid, BA_THREADS, 0, st>>>(src, off_in, off_out, pl.NB, ws.ba_desc.as<uint32_t>(), prefix, nrm, tot0, nthr);
                 G16_LAUNCH_CHECK();
                 // inversion tree over the nthr per-thread totals
                 std::vector<uint32_t> sz{nthr};
                 while (sz.back() > 4096 && sz.size() < 4) sz.push_back((sz.back() + BA_G - 1) / BA_G);
                 for (size_t l = 0; l + 1 < sz.size(); l++) {
-                    k_ba_up<CB><<<(sz[l + 1] + BA_THREADS - 1) / BA_THREADS, BA_THREADS, 0, st>>>(ws.ba_tot[l].as<E>(), sz[l], ws.ba_pref[l].as<E>(), ws.ba_tot[l + 1].as<E>(), sz[l + 1]);
+                    k_ba_up<NF><<<(sz[l + 1] + BA_THREADS - 1) / BA_THREADS, BA_THREADS, 0, st>>>(ws.ba_tot[l].as<NE>(), sz[l], ws.ba_pref[l].as<NE>(), ws.ba_tot[l + 1].as<NE>(), sz[l + 1]);
                     G16_LAUNCH_CHECK();
                 }
-                k_ba_leaf<CB><<<(sz.back() + BA_THREADS - 1) / BA_THREADS, BA_THREADS, 0, st>>>(ws.ba_tot[sz.size() - 1].as<E>(), sz.back());
+                k_ba_leaf<NF><<<(sz.back() + BA_THREADS - 1) / BA_THREADS, BA_THREADS, 0, st>>>(ws.ba_tot[sz.size() - 1].as<NE>(), sz.back());
                 G16_LAUNCH_CHECK();
                 for (size_t l = sz.size() - 1; l-- > 0;) {
-                    k_ba_down<CB><<<(sz[l + 1] + BA_THREADS - 1) / BA_THREADS, BA_THREADS, 0, st>>>(ws.ba_tot[l].as<E>(), sz[l], ws.ba_pref[l].as<E>(), ws.ba_tot[l + 1].as<E>(), ws.ba_tot[l].as<E>(), sz[l + 1]);
+                    k_ba_down<NF><<<(sz[l + 1] + BA_THREADS - 1) / BA_THREADS, BA_THREADS, 0, st>>>(ws.ba_tot[l].as<NE>(), sz[l], ws.ba_pref[l].as<NE>(), ws.ba_tot[l + 1].as<NE>(), ws.ba_tot[l].as<NE>(), sz[l + 1]);
                     G16_LAUNCH_CHECK();
                 }
-                k_ba_bwd<CB><<<grid, BA_THREADS, 0, st>>>(src, off_out, pl.NB, ws.ba_desc.as<uint32_t>(), ws.ba_prefix.as<E>(), tot0, out, nthr);
+                k_ba_bwd<CB><<<grid, BA_THREADS, 0, st>>>(src, off_out, pl.NB, ws.ba_desc.as<uint32_t>(), prefix, nrm, tot0, out, nthr);
                 G16_LAUNCH_CHECK();
                 src = BaSrc<CB>{out, nullptr};
                 off_in = off_out;
