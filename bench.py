@@ -344,6 +344,8 @@ def run_ours(args):
     ctx = lib.Context(devices if world > 1 else 0)
     ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
     ctx.set("msm_ba_rounds", args.ba_rounds)
+    if args.g2_weight:
+        ctx.set("g2_weight", args.g2_weight)
     nc = 1 << args.log_n
     case = chain_case(nc, g1_mul=ctx.g1_fixed_base_mul, g2_mul=ctx.g2_fixed_base_mul)
     n, nw, pk = case.n, case.nw, case.pk
@@ -446,12 +448,12 @@ def run_ours(args):
             "g2": {"kernel": "bucket accumulation of the G2 MSM: k_ba_fwd / k_ba_bwd rounds + k_accumulate<G2>",
                    "achieved": g2_ops / (g2_ms * 1e-3) / 1e12, "frac": g2_ops / (g2_ms * 1e-3) / peak,
                    "frac_definition": "entries x 30 Fp mul x 272 IMAD-eq / stage time / measured IMAD peak (SURVEY 8(d))",
-                   "mults_per_entry_executed": ((1 - 0.5 ** ba_r) * 14 + 0.5 ** ba_r * 28) if ba_r > 0 else 28.0,
-                   "frac_executed": g2_ops / (g2_ms * 1e-3) / peak * (((1 - 0.5 ** ba_r) * 14 + 0.5 ** ba_r * 28) if ba_r > 0 else 28.0) / 30.0},
+                   "mults_per_entry_executed": ((1 - 0.5 ** ba_r) * 15 + 0.5 ** ba_r * 28) if ba_r > 0 else 28.0,
+                   "frac_executed": g2_ops / (g2_ms * 1e-3) / peak * (((1 - 0.5 ** ba_r) * 15 + 0.5 ** ba_r * 28) if ba_r > 0 else 28.0) / 30.0},
             "share_of_step": (g1_ms + g2_ms) / st["ms_total"],
             "note": "stage times from one extra step with the five MSMs serialised (streams=1); the timed steps overlap them, which is "
                     "where the batch-affine rounds pay: their gathers and inversion trees hide under other MSMs' multiplications "
-                    "(serialised sum 69 ms, overlapped step 58 ms)"
+                    "(serialised sum 67 ms, overlapped step 56 ms)"
                     + ("; on a group: slowest rank's time per MSM against the whole job's work" if world > 1 else "")}
     if args.log_n == 22 and world == 1 and ba_r == 4:
         roof["traffic"] = 20.8e9
@@ -755,6 +757,7 @@ def main():
     ap.add_argument("--ba-rounds", type=int, default=4, help="batch-affine rounds of the MSMs (library default 4; 0 = XYZZ accumulation only)")
     ap.add_argument("--curve", default="bn254", choices=["bn254", "bls12_377"],
                     help="bls12_377 = BASELINE config 5 (use --log-n 24); the default line is the BN254 headline")
+    ap.add_argument("--g2-weight", type=int, default=0, help="multi-GPU key placement: cost of a G2 point in hundredths of a G1 point (0 = library default by group size)")
     ap.add_argument("--no-extras", action="store_true")
     ap.add_argument("--synthetic-key", action="store_true", help="bls12_377: random bases with the pow17 infinity shape instead of the trapdoor instance (no parity, no CPU leg)")
     ap.add_argument("--no-g1-tables", action="store_true", help="bls12_377: a table of multiples for G2.B only")

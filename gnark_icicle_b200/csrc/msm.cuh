@@ -103,6 +103,11 @@ inline int msm_pre_choose_c(uint64_t n, bool g2, int forced = 0) {
     // 2^21: 6.74 / 6.36 / 7.31 / 7.25 / 6.34 -- the cost model below overrates 18 and 19
 #if G16_CURVE != 377   // measured for the 8-limb field only
     if (!g2 && n < 1500000) return n < 750000 ? 16 : 17;
+    // G2 pieces (tools/prof_piece.py, with the batch-affine rounds; ms for c = 16 / 17 / 18 / 19 / 20): 730 k points 7.57 / 7.60 / 8.59 /
+    // 8.60 / 8.47, 930 k: 8.99 / 8.52 / 9.71 / 9.82 / 9.38, 1.4 M: 11.66 / 11.39 / 12.95 / 12.37 / 11.92, 2.8 M: 19.85 / 19.26 / 21.10 /
+    // 20.52 / 18.96 -- the bucket reduction (2 Fp2 XYZZ additions per bucket, a dependent chain of ~100) does not shrink
+    // with the piece, the cost model below (per-entry costs from before the rounds) picks 20 for all of them
+    if (g2 && n < 2000000) return 17;
 #endif
     int best = MSM_PRE_CMIN; double best_cost = 1e300;
     for (int c = MSM_PRE_CMIN; c <= MSM_PRE_CMAX; c++) {

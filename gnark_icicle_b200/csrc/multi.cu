@@ -257,8 +257,11 @@ void multi_pk_upload(g16_ctx* ctx, const g16_pk_desc* d, const Src* src, uint64_
     gp.active = L >= 2 * mg.g + 4 ? mg.n : 1;   // every rank needs a few stages on either side of the exchanges
     const uint64_t lens[5] = {d->n_a, d->n_b, d->n_k, d->n_z < d->domain_n ? d->n_z : d->domain_n - 1, d->n_b2};
     // cost of a G2 point in G1 points: "g2_weight" if set, else by group size -- the smaller the pieces, the more a G2 piece
-    // pays for its smaller window and its exposed bucket reduction (measured per piece at N = 2 / 4 / 8: ~3.0 / 3.4 / 4.0)
-    const double w2 = ctx->g2_weight > 0 ? ctx->g2_weight / 100.0 : (gp.active >= 8 ? 4.0 : gp.active >= 4 ? 3.4 : 3.0);
+    // pays for its smaller window and its exposed bucket reduction (measured per piece at N = 2 / 4 / 8: ~3.0 / 3.4 / 4.0
+    // before the G2 rounds moved their inversions to Fp, which took 9 % off a G2 MSM: swept again at N = 2, best at 2.75;
+    // the other two scaled by the same factor, then by what the 17-bit tables of small G2 pieces gained; per-piece times
+    // from tools/prof_piece.py: N = 4: 1.6 M G2 points ~12.7 ms against 5 M G1 points ~13.2; N = 8: 0.73 M ~7.6 against 2.7 M ~8.1)
+    const double w2 = ctx->g2_weight > 0 ? ctx->g2_weight / 100.0 : (gp.active >= 8 ? 3.5 : gp.active >= 4 ? 3.0 : 2.75);
     std::vector<PkRanges> place = place_key(lens, gp.active, w2, d->domain_n);
     PkRanges none;
     for (int i = 0; i < 5; i++) none.lo[i] = none.hi[i] = 0;
