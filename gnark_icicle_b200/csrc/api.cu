@@ -48,23 +48,26 @@ void copy_in(g16_ctx* ctx, void* dst, const Src& src, size_t bytes, cudaStream_t
     G16_CUDA(cudaStreamSynchronize(st));   // the staging buffers are reused by the next array
 }
 
+// pad_front: that many points at infinity in front of the array (the table then has n + pad_front columns)
 template <class C>
-void upload_bases(g16_ctx* ctx, DevBuf& dst, const Src& src, uint64_t n, int& pre_c, cudaStream_t st) {
+void upload_bases(g16_ctx* ctx, DevBuf& dst, const Src& src, uint64_t n, int& pre_c, cudaStream_t st, uint64_t pad_front = 0) {
     constexpr bool IS_G2 = sizeof(typename C::E) > sizeof(Fp::T);
-    const size_t row = (size_t)n * sizeof(typename C::Aff);
+    const uint64_t cols = n + pad_front;
+    const size_t row = (size_t)cols * sizeof(typename C::Aff);
     pre_c = 0;
-    if (ctx->msm_precompute && (IS_G2 || ctx->msm_precompute_g1) && n >= PRECOMPUTE_MIN_POINTS) {
-        const int c = msm_pre_choose_c(n, IS_G2, ctx->msm_pre_c);
+    if (ctx->msm_precompute && (IS_G2 || ctx->msm_precompute_g1) && cols >= PRECOMPUTE_MIN_POINTS) {
+        const int c = msm_pre_choose_c(cols, IS_G2, ctx->msm_pre_c);
         const size_t total = row * (size_t)(255 / c + 1);
         size_t free_b = 0, total_b = 0;
         G16_CUDA(cudaMemGetInfo(&free_b, &total_b));
         if (total <= free_b / 2) pre_c = c;
     }
     dst.reserve(pre_c ? row * (size_t)(255 / pre_c + 1) : (row ? row : 16));
-    copy_in(ctx, dst.p, src, row, st);
+    if (pad_front) G16_CUDA(cudaMemsetAsync(dst.p, 0, (size_t)pad_front * sizeof(typename C::Aff), st));   // (0, 0) = infinity
+    copy_in(ctx, (char*)dst.p + (size_t)pad_front * sizeof(typename C::Aff), src, (size_t)n * sizeof(typename C::Aff), st);
     if (pre_c) {
-        if constexpr (IS_G2) msm_g2_precompute(dst.as<G2::Aff>(), n, pre_c, st);
-        else msm_g1_precompute(dst.as<G1::Aff>(), n, pre_c, st);
+        if constexpr (IS_G2) msm_g2_precompute(dst.as<G2::Aff>(), cols, pre_c, st);
+        else msm_g1_precompute(dst.as<G1::Aff>(), cols, pre_c, st);
     }
 }
 template <class C>
@@ -273,8 +276,21 @@ void pk_upload_ranges(g16_ctx* ctx, const g16_pk_desc* d, const Src* src, const 
         touch(mk, lo, hi);
         if (pk.w_hi <= pk.w_lo) pk.w_lo = pk.w_hi = 0;
         pk.n_k = hi - lo;
-        upload_bases<G1>(ctx, pk.g1_k, src[2].at(lo * G1SZ), pk.n_k, pk.pre_c[G16_OUT_KRS_K], st);
-        upload(pk.map_k, mk.data() + lo, pk.n_k * 4, st);
+        // G1.K usually covers the wires of G1.A from some wire on (all private wires against all wires with a non-zero A
+        // polynomial): padded with that many points at infinity in front, its array lines up with G1.A position by
+        // position, and its MSM reuses G1.A's digits and bucket sort (the way bs1 reuses bs2's) instead of sorting the same
+        // scalars a second time.  Whole-array uploads only (shards and the ranks of a group cut A and K differently).
+        pk.k_pad = 0;
+        {
+            const uint64_t la = rg.lo[G16_OUT_AR], ha = rg.hi[G16_OUT_AR];
+            const uint64_t pad = (ha - la) - (hi - lo);
+            bool tail = la == 0 && ha == d->n_a && lo == 0 && hi == d->n_k && d->n_k >= PRECOMPUTE_MIN_POINTS && d->n_a >= d->n_k && pad <= 64;
+            for (uint64_t i = 0; tail && i < d->n_k; i++) tail = mk[i] == ma[pad + i];
+            if (tail) pk.k_pad = pad;
+        }
+        upload_bases<G1>(ctx, pk.g1_k, src[2].at(lo * G1SZ), pk.n_k, pk.pre_c[G16_OUT_KRS_K], st, pk.k_pad);
+        if (pk.k_pad) { pk.n_k += pk.k_pad; pk.same_ak = true; upload(pk.map_k, ma.data(), pk.n_k * 4, st); }
+        else { pk.same_ak = false; upload(pk.map_k, mk.data() + lo, pk.n_k * 4, st); }
         lo = rg.lo[G16_OUT_KRS_HZ]; hi = rg.hi[G16_OUT_KRS_HZ];
         pk.n_z = hi - lo;
         pk.z_off = lo;
@@ -413,7 +429,8 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
         msm_g1_enqueue(ctx->ws[G16_OUT_BS1], W_d, pk.map_b.as<uint32_t>(), pk.g1_b.as<G1::Aff>(), pk.n_b, ctx->msm_c, ctx->msm_waves, s, plan[1], &ms[1], overlap ? ctx->tails[1] : nullptr, pre(G16_OUT_BS1),
                        pk.same_b && pk.n_b == pk.n_b2 ? &ctx->ws[G16_OUT_BS2] : nullptr, acc_gate); });   // same scalars, same map: reuse the G2 MSM's sort
     if (phase != 2) run(G16_OUT_KRS_K, sK, [&](cudaStream_t s) {
-        msm_g1_enqueue(ctx->ws[G16_OUT_KRS_K], W_d, pk.map_k.as<uint32_t>(), pk.g1_k.as<G1::Aff>(), pk.n_k, ctx->msm_c, ctx->msm_waves, s, plan[2], &ms[2], overlap ? ctx->tails[2] : nullptr, pre(G16_OUT_KRS_K), nullptr, acc_gate); });
+        msm_g1_enqueue(ctx->ws[G16_OUT_KRS_K], W_d, pk.map_k.as<uint32_t>(), pk.g1_k.as<G1::Aff>(), pk.n_k, ctx->msm_c, ctx->msm_waves, s, plan[2], &ms[2], overlap ? ctx->tails[2] : nullptr, pre(G16_OUT_KRS_K),
+                       pk.same_ak ? &ctx->ws[G16_OUT_AR] : nullptr, acc_gate); });   // same wires, same positions: reuse G1.A's sort
     if (phase == 1) {
         for (int i = 0; i < 5; i++) ctx->pend_plan[i] = plan[i];
         return;
@@ -439,7 +456,7 @@ void prove_device(g16_ctx* ctx, PkDev& pk, const Fr::T* W_d, Fr::T* a_d, Fr::T* 
         G16_CUDA(cudaEventElapsedTime(&stats->ms_compute_h, ev[12], ev[13]));
         for (int i = 0; i < 5; i++) {
             G16_CUDA(cudaEventElapsedTime(&stats->ms_msm[i], ev[1 + i], ev[6 + i]));
-            stats->msm_c[i] = plan[i].c; stats->msm_windows[i] = plan[i].Wd; stats->msm_n[i] = ns[i];
+            stats->msm_c[i] = plan[i].c; stats->msm_windows[i] = plan[i].Wd; stats->msm_n[i] = ns[i] - (i == G16_OUT_KRS_K ? pk.k_pad : 0);
             if (ns[i]) G16_CUDA(cudaEventElapsedTime(&stats->ms_accumulate[i], ev[16 + 2 * i], ev[17 + 2 * i]));
         }
         G16_CUDA(cudaEventElapsedTime(&stats->ms_total, ev[0], ev[14]));

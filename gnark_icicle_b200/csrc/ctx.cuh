@@ -30,6 +30,8 @@ struct PkDev {
     DevBuf g1_a, g1_b, g1_k, g1_z, g2_b;
     DevBuf map_a, map_b, map_k, map_b2;   // u32 wire index per base (map_b2 only when the G1.B and G2.B slices differ)
     uint64_t n_a = 0, n_b = 0, n_k = 0, n_z = 0, n_b2 = 0;
+    uint64_t k_pad = 0;          // points at infinity in front of G1.K (included in n_k) that line it up with G1.A
+    bool same_ak = false;        // ... so that the K MSM reuses the A MSM's sort
     int pre_c[5] = {0, 0, 0, 0, 0}; // window bits of the precomputed-multiples table per MSM (G16_OUT_* order); 0 = none
     PkRanges ranges = {};         // the slices as requested at upload
     uint64_t z_off = 0;           // first h index of this shard's Z slice

@@ -170,3 +170,48 @@ def test_precomputed_tables_give_the_same_points_as_the_window_path(ctx, kind):
             assert_limbs_equal(got[0], case.expected_points(h), "precomputed mode vs trapdoor")
     finally:
         pk.free_device()
+
+
+# ---------------------------------------------------------------- G1.K lined up with G1.A (shared sort)
+@pytest.mark.parametrize("shape", ["tail", "tail_pad4", "hole", "k_longer", "k_index"])
+def test_krs_msm_reusing_the_ar_sort_matches_oracle(ctx, shape):
+    """When the wires of G1.K are a tail of the wires of G1.A, g16_pk_upload pads G1.K with points at infinity so that the
+    two arrays line up and the krs MSM reuses the ar MSM's digits and bucket sort (csrc/api.cu pk_upload_ranges).  All
+    five points against the oracle's bucket-method MSMs for keys where that applies (pad 1 as in every gnark key with
+    one public input; pad 4) and for keys where it must not (a wire missing from A in the middle; K longer than A; an
+    explicit k_index map)."""
+    nc = (1 << 14) + 37
+    case = ChainCase(nc, seed=73)
+    pk = case.pk
+    nw = case.nw
+    inf_a, inf_b = case.inf_a.copy(), case.inf_b.copy()
+    g1_a, g1_k, k_index = pk.g1_a, pk.g1_k, None
+    wk = case.W[2:]
+    if shape == "tail_pad4":            # five public wires: K starts at wire 5, A still lacks only wire 1
+        g1_k, wk = pk.g1_k[3:], case.W[5:]
+    elif shape == "hole":               # wire 100 has a zero A polynomial: same lengths, maps differ from there on
+        pos = int(np.count_nonzero(~inf_a[:100]))
+        inf_a[100] = True
+        g1_a = np.delete(pk.g1_a, pos, axis=0)
+    elif shape == "k_longer":           # wires 5..9 missing from A: K (nw - 2 points) is longer than A (nw - 6)
+        pos = int(np.count_nonzero(~inf_a[:5]))
+        inf_a[5:10] = True
+        g1_a = np.delete(pk.g1_a, np.arange(pos, pos + 5), axis=0)
+    elif shape == "k_index":            # an explicit map (what a key with commitments passes): every other private wire
+        k_index = np.arange(2, nw, 2, dtype=np.uint32)
+        g1_k, wk = pk.g1_k[::2], case.W[2::2]
+        assert len(g1_k) == len(k_index)
+    handle = ctx.pk_upload(pk.domain_n, g1_a, pk.g1_b, g1_k, pk.g1_z, pk.g2_b, inf_a.astype(np.uint8), inf_b.astype(np.uint8), nw,
+                           k_index=k_index)
+    try:
+        pts, st = ctx.prove(handle, case.W, case.a, case.b, case.c)
+        pts2, _ = ctx.prove(handle, case.W, case.a, case.b, case.c)
+    finally:
+        ctx.pk_free(handle)
+    h = ocpu.compute_h(case.a, case.b, case.c, case.n)
+    wa, wb = case.W[~inf_a], case.W[~inf_b]
+    want = np.concatenate([ocpu.msm_g1(g1_a, wa), ocpu.msm_g1(pk.g1_b, wb), ocpu.msm_g1(g1_k, wk),
+                           ocpu.msm_g1(pk.g1_z, h[: case.n - 1]), ocpu.msm_g2(pk.g2_b, wb)])
+    assert_limbs_equal(pts, want, f"{shape}: prove points vs CPU Pippenger")
+    assert_limbs_equal(pts2, pts, f"{shape}: second prove on the same key")
+    assert list(st["msm_n"][:3]) == [len(g1_a), len(pk.g1_b), len(g1_k)]     # the padding does not show in the stats
