@@ -12,10 +12,7 @@ from .curve import R, inv
 from .ntt import Domain, bit_reverse_list, compute_h
 from .msm import batch_scalar_mul_gen, msm_pippenger
 from . import commitment as CM
-if C.NAME == "bn254":
-    from .pairing import pairing_product
-else:
-    pairing_product = None   # BLS12-377: no restated pairing; proofs are checked on the exponent side (trapdoor)
+from .pairing import pairing_product      # curve-generic like this module (BN254 optimal ate / BLS12-377 ate)
 
 
 def filter_heap(slice_, first_index, to_remove):
@@ -154,7 +151,7 @@ def setup(cs, rng, tw=None):
     pk.g2_beta, pk.g2_delta = g2[len(B_nz)], g2[len(B_nz) + 1]
     vk.g2_delta, vk.g2_gamma = g2[len(B_nz) + 1], g2[len(B_nz) + 2]
     vk.g1_alpha, vk.g2_beta = pk.g1_alpha, pk.g2_beta
-    vk.e = pairing_product([(vk.g1_alpha, vk.g2_beta)]) if pairing_product else None   # vk.Precompute setup.go:353-362
+    vk.e = pairing_product([(vk.g1_alpha, vk.g2_beta)])   # vk.Precompute setup.go:353-362
     pk.domain = d
     pk.nb_public = nb_pub
     scal = dict(A=A_nz, B=B_nz, Z=Zbr, K=pkK, tw=tw, CK=ckK, sigma=sigmas)
@@ -275,8 +272,6 @@ def proof_bytes(proof):
 def verify(proof, vk, public_witness, hasher=None):
     """verify.go:49-148: e(Krs,-delta) e(Ar,Bs) e(kSum,-gamma) == e(alpha,beta), where kSum also takes the BSB22
     commitments and the commitment wires re-derived by hashing (verify.go:82-126)."""
-    if pairing_product is None:
-        raise NotImplementedError("the restated pairing check exists for BN254 only")
     pacc = getattr(vk, "public_and_commitment_committed", [])
     nb_public_vars = len(vk.g1_k) - len(pacc)
     if len(public_witness) != nb_public_vars - 1:

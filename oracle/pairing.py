@@ -1,17 +1,32 @@
-"""BN254 optimal-ate pairing on Python ints (oracle; test infrastructure only).
+"""Ate pairings of the two curves on Python ints (oracle; test infrastructure only).
 
 Used only by the restated verifier (backend/groth16/bn254/verify.go:49-148:
 curve.MillerLoop :77,:131, curve.FinalExponentiation :141, vk.Precompute
-setup.go:353-362).  Any correct non-degenerate bilinear map accepts exactly the
-same proofs, so this follows the textbook construction: Fp12 = Fp[w]/(w^12 -
-18 w^6 + 82), G2 untwisted into E(Fp12), Miller loop over 6x+2 with the two
-Frobenius correction steps, final exponent (p^12-1)/r.
+setup.go:353-362; backend/groth16/bls12-377/verify.go is the same file over the
+other curve package).  Any correct non-degenerate bilinear map accepts exactly the
+same proofs, so this follows the textbook construction: Fp12 = Fp[w]/(modulus of
+degree 12), G2 untwisted into E(Fp12), Miller loop with generic line functions,
+final exponent (p^12-1)/r.
+  BN254:     u^2 = -1, xi = 9 + u = w^6  =>  w^12 = 18 w^6 - 82; loop over 6x+2 with the
+             two Frobenius correction steps (optimal ate).
+  BLS12-377: u^2 = -5, xi = u = w^6 (gnark-crypto's tower: v^3 = u, w^2 = v)  =>  w^12 = -5;
+             twist y^2 = x^3 + 1/u (D type), loop over the seed x = 0x8508c00000000001 (ate
+             pairing with T = t - 1 = x), no correction steps.
+Like the rest of the oracle the module is curve-generic through the alias package
+(oracle.pairing = BN254, oracle.bls12_377.pairing = BLS12-377).
 """
-from .curve import P, R, inv
+from .curve import NAME, P, R, inv
 
-_MOD = (82, 0, 0, 0, 0, 0, -18, 0, 0, 0, 0, 0)   # w^12 = 18 w^6 - 82
-ATE_LOOP = 29793968203157093288                  # 6x+2, x = 4965661367192848881
-LOG_ATE = 63
+if NAME == "bn254":
+    _MOD = (82, 0, 0, 0, 0, 0, -18, 0, 0, 0, 0, 0)   # w^12 = 18 w^6 - 82
+    ATE_LOOP = 29793968203157093288                  # 6x+2, x = 4965661367192848881
+    LOG_ATE = 63
+    _XI_SHIFT = 9                                    # u = w^6 - 9
+else:
+    _MOD = (5, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0)      # w^12 = u^2 = -5
+    ATE_LOOP = 0x8508c00000000001                    # the curve seed x
+    LOG_ATE = 62                                     # bits below the leading one
+    _XI_SHIFT = 0                                    # u = w^6
 
 
 def f12(c0=0, *rest):
@@ -37,11 +52,12 @@ def f12_mul(a, b):
         if x:
             for j, y in enumerate(b):
                 t[i + j] += x * y
-    for k in range(22, 11, -1):          # reduce w^k = w^(k-12) * (18 w^6 - 82)
+    for k in range(22, 11, -1):          # reduce w^k = w^(k-12) * (-_MOD[6] w^6 - _MOD[0])
         c = t[k]
         if c:
-            t[k - 6] += 18 * c
-            t[k - 12] -= 82 * c
+            if _MOD[6]:
+                t[k - 6] -= _MOD[6] * c
+            t[k - 12] -= _MOD[0] * c
     return tuple(x % P for x in t[:12])
 
 
@@ -98,10 +114,11 @@ _W3 = f12_mul(_W2, _W)
 
 
 def _twist(q):
-    """E'(Fp2) -> E(Fp12); u = w^6 - 9."""
+    """E'(Fp2) -> E(Fp12): (x, y) -> (x w^2, y w^3) with u = w^6 - _XI_SHIFT embedded.  With xi = w^6:
+    (y w^3)^2 = y^2 xi and (x w^2)^3 = x^3 xi, so y^2 = x^3 + b/xi (both twists are of D type)."""
     (x0, x1), (y0, y1) = q
-    nx = f12(x0 - 9 * x1, 0, 0, 0, 0, 0, x1)
-    ny = f12(y0 - 9 * y1, 0, 0, 0, 0, 0, y1)
+    nx = f12(x0 - _XI_SHIFT * x1, 0, 0, 0, 0, 0, x1)
+    ny = f12(y0 - _XI_SHIFT * y1, 0, 0, 0, 0, 0, y1)
     return (f12_mul(nx, _W2), f12_mul(ny, _W3))
 
 
@@ -146,7 +163,7 @@ def _line(p1, p2, t):
 
 
 def miller_loop(p_g1, q_g2):
-    """f_{6x+2,Q}(P) with Frobenius corrections; no final exponentiation."""
+    """f_{T,Q}(P), T = ATE_LOOP (BN254: with the Frobenius corrections); no final exponentiation."""
     if p_g1 is None or q_g2 is None:
         return F12_ONE
     Q = _twist(q_g2)
@@ -159,6 +176,8 @@ def miller_loop(p_g1, q_g2):
         if ATE_LOOP & (1 << i):
             f = f12_mul(f, _line(Rp, Q, Pt))
             Rp = _add(Rp, Q)
+    if NAME != "bn254":
+        return f
     Q1 = (f12_pow(Q[0], P), f12_pow(Q[1], P))
     nQ2 = (f12_pow(Q1[0], P), f12_sub(F12_ZERO, f12_pow(Q1[1], P)))
     f = f12_mul(f, _line(Rp, Q1, Pt))

@@ -178,7 +178,7 @@ def test_prove_matches_oracle_bytes(case):
     else:
         cs, _ = orcs.mimc_chain(200, rng, power=17)
         w = _solve_chain(cs, rng)
-    pk_py, _, _ = og.setup(cs, rng)
+    pk_py, vk_py, _ = og.setup(cs, rng)
     r, s = rng.field(R), rng.field(R)
     parts = og.prove_parts(cs, pk_py, w)
     want = og.assemble(pk_py, parts, r, s)
@@ -191,6 +191,11 @@ def test_prove_matches_oracle_bytes(case):
         assert g2_pts(points[48:]) == [parts["bs2"]]
         proof = g16.Prove(None, pk, sol, g16.WithIcicleAcceleration(), g16.WithRandomness(fr_arr([r])[0], fr_arr([s])[0]))
         assert proof.raw() == og.proof_bytes(want)
+        # and the GPU's proof passes the restated pairing check of verify.go (oracle.bls12_377.pairing)
+        raw = proof.raw()
+        got = {"ar": C.g1_from_bytes(raw[:96]), "bs": C.g2_from_bytes(raw[96:288]), "krs": C.g1_from_bytes(raw[288:384])}
+        assert og.verify(got, vk_py, w[1:cs.nb_public])
+        assert not og.verify(got, vk_py, [(x + 1) % R for x in w[1:cs.nb_public]])
     finally:
         pk.free_device()
 

@@ -96,7 +96,7 @@ def test_pippenger_matches_naive_and_trapdoor():
     assert omsm.msm_pippenger(p2, ss[:8], c=5, g2=True) == want2
 
 
-# ---- Groth16 algebra: exponent-side check with the toxic waste (no pairing restated for this curve)
+# ---- Groth16 algebra: exponent-side check with the toxic waste, then the restated pairing check
 def test_proof_satisfies_the_exponent_side_equations():
     rng = Xoshiro(SEED_BASE + 53)
     cs, _ = orcs.mimc_chain(22, rng, power=17)
@@ -118,6 +118,36 @@ def test_proof_satisfies_the_exponent_side_equations():
     Cexp = (sum(x * y for x, y in zip(w[pk.nb_public:], scal["K"])) + sum(x * y for x, y in zip(h, scal["Z"]))
             + s * A + r * B - r * s * tw.delta) % R
     assert proof["krs"] == C.g1_mul(C.G1_GEN, Cexp)
+
+
+def test_pairing_is_bilinear_and_nondegenerate():
+    from oracle.bls12_377 import pairing as PR
+    a, b = 0x1234567, 0x89abcdef1
+    e = PR.pairing_product([(C.g1_mul(C.G1_GEN, a), C.g2_mul(C.G2_GEN, b))])
+    base = PR.pairing_product([(C.G1_GEN, C.G2_GEN)])
+    assert e == PR.f12_pow(base, a * b % R) and base != PR.F12_ONE and PR.f12_pow(base, R) == PR.F12_ONE
+    assert PR.pairing_product([(C.g1_mul(C.G1_GEN, a), C.G2_GEN), (C.g1_neg(C.G1_GEN), C.g2_mul(C.G2_GEN, a))]) == PR.F12_ONE
+
+
+def test_proofs_verify_under_the_pairing_check():
+    """verify.go:49-148 restated over BLS12-377: the oracle prover's proofs are accepted, a wrong public input, a tampered
+    point and a proof for another witness are not (cubic: examples/cubic/cubic_test.go:23-38; pow17 chain)."""
+    rng = Xoshiro(SEED_BASE + 57)
+    cs, w = orcs.cubic_circuit(), orcs.cubic_witness(3, 35)
+    pk, vk, _ = og.setup(cs, rng)
+    proof = og.prove(cs, pk, w, rng.field(R), rng.field(R))
+    assert og.verify(proof, vk, [35])
+    assert not og.verify(proof, vk, [36])
+    bad = dict(proof)
+    bad["krs"] = C.g1_add(proof["krs"], C.G1_GEN)
+    assert not og.verify(bad, vk, [35])
+    cs2, _ = orcs.mimc_chain(31, rng, power=17)
+    pk2, vk2, _ = og.setup(cs2, rng)
+    w2 = orcs.mimc_chain_witness(cs2, rng.field(R), rng.field(R))
+    w2[1] = sum(cf * w2[i] for cf, i in cs2.constraints[-1][0]) % R
+    proof2 = og.prove(cs2, pk2, w2, rng.field(R), rng.field(R))
+    assert og.verify(proof2, vk2, [w2[1]])
+    assert not og.verify(proof2, vk2, [(w2[1] + 1) % R])
 
 
 # ---- the library: BLS12-377 entry points and host helpers
