@@ -335,6 +335,77 @@ struct Field {
         return pow(a, e, N);
     }
     G16_HD static T from_u64(uint64_t v) { T t = zero(); t.l[0] = (uint32_t)v; t.l[1] = (uint32_t)(v >> 32); return to_mont(t); }
+
+    // The same inverse by the binary extended Euclidean algorithm (right shifts only, the modulus is odd): for the
+    // inversion-tree leaves of the batch-affine rounds (msm_ba.cuh), where ONE thread's chain is the latency of the whole
+    // round -- ~0.7 log2(p) iterations of limb-wise shifts, masks and carry chains instead of the ~1.5 log2(p) dependent
+    // multiplications of the Fermat power.  Branch-free inside an iteration (the lanes of a warp only differ in their
+    // iteration count).  Input and output canonical Montgomery images; inv_binary(0) = 0.
+    // Invariants: x1 * a = u and x2 * a = v (mod p) on the plain integer a behind the image; v stays odd; u reaches 0
+    // with v = gcd = 1, so x2 = a^-1.  One iteration: if u is odd, make it even (u -= v after ordering them, x1 -= x2),
+    // then strip all k <= 31 trailing zero bits of u at once and divide x1 by 2^k mod p: x1 = (x1 + m p) >> k with
+    // m = x1 * (-p^-1) mod 2^k (one row of a Montgomery reduction).
+    // The integer handed in is aR, so x2 = a^-1 R^-1: two to_mont bring it to a^-1 R.
+    G16_HD_COLD static T inv_binary(const T& a) {
+        uint32_t u[N], v[N], x1[N], x2[N];
+#pragma unroll
+        for (int i = 0; i < N; i++) { u[i] = a.l[i]; v[i] = P::mod(i); x1[i] = 0; x2[i] = 0; }
+        x1[0] = 1;
+        for (int it = 0; it < 64 * N; it++) {                 // bitlen(u) + bitlen(v) drops every iteration: < 64 N of them
+            uint32_t nz = 0;
+#pragma unroll
+            for (int i = 0; i < N; i++) nz |= u[i];
+            if (!nz) break;
+            const uint32_t odd = 0u - (u[0] & 1u);
+            // lt = odd and u < v (borrow of u - v)
+            uint32_t br = 0;
+#pragma unroll
+            for (int i = 0; i < N; i++) { const uint64_t d = (uint64_t)u[i] - v[i] - br; br = (uint32_t)(d >> 32) & 1u; }
+            const uint32_t lt = odd & (0u - br);
+#pragma unroll
+            for (int i = 0; i < N; i++) {                     // conditional swap (u, v), (x1, x2)
+                uint32_t t = (u[i] ^ v[i]) & lt; u[i] ^= t; v[i] ^= t;
+                t = (x1[i] ^ x2[i]) & lt; x1[i] ^= t; x2[i] ^= t;
+            }
+            // odd: u -= v (now u >= v), x1 -= x2 mod p
+            br = 0;
+#pragma unroll
+            for (int i = 0; i < N; i++) { const uint64_t d = (uint64_t)u[i] - (v[i] & odd) - br; u[i] = (uint32_t)d; br = (uint32_t)(d >> 32) & 1u; }
+            br = 0;
+#pragma unroll
+            for (int i = 0; i < N; i++) { const uint64_t d = (uint64_t)x1[i] - (x2[i] & odd) - br; x1[i] = (uint32_t)d; br = (uint32_t)(d >> 32) & 1u; }
+            const uint32_t fix = 0u - br;
+            uint32_t cy = 0;
+#pragma unroll
+            for (int i = 0; i < N; i++) { const uint64_t d = (uint64_t)x1[i] + (P::mod(i) & fix) + cy; x1[i] = (uint32_t)d; cy = (uint32_t)(d >> 32); }
+            // u is even now (or zero): strip k trailing zero bits, 1 <= k <= 31 (k = 0 only when u became 0: nothing moves)
+            uint32_t low = u[0] | 0x80000000u;                // a zero low limb moves 31 bits now and the rest next time
+            int k = 0;
+#ifdef __CUDA_ARCH__
+            k = __ffs((int)low) - 1;
+#else
+            k = __builtin_ctz(low);
+#endif
+            if (k) {
+#pragma unroll
+                for (int i = 0; i < N - 1; i++) u[i] = (u[i] >> k) | (u[i + 1] << (32 - k));
+                u[N - 1] >>= k;
+                // x1 / 2^k mod p
+                const uint32_t m = (x1[0] * P::INV) & ((1u << k) - 1u);
+                uint64_t c = 0;
+                uint32_t t[N + 1];
+#pragma unroll
+                for (int i = 0; i < N; i++) { c += (uint64_t)m * P::mod(i) + x1[i]; t[i] = (uint32_t)c; c >>= 32; }
+                t[N] = (uint32_t)c;
+#pragma unroll
+                for (int i = 0; i < N; i++) x1[i] = (t[i] >> k) | (t[i + 1] << (32 - k));
+            }
+        }
+        T r;
+#pragma unroll
+        for (int i = 0; i < N; i++) r.l[i] = x2[i];
+        return to_mont(to_mont(r));
+    }
 };
 
 // Same field, but multiplication is a real (register-ABI) call on the device: the curve kernels issue 10-30

@@ -287,7 +287,8 @@ template <class NF>
 __global__ void __launch_bounds__(BA_THREADS) k_ba_leaf(typename NF::T* __restrict__ a, uint32_t n) {
     typedef typename NF::T NE;
     const uint32_t i = blockIdx.x * BA_THREADS + threadIdx.x;
-    if (i < n) ba_st<NE>(a + i, NF::inv(NF::canon(ba_ld<NE>(a + i))));
+    // binary Euclid, not the Fermat power: this one thread's chain is the latency of the round (0.17 ms as a power)
+    if (i < n) ba_st<NE>(a + i, NF::inv_binary(NF::canon(ba_ld<NE>(a + i))));
 }
 // down: inv_grp[u] = inverse of the group's product  ->  inv[e] for every element of the group (in and inv may alias)
 template <class NF>
