@@ -880,8 +880,22 @@ void msm_enqueue(MsmWorkspace& ws, const Fr::T* scalars_d, const uint32_t* map_d
     // every round pays a fixed inversion-tree latency (~0.4-0.6 ms, one Fermat chain): small MSMs -- the pieces of a
     // multi-GPU prove, which have little else running beside them -- get fewer rounds
     int ba_rounds = (ws.ba_rounds > 0 && !ws.ba_no_memory && n >= (1u << 17)) ? (ws.ba_rounds > 6 ? 6 : ws.ba_rounds) : 0;
-    if (ba_rounds > 3 && total_max < (32u << 20)) ba_rounds = 3;
-    if (ba_rounds > 2 && total_max < (6u << 20)) ba_rounds = 2;
+    static const bool ba_noclamp = getenv("G16_BA_NOCLAMP") != nullptr;   // experiments (tools/prof_piece.py --ba): take "msm_ba_rounds" as given
+    if (!ba_noclamp) {
+        // measured alone on a B200 (tools/prof_piece.py --ba 1 2 3 4 5 with G16_BA_NOCLAMP=1; ms for 1 / 2 / 3 / 4 rounds).  G1: 2^18 points
+        // 1.73 / 1.85 / 2.04 / 2.29, 2^19: 2.38 / 2.61 / 2.73 / 2.93, 2^20: 3.78 / 3.88 / 4.04 / 4.19, 2.7 M: 7.58 / 7.48 / 7.49 / 7.79,
+        // 4.2 M: 11.19 / 10.86 / 10.78 / 10.99.  G2: 0.73 M 7.86 / 7.32 / 7.33 / 7.38, 1.4 M: 12.69 / 11.39 / 11.12 / 11.11, 2.8 M:
+        // 21.54 / 19.44 / 18.49 / 18.60.  With five MSMs in flight the multiplication count matters more than the tree latency,
+        // which is why the large arrays of a whole key keep 4 rounds (prove at 2^22: 57.7 ms with 3 + 3, 56.4 with 4 + 4).
+        if (IS_G2) {
+            if (ba_rounds > 3 && total_max < (32u << 20)) ba_rounds = 3;
+            if (ba_rounds > 2 && total_max < (6u << 20)) ba_rounds = 2;
+        } else {
+            if (ba_rounds > 3 && total_max < (32u << 20)) ba_rounds = 3;
+            if (ba_rounds > 2 && total_max < (20u << 20)) ba_rounds = 2;
+            if (ba_rounds > 1 && total_max < (12u << 20)) ba_rounds = 1;
+        }
+    }
     // the gate exists for the long-lived CTAs of a direct XYZZ accumulation (~180 entries per thread); the kernels of the
     // batch-affine rounds are short-lived, and after >= 3 rounds so is the accumulation that follows them
     if (acc_gate && ba_rounds < 3) G16_CUDA(cudaStreamWaitEvent(st, acc_gate, 0));

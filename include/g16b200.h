@@ -80,7 +80,8 @@ const char* g16_last_error(const g16_ctx* ctx);
  * "stage_threads" (copier threads that stage PAGEABLE caller memory -- e.g. Go heap slices -- into the context's pinned
  * ring; 0 = half of the host cores divided by the GPU count, between 2 and 8; page-locked buffers are DMA'd directly),
  * "msm_ba_rounds" / "msm_ba_rounds_g1" / "msm_ba_rounds_g2" (rounds of batch-affine pair additions that pre-reduce the
- * sorted bucket entries before the XYZZ accumulation, default 4; 0 = off; applies to MSMs of at least 2^17 points),
+ * sorted bucket entries before the XYZZ accumulation, default 4; 0 = off; applies to MSMs of at least 2^17 points; an upper
+ * bound: small MSMs take fewer -- G1 below 12 M / 20 M / 32 M bucket entries 1 / 2 / 3, G2 below 6 M / 32 M 2 / 3),
  * "g2_weight" (multi-GPU key placement: cost of a G2 point in hundredths of a G1 point; 0 = by group size, 275 / 300 / 350 for 2 / 4 / 8 GPUs; before the upload) */
 int g16_ctx_set(g16_ctx* ctx, const char* key, int64_t value);
 /* total kernels launched by this library in this process (bench.py's gpu_launches evidence) */

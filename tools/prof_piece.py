@@ -19,6 +19,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--n", type=int, default=900000)
 ap.add_argument("--g2", action="store_true")
 ap.add_argument("--runs", type=int, default=2)
+ap.add_argument("--ba", type=int, nargs="*", default=[-1], help="msm_ba_rounds values to try (-1 = library default)")
 ap.add_argument("--pre-c", type=int, nargs="*", default=[0], help="window bits of the table (0 = the library's choice); several values: one upload each")
 args = ap.parse_args()
 dev = torch.device("cuda:0")
@@ -42,13 +43,16 @@ ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
 for c in args.pre_c:
     ctx.set("msm_pre_c", c)
     h = ctx.bases_upload_dev(bases.data_ptr(), args.n, g2=args.g2)
-    best = 1e9
-    for _ in range(args.runs):
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(ext)
-        ctx.msm_resident_dev(h, s.data_ptr(), g2=args.g2)
-        e1.record(ext)
-        torch.cuda.synchronize()
-        best = min(best, e0.elapsed_time(e1))
-    print("MSM_MS", "n", args.n, "g2" if args.g2 else "g1", "pre_c", c, best)
+    for ba in args.ba:
+        if ba >= 0:
+            ctx.set("msm_ba_rounds", ba)
+        best = 1e9
+        for _ in range(args.runs):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(ext)
+            ctx.msm_resident_dev(h, s.data_ptr(), g2=args.g2)
+            e1.record(ext)
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        print("MSM_MS", "n", args.n, "g2" if args.g2 else "g1", "pre_c", c, "ba_rounds", ba, best)
     ctx.bases_free(h)
